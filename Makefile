@@ -1,0 +1,44 @@
+# Top-level build: the product library (CUDA, sm_100a only), the peak probe, the C harness and the checker.
+#   make            -> libdgemm_b200.so + peak_probe + dgemm_b200 harness + oracle
+#   make lib        -> optimizing-dgemm-on-intel-cpus-with-avx512f_b200/libdgemm_b200.so
+# Mirrors the reference's Makefile:1-15 (one `build` target producing dgemm_x86) with an nvcc target added.
+PKG      := optimizing-dgemm-on-intel-cpus-with-avx512f_b200
+CSRC     := $(PKG)/csrc
+NVCC     ?= nvcc
+# the image exports CC/CXX=/opt/gcc/bin/..., wrappers without libgomp: pin the system compilers
+HOSTCC   := /usr/bin/gcc
+HOSTCXX  := /usr/bin/g++
+ARCH     := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS  := $(ARCH) -O3 -lineinfo -std=c++17 -ccbin $(HOSTCXX) -Xcompiler -fPIC -Xcompiler -Wall
+LIB      := $(PKG)/libdgemm_b200.so
+LIB_SRCS := $(CSRC)/dgemm_kernels.cu $(CSRC)/dgemm_api.cu $(CSRC)/dgemm_multi.cu
+LIB_HDRS := $(CSRC)/dgemm_device.cuh $(CSRC)/dgemm_host.h include/dgemm_b200.h
+
+all: lib probe harness oracle
+build: all
+
+lib: $(LIB)
+$(LIB): $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
+probe: $(PKG)/bin/peak_probe
+$(PKG)/bin/peak_probe: $(CSRC)/peak_probe.cu
+	mkdir -p $(PKG)/bin
+	$(NVCC) $(ARCH) -O3 -lineinfo -ccbin $(HOSTCXX) -o $@ $<
+
+harness: $(PKG)/bin/dgemm_b200
+$(PKG)/bin/dgemm_b200: $(PKG)/harness/test.c $(PKG)/harness/utils.c $(PKG)/harness/utils.h include/kernel20.h include/dgemm_b200.h $(LIB)
+	mkdir -p $(PKG)/bin
+	$(HOSTCC) -O2 -Wall -Iinclude -I$(PKG)/harness -o $@ $(PKG)/harness/test.c $(PKG)/harness/utils.c \
+	    -L$(PKG) -ldgemm_b200 -Wl,-rpath,'$$ORIGIN/..' -lm
+
+oracle:
+	$(MAKE) -C oracle all
+
+sass: $(LIB)
+	cuobjdump -sass $(LIB) | grep -E "DMMA|UTMALDG|LDGSTS|SYNCS" | sed 's/\/\*[0-9a-f]*\*\///g' | awk '{print $$1}' | sort | uniq -c
+
+clean:
+	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
+	$(MAKE) -C oracle clean
+.PHONY: all build lib probe harness oracle sass clean

@@ -1,0 +1,106 @@
+/*
+ * dgemm_b200.h — C ABI of the B200 (sm_100a) DGEMM hot path.  Plain C: pointers and sizes only.
+ *
+ * Drop-in boundary: the reference dispatches twenty kernels with one 11-argument signature,
+ *     void mydgemm_cpu_vNN(int M, int N, int K, double alpha, double *A, int LDA, double *B, int LDB,
+ *                          double beta, double *C, int LDC)
+ * (reference include/kernel18.h:629-640, include/kernel19.h:678-689) through test_mydgemm_vNN / test_kernel
+ * (reference utils.c:159-165, 167-191).  mydgemm_gpu_v20 / mydgemm_gpu_v21 below are "one more kernel_number":
+ * same parameters, same meaning, HOST pointers, column-major, NoTrans/NoTrans, C updated in place.
+ * include/kernel20.h wraps them for a kernels.h-style aggregator; INTEGRATION.md shows the reference-side patch.
+ *
+ * Semantics (BLAS / kernel18 order, reference kernel18.h:644-645):
+ *   M == 0 or N == 0      -> no-op
+ *   alpha == 0 or K == 0  -> C = beta*C only (kernel19's skip of the beta scaling, kernel19.h:693, is NOT kept)
+ *   beta == 0             -> C is not read (NaN/Inf in C are overwritten)
+ *   rows M..LDC-1 of every column of C (caller padding) are never written; A and B are read-only
+ *   odd M / N are computed correctly (the reference drops them, kernel18.h:612-625: that bug is NOT kept)
+ * The 11-argument entries return void like the reference's; failures print one line to stderr and set a
+ * status readable with dgemm_b200_last_status().  There is NO CPU fallback: without a usable CUDA device the
+ * call fails with DGEMM_B200_ERR_NO_DEVICE and leaves C untouched.
+ * Threading: entries may be called from any host thread, one call at a time (a process-wide mutex serialises).
+ */
+#ifndef DGEMM_B200_H
+#define DGEMM_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  DGEMM_B200_OK = 0,
+  DGEMM_B200_ERR_NO_DEVICE = 1,    /* no CUDA device / driver, or not compute capability 10.x */
+  DGEMM_B200_ERR_BAD_ARG = 2,      /* negative dimension, LDA < M, LDB < K, LDC < M, null pointer */
+  DGEMM_B200_ERR_OOM = 3,          /* device or pinned-host allocation failed */
+  DGEMM_B200_ERR_CUDA = 4,         /* any other CUDA runtime / driver error (message in last_error) */
+  DGEMM_B200_ERR_NCCL = 5          /* multi-GPU entry: NCCL error */
+};
+
+/* kernel variants, for tests / ablations (dgemm_b200_device_ex) */
+enum {
+  DGEMM_B200_VARIANT_AUTO = 0,
+  DGEMM_B200_VARIANT_TMA = 1,        /* TMA + mbarrier warp-specialised persistent kernel */
+  DGEMM_B200_VARIANT_CPASYNC8 = 2,   /* cp.async 8-byte loader: any alignment / odd leading dimensions */
+  DGEMM_B200_VARIANT_CPASYNC16 = 3   /* cp.async 16-byte loader */
+};
+
+/* ---- the reference's kernel signature (replaces mydgemm_cpu_v18 / v19 at utils.c:159-165) ---------------- */
+/* single GPU; host pointers (pageable or pinned); includes H2D of A, B (and C when beta != 0) and D2H of C */
+void mydgemm_gpu_v20(int M, int N, int K, double alpha, double *A, int LDA, double *B, int LDB, double beta,
+                     double *C, int LDC);
+/* all visible GPUs of the box: column panels of B and C per GPU, A replicated over NVLink with NCCL */
+void mydgemm_gpu_v21(int M, int N, int K, double alpha, double *A, int LDA, double *B, int LDB, double beta,
+                     double *C, int LDC);
+
+int dgemm_b200_last_status(void);        /* status of the most recent call on this thread's process */
+const char *dgemm_b200_last_error(void); /* human-readable message for the last failure ("" if none) */
+
+/* ---- lifetime ------------------------------------------------------------------------------------------- */
+int dgemm_b200_device_count(void);        /* usable sm_100 devices; 0 when there is none */
+int dgemm_b200_init(int device);          /* optional: create the context for `device` now; returns status */
+int dgemm_b200_shutdown(void);            /* frees every cached device / pinned buffer, stream and communicator */
+int dgemm_b200_set_max_gpus(int n);       /* cap the GPUs v21 uses (0 = all visible) */
+
+/* ---- device-pointer API (kernel-only path; what the 11-argument entries call after staging) ----------------
+ * dA, dB, dC are device pointers on the CURRENT device; `stream` is a cudaStream_t (NULL = default stream).
+ * Asynchronous with respect to the host. Returns a status code. */
+int dgemm_b200_device(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
+                      long long ldb, double beta, double *dC, long long ldc, void *stream);
+/* same, forcing a kernel variant and a split-K factor (0 = heuristic) */
+int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
+                         long long ldb, double beta, double *dC, long long ldc, void *stream, int variant,
+                         int splits);
+/* plan the heuristic would use: writes variant, split-K factor, CTA count; returns status */
+int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const double *dB, long long ldb,
+                    int *variant, int *splits, int *ctas);
+
+/* ---- helpers so a plain-C harness needs no CUDA headers -------------------------------------------------------- */
+void *dgemm_b200_malloc(size_t bytes);                 /* device memory on the current device (NULL on failure) */
+void dgemm_b200_free(void *dptr);
+void *dgemm_b200_host_alloc(size_t bytes);             /* pinned host memory */
+void dgemm_b200_host_free(void *hptr);
+/* 2-D column-major copies: `cols` columns of `rows` doubles, leading dimensions in elements */
+int dgemm_b200_h2d(double *dst_dev, long long ldd, const double *src_host, long long lds, long long rows,
+                   long long cols, void *stream);
+int dgemm_b200_d2h(double *dst_host, long long ldd, const double *src_dev, long long lds, long long rows,
+                   long long cols, void *stream);
+int dgemm_b200_sync(void *stream);                      /* cudaStreamSynchronize (NULL: whole device) */
+/* counter-based U(-1,1) fill on the device; entry (i,j) = f(seed, row0+i, col0+j), identical to the oracle's
+ * oracle_signed_value, so huge matrices never have to exist on the host */
+int dgemm_b200_fill_signed(double *dX, int rows, int cols, long long ld, unsigned long long seed,
+                           unsigned long long row0, unsigned long long col0, void *stream);
+/* runs the device call `reps` times between two CUDA events on `stream`; returns average milliseconds
+ * per call (< 0 on failure). flush_l2_bytes > 0: a buffer of that size is overwritten before every rep. */
+double dgemm_b200_time_device(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
+                              long long ldb, double beta, double *dC, long long ldc, int variant, int splits,
+                              int warmup, int reps, size_t flush_l2_bytes);
+/* number of kernels this library has launched since the last reset (bench.py's gpu_launches) */
+int dgemm_b200_launch_count(void);
+void dgemm_b200_reset_launch_count(void);
+/* SM clock (MHz) as seen by a short in-kernel clock64()/globaltimer measurement; < 0 on failure */
+double dgemm_b200_sm_clock_mhz(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGEMM_B200_H */

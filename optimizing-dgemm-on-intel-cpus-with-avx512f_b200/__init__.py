@@ -1,0 +1,190 @@
+"""Python host-side mirror of the reference's dispatch interface for the DGEMM hot path, over the C ABI.
+
+The reference is C: `test_kernel(kernel_num, m, n, k, alpha, A, B, beta, C)` switches to
+`test_mydgemm_vNN`, which fixes LDA=m, LDB=k, LDC=m and calls the 11-argument kernel
+(reference utils.c:159-165, 167-191; include/kernel18.h:629-640).  This module binds
+`libdgemm_b200.so` (include/dgemm_b200.h) with ctypes and exposes the same three levels:
+
+    mydgemm_gpu_v20(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC)   # host numpy arrays, in place
+    test_mydgemm_v20(m, n, k, alpha, A, B, beta, C)                 # LDA=m, LDB=k, LDC=m
+    test_kernel(kernel_num, m, n, k, alpha, A, B, beta, C)          # kernel_num 20 / 21
+
+plus the device-pointer entry used for kernel-only timing.  There is no CPU fallback: if the CUDA
+library is missing, importing this module raises; if there is no sm_100 device, calls raise DgemmError.
+(The package directory name contains hyphens; `import dgemm_b200` at the repo root loads it.)
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdgemm_b200.so")
+
+OK, ERR_NO_DEVICE, ERR_BAD_ARG, ERR_OOM, ERR_CUDA, ERR_NCCL = range(6)
+VARIANT_AUTO, VARIANT_TMA, VARIANT_CPASYNC8, VARIANT_CPASYNC16 = range(4)
+VARIANT_NAMES = {VARIANT_AUTO: "auto", VARIANT_TMA: "tma_ws", VARIANT_CPASYNC8: "cpasync8",
+                 VARIANT_CPASYNC16: "cpasync16"}
+
+# every symbol include/dgemm_b200.h declares (tests check the library exports all of them)
+EXPORTS = [
+    "mydgemm_gpu_v20", "mydgemm_gpu_v21", "dgemm_b200_last_status", "dgemm_b200_last_error",
+    "dgemm_b200_device_count", "dgemm_b200_init", "dgemm_b200_shutdown", "dgemm_b200_set_max_gpus",
+    "dgemm_b200_device", "dgemm_b200_device_ex", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
+    "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
+    "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz",
+]
+
+
+class DgemmError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"dgemm_b200 status {status}: {message}")
+        self.status = status
+
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `make lib` (or __graft_entry__.build()). "
+        "The DGEMM path is CUDA-only; there is no CPU fallback.")
+
+lib = C.CDLL(LIB_PATH)
+_dp = C.POINTER(C.c_double)
+_vp = C.c_void_p
+_ll = C.c_longlong
+
+lib.mydgemm_gpu_v20.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, _vp, C.c_int, _vp, C.c_int, C.c_double, _vp,
+                                C.c_int]
+lib.mydgemm_gpu_v20.restype = None
+lib.mydgemm_gpu_v21.argtypes = lib.mydgemm_gpu_v20.argtypes
+lib.mydgemm_gpu_v21.restype = None
+lib.dgemm_b200_last_error.restype = C.c_char_p
+lib.dgemm_b200_init.argtypes = [C.c_int]
+lib.dgemm_b200_set_max_gpus.argtypes = [C.c_int]
+_DEV_ARGS = [C.c_int, C.c_int, C.c_int, C.c_double, _vp, _ll, _vp, _ll, C.c_double, _vp, _ll]
+lib.dgemm_b200_device.argtypes = _DEV_ARGS + [_vp]
+lib.dgemm_b200_device_ex.argtypes = _DEV_ARGS + [_vp, C.c_int, C.c_int]
+lib.dgemm_b200_plan.argtypes = [C.c_int, C.c_int, C.c_int, _vp, _ll, _vp, _ll, C.POINTER(C.c_int),
+                                C.POINTER(C.c_int), C.POINTER(C.c_int)]
+lib.dgemm_b200_malloc.argtypes = [C.c_size_t]
+lib.dgemm_b200_malloc.restype = _vp
+lib.dgemm_b200_free.argtypes = [_vp]
+lib.dgemm_b200_free.restype = None
+lib.dgemm_b200_host_alloc.argtypes = [C.c_size_t]
+lib.dgemm_b200_host_alloc.restype = _vp
+lib.dgemm_b200_host_free.argtypes = [_vp]
+lib.dgemm_b200_host_free.restype = None
+lib.dgemm_b200_h2d.argtypes = [_vp, _ll, _vp, _ll, _ll, _ll, _vp]
+lib.dgemm_b200_d2h.argtypes = [_vp, _ll, _vp, _ll, _ll, _ll, _vp]
+lib.dgemm_b200_sync.argtypes = [_vp]
+lib.dgemm_b200_fill_signed.argtypes = [_vp, C.c_int, C.c_int, _ll, C.c_ulonglong, C.c_ulonglong, C.c_ulonglong, _vp]
+lib.dgemm_b200_time_device.argtypes = _DEV_ARGS + [C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t]
+lib.dgemm_b200_time_device.restype = C.c_double
+lib.dgemm_b200_reset_launch_count.restype = None
+lib.dgemm_b200_sm_clock_mhz.restype = C.c_double
+
+
+def last_status():
+    return lib.dgemm_b200_last_status()
+
+
+def last_error():
+    return (lib.dgemm_b200_last_error() or b"").decode()
+
+
+def _check(status=None):
+    st = lib.dgemm_b200_last_status() if status is None else status
+    if st != OK:
+        raise DgemmError(st, last_error())
+
+
+def device_count():
+    return lib.dgemm_b200_device_count()
+
+
+def _host_ptr(a):
+    if isinstance(a, np.ndarray):
+        if a.dtype != np.float64:
+            raise TypeError("matrices must be float64")
+        if not a.flags.f_contiguous:
+            raise ValueError("matrices must be column-major (Fortran-ordered) numpy arrays of shape (ld, cols)")
+        return a.ctypes.data
+    return int(a)  # raw host address (e.g. pinned memory)
+
+
+# ---- the reference's three dispatch levels ------------------------------------------------------------------
+def mydgemm_gpu_v20(M, N, K, alpha, A, LDA, B, LDB, beta, Cm, LDC):
+    """C = alpha*A*B + beta*C on one B200; host operands; same 11 arguments as mydgemm_cpu_v18."""
+    lib.mydgemm_gpu_v20(M, N, K, float(alpha), _host_ptr(A), LDA, _host_ptr(B), LDB, float(beta), _host_ptr(Cm), LDC)
+    _check()
+
+
+def mydgemm_gpu_v21(M, N, K, alpha, A, LDA, B, LDB, beta, Cm, LDC):
+    """Same call sharded over all visible B200s (column panels of B and C, A replicated with NCCL)."""
+    lib.mydgemm_gpu_v21(M, N, K, float(alpha), _host_ptr(A), LDA, _host_ptr(B), LDB, float(beta), _host_ptr(Cm), LDC)
+    _check()
+
+
+def test_mydgemm_v20(m, n, k, alpha, A, B, beta, Cm):
+    """reference utils.c:159-165 wrapper shape: LDA=m, LDB=k, LDC=m."""
+    mydgemm_gpu_v20(m, n, k, alpha, A, m, B, k, beta, Cm, m)
+
+
+def test_mydgemm_v21(m, n, k, alpha, A, B, beta, Cm):
+    mydgemm_gpu_v21(m, n, k, alpha, A, m, B, k, beta, Cm, m)
+
+
+def test_kernel(kernel_num, m, n, k, alpha, A, B, beta, Cm):
+    """reference utils.c:167-191 switch, for the two kernel numbers this package adds."""
+    if kernel_num == 20:
+        test_mydgemm_v20(m, n, k, alpha, A, B, beta, Cm)
+    elif kernel_num == 21:
+        test_mydgemm_v21(m, n, k, alpha, A, B, beta, Cm)
+    else:
+        raise ValueError("this package provides kernel_num 20 (one B200) and 21 (all B200s of the box)")
+
+
+# ---- device-pointer entry -----------------------------------------------------------------------------------------
+def dgemm_device(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0, variant=VARIANT_AUTO, splits=0):
+    """Asynchronous DGEMM on device pointers of the current CUDA device (ints / data_ptr())."""
+    st = lib.dgemm_b200_device_ex(M, N, K, float(alpha), int(dA), lda, int(dB), ldb, float(beta), int(dC), ldc,
+                                  int(stream) or None, variant, splits)
+    _check(st)
+
+
+def plan(M, N, K, dA=0, lda=None, dB=0, ldb=None):
+    v, s, c = C.c_int(), C.c_int(), C.c_int()
+    st = lib.dgemm_b200_plan(M, N, K, int(dA) or None, lda or max(M, 1), int(dB) or None, ldb or max(K, 1),
+                             C.byref(v), C.byref(s), C.byref(c))
+    _check(st)
+    return {"variant": VARIANT_NAMES[v.value], "splits": s.value, "ctas": c.value}
+
+
+def time_device(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, variant=VARIANT_AUTO, splits=0, warmup=3, reps=5,
+                flush_l2_bytes=0):
+    ms = lib.dgemm_b200_time_device(M, N, K, float(alpha), int(dA), lda, int(dB), ldb, float(beta), int(dC), ldc,
+                                    variant, splits, warmup, reps, flush_l2_bytes)
+    if ms < 0:
+        _check()
+        raise DgemmError(ERR_CUDA, "timed run failed")
+    return ms
+
+
+def fill_signed(dX, rows, cols, ld, seed, row0=0, col0=0, stream=0):
+    _check(lib.dgemm_b200_fill_signed(int(dX), rows, cols, ld, seed, row0, col0, int(stream) or None))
+
+
+def launch_count():
+    return lib.dgemm_b200_launch_count()
+
+
+def reset_launch_count():
+    lib.dgemm_b200_reset_launch_count()
+
+
+def sm_clock_mhz():
+    return lib.dgemm_b200_sm_clock_mhz()
+
+
+def shutdown():
+    lib.dgemm_b200_shutdown()

@@ -1,0 +1,546 @@
+// dgemm_api.cu — the C ABI declared in include/dgemm_b200.h: argument checking, planning (variant, split-K),
+// per-device context (streams, cached device buffers, split-K workspace), host staging for the 11-argument
+// reference signature (reference include/kernel18.h:629-640 / utils.c:159-165) and timing helpers.
+// No CPU fallback: every path ends in a kernel from dgemm_kernels.cu or fails with a status.
+#include "../../include/dgemm_b200.h"
+#include "dgemm_device.cuh"
+#include "dgemm_host.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+std::recursive_mutex g_mu;
+int g_status = DGEMM_B200_OK;
+char g_errmsg[512] = "";
+
+int fail(int status, const char* fmt, ...) {
+  g_status = status;
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_errmsg, sizeof(g_errmsg), fmt, ap);
+  va_end(ap);
+  fprintf(stderr, "dgemm_b200: error %d: %s\n", status, g_errmsg);
+  return status;
+}
+int ok() {
+  g_status = DGEMM_B200_OK;
+  g_errmsg[0] = 0;
+  return DGEMM_B200_OK;
+}
+
+#define CU_TRY(expr)                                                                                   \
+  do {                                                                                                 \
+    cudaError_t e_ = (expr);                                                                           \
+    if (e_ != cudaSuccess)                                                                             \
+      return fail(e_ == cudaErrorMemoryAllocation ? DGEMM_B200_ERR_OOM : DGEMM_B200_ERR_CUDA, "%s: %s", \
+                  #expr, cudaGetErrorString(e_));                                                      \
+  } while (0)
+
+// ---- per-device context ----------------------------------------------------------------------------------
+struct Buf {
+  double* p = nullptr;
+  size_t cap = 0;  // bytes
+};
+struct DeviceCtx {
+  int dev = -1;
+  int num_sms = 0;
+  bool ready = false;
+  cudaStream_t s_compute = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+  Buf ws;                     // split-K workspace
+  cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
+  bool ws_used = false;
+  Buf a, b, c;                // staging for the host-pointer entries
+  Buf flush;                  // L2 flush buffer for dgemm_b200_time_device
+};
+constexpr int MAX_DEV = 16;
+DeviceCtx g_ctx[MAX_DEV];
+int g_ndev = -1;  // usable devices (compute capability 10.x), -1 = not probed
+int g_max_gpus = 0;
+
+int probe_devices() {
+  if (g_ndev >= 0) return g_ndev;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  int usable = 0;
+  for (int d = 0; d < n && d < MAX_DEV; d++) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) != cudaSuccess) break;
+    if (major != 10) break;  // the fatbin holds sm_100a code only
+    usable++;
+  }
+  g_ndev = usable;
+  return g_ndev;
+}
+
+int ensure_ctx(int dev, DeviceCtx** out) {
+  if (probe_devices() <= 0)
+    return fail(DGEMM_B200_ERR_NO_DEVICE, "no usable sm_100 CUDA device (this library has no CPU fallback)");
+  if (dev < 0 || dev >= g_ndev) return fail(DGEMM_B200_ERR_BAD_ARG, "device %d out of range (0..%d)", dev, g_ndev - 1);
+  DeviceCtx& c = g_ctx[dev];
+  if (!c.ready) {
+    int prev = 0;
+    cudaGetDevice(&prev);
+    CU_TRY(cudaSetDevice(dev));
+    c.dev = dev;
+    CU_TRY(cudaDeviceGetAttribute(&c.num_sms, cudaDevAttrMultiProcessorCount, dev));
+    CU_TRY(cudaStreamCreateWithFlags(&c.s_compute, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&c.ws_free, cudaEventDisableTiming));
+    c.ready = true;
+    cudaSetDevice(prev);
+  }
+  *out = &c;
+  return DGEMM_B200_OK;
+}
+
+int grow(Buf& b, size_t bytes) {
+  if (b.cap >= bytes) return DGEMM_B200_OK;
+  if (b.p) {
+    CU_TRY(cudaDeviceSynchronize());
+    cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  size_t want = bytes + bytes / 8;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    want = bytes;
+    e = cudaMalloc(&b.p, want);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    b.p = nullptr;
+    return fail(DGEMM_B200_ERR_OOM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+  }
+  b.cap = want;
+  return DGEMM_B200_OK;
+}
+
+// ---- planning ------------------------------------------------------------------------------------------------
+// Cost model in units of one k-tile (16 k) of main-loop time on one SM (~2048 clk ~ 1 us):
+//   waves * (k-tiles per unit + pipeline fill) [+ split-K: partial store, reduce pass and its launch]
+int choose_splits(int tiles, int k_tiles, int num_sms) {
+  if (k_tiles < 16) return 1;
+  double best = 1e300;
+  int best_s = 1;
+  const int max_s = std::min(32, k_tiles / 8);
+  for (int s = 1; s <= max_s; s++) {
+    const long long units = (long long)tiles * s;
+    const long long waves = (units + num_sms - 1) / num_sms;
+    const int kt = (k_tiles + s - 1) / s;
+    double t = (double)waves * (kt + 6.0);
+    if (s > 1) t += waves * 3.0 + 5.0 + (double)units * 0.02 * 2.0;  // partial write + reduce read, ~0.02 per 128 KB
+    if (t < best * 0.97) {  // prefer fewer splits unless the gain is real
+      best = t;
+      best_s = s;
+    }
+  }
+  return best_s;
+}
+
+int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
+                long long ldb, double beta, double* dC, long long ldc, int splits, int num_sms) {
+  P.M = M; P.N = N; P.K = K;
+  P.alpha = alpha; P.beta = beta;
+  P.A = dA; P.lda = lda; P.B = dB; P.ldb = ldb; P.C = dC; P.ldc = ldc;
+  P.tiles_m = (M + dg::BM - 1) / dg::BM;
+  P.tiles_n = (N + dg::BN - 1) / dg::BN;
+  P.k_tiles = (K + dg::BK - 1) / dg::BK;
+  const int tiles = P.tiles_m * P.tiles_n;
+  if (splits <= 0) splits = choose_splits(tiles, P.k_tiles, num_sms);
+  splits = std::max(1, std::min(splits, P.k_tiles));
+  P.k_tiles_per_split = (P.k_tiles + splits - 1) / splits;
+  P.splits = (P.k_tiles + P.k_tiles_per_split - 1) / P.k_tiles_per_split;  // no empty splits
+  // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
+  P.group_m = std::min(P.tiles_m, 16);
+  P.c_vec2 = ((uintptr_t)dC % 16 == 0) && (ldc % 2 == 0);
+  P.workspace = nullptr;
+  return DGEMM_B200_OK;
+}
+
+int check_args(int M, int N, int K, const void* A, long long lda, const void* B, long long ldb, const void* C,
+               long long ldc) {
+  if (M < 0 || N < 0 || K < 0) return fail(DGEMM_B200_ERR_BAD_ARG, "negative dimension M=%d N=%d K=%d", M, N, K);
+  if (lda < std::max(1, M)) return fail(DGEMM_B200_ERR_BAD_ARG, "LDA=%lld < max(1,M)=%d", lda, std::max(1, M));
+  if (ldb < std::max(1, K)) return fail(DGEMM_B200_ERR_BAD_ARG, "LDB=%lld < max(1,K)=%d", ldb, std::max(1, K));
+  if (ldc < std::max(1, M)) return fail(DGEMM_B200_ERR_BAD_ARG, "LDC=%lld < max(1,M)=%d", ldc, std::max(1, M));
+  if (M > 0 && N > 0 && !C) return fail(DGEMM_B200_ERR_BAD_ARG, "C is NULL");
+  if (M > 0 && N > 0 && K > 0 && (!A || !B)) return fail(DGEMM_B200_ERR_BAD_ARG, "A or B is NULL");
+  return DGEMM_B200_OK;
+}
+
+// the device-side DGEMM on context c (current device must be c.dev)
+int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
+               long long ldb, double beta, double* dC, long long ldc, cudaStream_t stream, int variant, int splits) {
+  if (M == 0 || N == 0) return ok();
+  if (alpha == 0.0 || K == 0) {  // C = beta*C only (kernel18.h:644-645)
+    CU_TRY(dg::launch_scale_c(dC, M, N, ldc, beta, c.num_sms, stream));
+    return ok();
+  }
+  dg::Params P;
+  fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, c.num_sms);
+  const bool tma_ok = dg::tma_eligible(P);
+  if (variant == dg::VARIANT_AUTO) variant = tma_ok ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  if ((variant == dg::VARIANT_TMA || variant == dg::VARIANT_CPASYNC16) && !tma_ok)
+    return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
+  if (P.splits > 1) {
+    const size_t need = (size_t)P.tiles_m * P.tiles_n * P.splits * dg::BM * dg::BN * sizeof(double);
+    if (c.ws.cap < need) {
+      int st = grow(c.ws, need);
+      if (st) return st;
+      c.ws_used = false;
+    }
+    if (c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream) done
+    P.workspace = c.ws.p;
+  }
+  CU_TRY(dg::launch_gemm(P, variant, c.num_sms, stream));
+  if (P.splits > 1) {
+    CU_TRY(cudaEventRecord(c.ws_free, stream));
+    c.ws_used = true;
+  }
+  return ok();
+}
+
+int current_ctx(DeviceCtx** out) {
+  if (probe_devices() <= 0)
+    return fail(DGEMM_B200_ERR_NO_DEVICE, "no usable sm_100 CUDA device (this library has no CPU fallback)");
+  int dev = 0;
+  CU_TRY(cudaGetDevice(&dev));
+  return ensure_ctx(dev, out);
+}
+
+// ---- host-pointer path: one GPU, column panels pipelined H2D -> DGEMM -> D2H ---------------------------------
+int run_host_single(int dev, int M, int N, int K, double alpha, const double* A, int LDA, const double* B, int LDB,
+                    double beta, double* C, int LDC) {
+  int st = check_args(M, N, K, A, LDA, B, LDB, C, LDC);
+  if (st) return st;
+  if (M == 0 || N == 0) return ok();
+  DeviceCtx* cp;
+  if ((st = ensure_ctx(dev, &cp))) return st;
+  DeviceCtx& c = *cp;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  CU_TRY(cudaSetDevice(dev));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+
+  const bool need_ab = !(alpha == 0.0 || K == 0);
+  const bool need_c_in = beta != 0.0;
+  // compact, TMA-friendly device layouts: leading dimensions rounded up to even
+  const long long ldaD = (M + 1) & ~1ll, ldbD = (K + 1) & ~1ll, ldcD = (M + 1) & ~1ll;
+  if (need_ab) {
+    if ((st = grow(c.a, (size_t)ldaD * K * 8))) return st;
+    if ((st = grow(c.b, (size_t)ldbD * N * 8))) return st;
+  }
+  if ((st = grow(c.c, (size_t)ldcD * N * 8))) return st;
+
+  // panel width: multiple of the CTA tile, >= 4 panels for overlap when N allows, each panel >= ~1 wave of tiles
+  int panel = N;
+  if (need_ab && N >= 4 * dg::BN) {
+    const int tiles_m = (M + dg::BM - 1) / dg::BM;
+    int min_cols = ((c.num_sms + tiles_m - 1) / tiles_m) * dg::BN;  // one full wave of CTAs
+    panel = std::max(min_cols, ((N / 8 + dg::BN - 1) / dg::BN) * dg::BN);
+    panel = std::min(panel, N);
+  }
+  const int npanels = (N + panel - 1) / panel;
+  std::vector<cudaEvent_t> ev_in(npanels), ev_done(npanels);
+  for (int p = 0; p < npanels; p++) {
+    CU_TRY(cudaEventCreateWithFlags(&ev_in[p], cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&ev_done[p], cudaEventDisableTiming));
+  }
+  int result = DGEMM_B200_OK;
+  auto body = [&]() -> int {
+    if (need_ab)
+      CU_TRY(cudaMemcpy2DAsync(c.a.p, ldaD * 8, A, (size_t)LDA * 8, (size_t)M * 8, K, cudaMemcpyHostToDevice, c.s_h2d));
+    for (int p = 0; p < npanels; p++) {
+      const int n0 = p * panel, nb = std::min(panel, N - n0);
+      if (need_ab)
+        CU_TRY(cudaMemcpy2DAsync(c.b.p + (size_t)n0 * ldbD, ldbD * 8, B + (size_t)n0 * LDB, (size_t)LDB * 8,
+                                 (size_t)K * 8, nb, cudaMemcpyHostToDevice, c.s_h2d));
+      if (need_c_in)
+        CU_TRY(cudaMemcpy2DAsync(c.c.p + (size_t)n0 * ldcD, ldcD * 8, C + (size_t)n0 * LDC, (size_t)LDC * 8,
+                                 (size_t)M * 8, nb, cudaMemcpyHostToDevice, c.s_h2d));
+      CU_TRY(cudaEventRecord(ev_in[p], c.s_h2d));
+      CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[p], 0));
+      int s2 = run_device(c, M, nb, K, alpha, c.a.p, ldaD, c.b.p + (size_t)n0 * ldbD, ldbD, beta,
+                          c.c.p + (size_t)n0 * ldcD, ldcD, c.s_compute, dg::VARIANT_AUTO, 0);
+      if (s2) return s2;
+      CU_TRY(cudaEventRecord(ev_done[p], c.s_compute));
+      CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done[p], 0));
+      CU_TRY(cudaMemcpy2DAsync(C + (size_t)n0 * LDC, (size_t)LDC * 8, c.c.p + (size_t)n0 * ldcD, ldcD * 8,
+                               (size_t)M * 8, nb, cudaMemcpyDeviceToHost, c.s_d2h));
+    }
+    CU_TRY(cudaStreamSynchronize(c.s_d2h));
+    CU_TRY(cudaStreamSynchronize(c.s_compute));
+    CU_TRY(cudaStreamSynchronize(c.s_h2d));
+    return DGEMM_B200_OK;
+  };
+  result = body();
+  for (int p = 0; p < npanels; p++) {
+    cudaEventDestroy(ev_in[p]);
+    cudaEventDestroy(ev_done[p]);
+  }
+  return result ? result : ok();
+}
+
+__global__ void clock_probe_kernel(unsigned long long* out) {
+  unsigned long long c0 = clock64(), t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  double x = threadIdx.x;
+  for (int i = 0; i < 20000; i++) x = fma(x, 1.0000001, 1e-9);
+  unsigned long long c1 = clock64();
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+  if (threadIdx.x == 0) { out[0] = c1 - c0; out[1] = t1 - t0; out[2] = (unsigned long long)x; }
+}
+
+}  // namespace
+
+// multi-GPU entry lives in dgemm_multi.cu
+void dgemm_b200_multi_shutdown();
+int dgemm_b200_run_host_multi(int M, int N, int K, double alpha, const double* A, int LDA, const double* B, int LDB,
+                              double beta, double* C, int LDC, int max_gpus);
+
+// shared with dgemm_multi.cu
+int dgemm_b200_internal_fail(int status, const char* msg) { return fail(status, "%s", msg); }
+int dgemm_b200_internal_ok() { return ok(); }
+std::recursive_mutex& dgemm_b200_internal_mutex() { return g_mu; }
+int dgemm_b200_internal_run_on(int dev, int M, int N, int K, double alpha, const double* dA, long long lda,
+                               const double* dB, long long ldb, double beta, double* dC, long long ldc,
+                               cudaStream_t stream) {
+  DeviceCtx* c = nullptr;
+  int st = ensure_ctx(dev, &c);
+  if (st) return st;
+  return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream, dg::VARIANT_AUTO, 0);
+}
+
+extern "C" {
+
+void mydgemm_gpu_v20(int M, int N, int K, double alpha, double* A, int LDA, double* B, int LDB, double beta, double* C,
+                     int LDC) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  int dev = 0;
+  if (const char* e = getenv("DGEMM_B200_DEVICE")) dev = atoi(e);
+  run_host_single(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
+}
+
+void mydgemm_gpu_v21(int M, int N, int K, double alpha, double* A, int LDA, double* B, int LDB, double beta, double* C,
+                     int LDC) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  int st = check_args(M, N, K, A, LDA, B, LDB, C, LDC);
+  if (st) return;
+  if (probe_devices() <= 0) {
+    fail(DGEMM_B200_ERR_NO_DEVICE, "no usable sm_100 CUDA device (this library has no CPU fallback)");
+    return;
+  }
+  int g = g_ndev;
+  if (g_max_gpus > 0) g = std::min(g, g_max_gpus);
+  if (const char* e = getenv("DGEMM_B200_MAX_GPUS")) g = std::max(1, std::min(g, atoi(e)));
+  if (g <= 1 || N < 2 * dg::BN) {
+    run_host_single(0, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
+    return;
+  }
+  dgemm_b200_run_host_multi(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC, g);
+}
+
+int dgemm_b200_last_status(void) { return g_status; }
+const char* dgemm_b200_last_error(void) { return g_errmsg; }
+
+int dgemm_b200_device_count(void) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  return probe_devices();
+}
+int dgemm_b200_init(int device) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  DeviceCtx* c;
+  int st = ensure_ctx(device, &c);
+  return st ? st : ok();
+}
+int dgemm_b200_set_max_gpus(int n) {
+  g_max_gpus = n < 0 ? 0 : n;
+  return DGEMM_B200_OK;
+}
+
+int dgemm_b200_shutdown(void) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  dgemm_b200_multi_shutdown();
+  int prev = 0;
+  if (g_ndev > 0) cudaGetDevice(&prev);
+  for (int d = 0; d < MAX_DEV; d++) {
+    DeviceCtx& c = g_ctx[d];
+    if (!c.ready) continue;
+    cudaSetDevice(d);
+    cudaDeviceSynchronize();
+    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.flush}) {
+      if (b->p) cudaFree(b->p);
+      b->p = nullptr;
+      b->cap = 0;
+    }
+    cudaStreamDestroy(c.s_compute);
+    cudaStreamDestroy(c.s_h2d);
+    cudaStreamDestroy(c.s_d2h);
+    cudaEventDestroy(c.ws_free);
+    c = DeviceCtx();
+  }
+  if (g_ndev > 0) cudaSetDevice(prev);
+  return ok();
+}
+
+int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
+                         long long ldb, double beta, double* dC, long long ldc, void* stream, int variant, int splits) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  int st = check_args(M, N, K, dA, lda, dB, ldb, dC, ldc);
+  if (st) return st;
+  DeviceCtx* c;
+  if ((st = current_ctx(&c))) return st;
+  return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, (cudaStream_t)stream, variant, splits);
+}
+
+int dgemm_b200_device(int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
+                      long long ldb, double beta, double* dC, long long ldc, void* stream) {
+  return dgemm_b200_device_ex(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream, DGEMM_B200_VARIANT_AUTO, 0);
+}
+
+int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const double* dB, long long ldb, int* variant,
+                    int* splits, int* ctas) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  DeviceCtx* c;
+  int st = current_ctx(&c);
+  if (st) return st;
+  dg::Params P;
+  fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, c->num_sms);
+  const int v = dg::tma_eligible(P) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  if (variant) *variant = v;
+  if (splits) *splits = P.splits;
+  const int units = P.tiles_m * P.tiles_n * P.splits;
+  if (ctas) *ctas = v == dg::VARIANT_TMA ? std::min(units, c->num_sms) : units;
+  return ok();
+}
+
+void* dgemm_b200_malloc(size_t bytes) {
+  void* p = nullptr;
+  if (probe_devices() <= 0) {
+    fail(DGEMM_B200_ERR_NO_DEVICE, "no usable sm_100 CUDA device");
+    return nullptr;
+  }
+  cudaError_t e = cudaMalloc(&p, bytes ? bytes : 1);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    fail(DGEMM_B200_ERR_OOM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    return nullptr;
+  }
+  return p;
+}
+void dgemm_b200_free(void* dptr) {
+  if (dptr) cudaFree(dptr);
+}
+void* dgemm_b200_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (probe_devices() <= 0) {
+    fail(DGEMM_B200_ERR_NO_DEVICE, "no usable sm_100 CUDA device");
+    return nullptr;
+  }
+  cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    fail(DGEMM_B200_ERR_OOM, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    return nullptr;
+  }
+  return p;
+}
+void dgemm_b200_host_free(void* hptr) {
+  if (hptr) cudaFreeHost(hptr);
+}
+int dgemm_b200_h2d(double* dst_dev, long long ldd, const double* src_host, long long lds, long long rows, long long cols,
+                   void* stream) {
+  if (rows <= 0 || cols <= 0) return ok();
+  CU_TRY(cudaMemcpy2DAsync(dst_dev, (size_t)ldd * 8, src_host, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
+                           cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return ok();
+}
+int dgemm_b200_d2h(double* dst_host, long long ldd, const double* src_dev, long long lds, long long rows, long long cols,
+                   void* stream) {
+  if (rows <= 0 || cols <= 0) return ok();
+  CU_TRY(cudaMemcpy2DAsync(dst_host, (size_t)ldd * 8, src_dev, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
+                           cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return ok();
+}
+int dgemm_b200_sync(void* stream) {
+  if (stream) CU_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  else CU_TRY(cudaDeviceSynchronize());
+  return ok();
+}
+int dgemm_b200_fill_signed(double* dX, int rows, int cols, long long ld, unsigned long long seed,
+                           unsigned long long row0, unsigned long long col0, void* stream) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  DeviceCtx* c;
+  int st = current_ctx(&c);
+  if (st) return st;
+  CU_TRY(dg::launch_fill_signed(dX, rows, cols, ld, seed, row0, col0, c->num_sms, (cudaStream_t)stream));
+  return ok();
+}
+
+double dgemm_b200_time_device(int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
+                              long long ldb, double beta, double* dC, long long ldc, int variant, int splits, int warmup,
+                              int reps, size_t flush_l2_bytes) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  DeviceCtx* c;
+  if (current_ctx(&c)) return -1.0;
+  if (check_args(M, N, K, dA, lda, dB, ldb, dC, ldc)) return -1.0;
+  if (flush_l2_bytes && grow(c->flush, flush_l2_bytes)) return -1.0;
+  cudaStream_t s = c->s_compute;
+  for (int i = 0; i < warmup; i++)
+    if (run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, s, variant, splits)) return -1.0;
+  cudaEvent_t e0, e1;
+  if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return -1.0;
+  double total_ms = 0.0;
+  bool bad = false;
+  for (int i = 0; i < reps && !bad; i++) {
+    if (flush_l2_bytes) cudaMemsetAsync(c->flush.p, i & 0xff, flush_l2_bytes, s);
+    cudaEventRecord(e0, s);
+    if (run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, s, variant, splits)) bad = true;
+    cudaEventRecord(e1, s);
+    if (cudaEventSynchronize(e1) != cudaSuccess) bad = true;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    total_ms += ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (bad) {
+    cudaError_t e = cudaGetLastError();
+    if (g_status == DGEMM_B200_OK) fail(DGEMM_B200_ERR_CUDA, "timed run failed: %s", cudaGetErrorString(e));
+    return -1.0;
+  }
+  return total_ms / std::max(1, reps);
+}
+
+int dgemm_b200_launch_count(void) { return dg::launch_count(); }
+void dgemm_b200_reset_launch_count(void) { dg::reset_launch_count(); }
+
+double dgemm_b200_sm_clock_mhz(void) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  DeviceCtx* c;
+  if (current_ctx(&c)) return -1.0;
+  unsigned long long* d = nullptr;
+  unsigned long long h[3] = {0, 0, 0};
+  if (cudaMalloc(&d, sizeof(h)) != cudaSuccess) return -1.0;
+  clock_probe_kernel<<<1, 32, 0, c->s_compute>>>(d);
+  cudaError_t e = cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, c->s_compute);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->s_compute);
+  cudaFree(d);
+  if (e != cudaSuccess || h[1] == 0) return -1.0;
+  return 1e3 * (double)h[0] / (double)h[1];
+}
+
+}  // extern "C"

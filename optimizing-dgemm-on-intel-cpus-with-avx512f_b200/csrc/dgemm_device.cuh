@@ -1,0 +1,257 @@
+// dgemm_device.cuh — device-side building blocks of the B200 DGEMM (column-major C = alpha*A*B + beta*C).
+//
+// Replaces the reference's micro/macro kernel (include/kernel18.h:113-626: COMPUTE_m24n8 ... macro_kernel_k18),
+// its packing routines (packing_a_k18 / packing_b_k18, kernel18.h:48-110) and its separate beta pass
+// (scale_c_k18, kernel18.h:12-46).  Nothing here is translated from that code: the register tile is a
+// warp-level FP64 tensor-core tile (mma.sync.m8n8k4.f64 -> SASS DMMA.8x8x4, the only native FP64 MMA on
+// sm_100a), "packing" is a swizzled shared-memory tile written by TMA (or cp.async), and beta is fused
+// into the epilogue.
+//
+// CTA tile 128(m) x 128(n) x 16(k) per pipeline stage, 8 consumer warps, warp tile 64(m) x 32(n):
+//   * A stage  = 8 sub-tiles of [16 k][16 m] doubles (2 KB each, m contiguous = column-major A as it lies
+//                in HBM), 128-byte rows, SWIZZLE_128B with the k index as the swizzle row;
+//   * B stage  = [128 n][16 k] doubles (k contiguous = column-major B), 128-byte rows, SWIZZLE_128B with
+//                the n index as the swizzle row.
+// The MMA is fed "transposed": the m8n8k4 row operand comes from B (rows = n), the column operand from A
+// (cols = m), so every lane's accumulator pair is two CONSECUTIVE ROWS of one column of C -> 16-byte
+// stores into column-major C.  Which n / m a lane feeds is permuted (kPermN / kMapM) so that every
+// LDS.64 of a fragment is bank-conflict free under the 128B swizzle (tools/check_swizzle.py enumerates it).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dg {
+
+constexpr int BM = 128;
+constexpr int BN = 128;
+constexpr int BK = 16;
+constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KiB
+constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KiB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int CONSUMER_WARPS = 8;
+constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
+constexpr int WARPS_M = 2;  // warp grid inside the CTA tile: 2 (m) x 4 (n)
+constexpr int WARPS_N = 4;
+constexpr int WM = BM / WARPS_M;  // 64
+constexpr int WN = BN / WARPS_N;  // 32
+constexpr int FRAG_M = WM / 8;    // 8 column fragments (from A)
+constexpr int FRAG_N = WN / 8;    // 4 row fragments (from B)
+constexpr int ACC_PER_THREAD = FRAG_M * FRAG_N * 2;  // 64 doubles = 128 registers
+
+struct Params {
+  int M, N, K;
+  double alpha, beta;
+  const double* A; long long lda;
+  const double* B; long long ldb;
+  double* C; long long ldc;
+  int tiles_m, tiles_n;
+  int k_tiles;            // ceil(K / BK)
+  int splits;             // split-K factor, 1 = none
+  int k_tiles_per_split;  // ceil(k_tiles / splits)
+  int group_m;            // rasterisation: tiles are walked in bands of group_m tile-rows
+  int c_vec2;             // C base 16-byte aligned and ldc even -> 16-byte epilogue accesses
+  double* workspace;      // splits > 1: [split][tile][ACC_PER_THREAD][CONSUMER_THREADS] partial accumulators
+};
+
+// ---- lane -> matrix index maps (see header comment) -------------------------------------------------------
+// row fragment (from B): mma row r = lane/4 feeds n = 8*t + kPermN(r)
+__device__ __forceinline__ int perm_n(int r) { return ((r & 3) << 1) | (r >> 2); }  // 0,2,4,6,1,3,5,7
+// column fragment (from A): mma col c feeds m = 16*s + 4*f + kMapM(c)
+__device__ __forceinline__ int map_m(int c) { return (c & 1) | ((c & 2) << 2) | ((c & 4) >> 1); }  // 0,1,8,9,2,3,10,11
+
+// ---- raw PTX wrappers ----------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double v;
+  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
+
+// D(8x8) += Arow(8x4) * Bcol(4x8), FP64 tensor core.  SASS: DMMA.8x8x4
+__device__ __forceinline__ void dmma_8x8x4(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(bar), "r"(parity)
+      : "memory");
+}
+// TMA: 2-D tiled load global -> shared, completion counted on an mbarrier.  SASS: UTMALDG.2D
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+// cp.async with zero fill (src_bytes = 0 -> the destination is filled with zeros).  SASS: LDGSTS
+template <int BYTES>
+__device__ __forceinline__ void cp_async_zfill(uint32_t dst, const void* src, int src_bytes) {
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// ---- swizzled shared-memory offsets (bytes inside one stage's A or B region) ----------------------------
+// A element (m_local, k_local): sub-tile m_local/16, row k_local, 16-byte chunk (mm/2) ^ (k_local & 7)
+__device__ __forceinline__ uint32_t a_smem_off(int m_local, int k_local) {
+  int mm = m_local & 15;
+  return (uint32_t)((m_local >> 4) * 2048 + k_local * 128 + ((((mm >> 1) ^ (k_local & 7))) << 4) + ((mm & 1) << 3));
+}
+// B element (k_local, n_local): row n_local, 16-byte chunk (k_local/2) ^ (n_local & 7)
+__device__ __forceinline__ uint32_t b_smem_off(int k_local, int n_local) {
+  return (uint32_t)(n_local * 128 + ((((k_local >> 1) ^ (n_local & 7))) << 4) + ((k_local & 1) << 3));
+}
+
+// Per-lane fragment offsets, computed once per thread.
+struct LaneOffsets {
+  uint32_t a[2][2];  // [k-parity p = kk&1][f]: row (p*4+q), col 4f + map_m(r), sub-tile 0
+  uint32_t b[4];     // [kk]: row perm_n(r), k = kk*4+q, n-block 0
+};
+__device__ __forceinline__ LaneOffsets make_lane_offsets(int lane, int warp_m, int warp_n) {
+  const int r = lane >> 2, q = lane & 3;
+  LaneOffsets lo;
+#pragma unroll
+  for (int p = 0; p < 2; p++)
+#pragma unroll
+    for (int f = 0; f < 2; f++) lo.a[p][f] = a_smem_off(warp_m * WM + 4 * f + map_m(r), p * 4 + q);
+#pragma unroll
+  for (int kk = 0; kk < 4; kk++) lo.b[kk] = b_smem_off(kk * 4 + q, warp_n * WN + perm_n(r));
+  return lo;
+}
+
+// One pipeline stage (16 k) of the warp tile: 4 k-steps x (8 + 4 fragment loads, 32 DMMAs).
+__device__ __forceinline__ void mma_stage(double (&acc)[FRAG_N][FRAG_M][2], uint32_t sA, uint32_t sB,
+                                          const LaneOffsets& lo) {
+#pragma unroll
+  for (int kk = 0; kk < BK / 4; kk++) {
+    double a[FRAG_M], b[FRAG_N];
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++)  // sub-tile j/2, half f = j&1; rows kk*4.. -> (kk>>1)*1024 + (kk&1)*512
+      a[j] = lds_f64(sA + lo.a[kk & 1][j & 1] + (kk >> 1) * 1024 + (j >> 1) * 2048);
+#pragma unroll
+    for (int i = 0; i < FRAG_N; i++) b[i] = lds_f64(sB + lo.b[kk] + i * 1024);
+#pragma unroll
+    for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+      for (int j = 0; j < FRAG_M; j++) dmma_8x8x4(acc[i][j][0], acc[i][j][1], b[i], a[j]);
+  }
+}
+
+__device__ __forceinline__ void zero_acc(double (&acc)[FRAG_N][FRAG_M][2]) {
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+}
+
+// Fused epilogue: C = alpha*acc + beta*C on the lanes' own entries, straight from registers.
+// beta == 0 never reads C (BLAS convention; NaN/Inf in C are overwritten).  Rows >= M / cols >= N are
+// predicated off, so padding rows M..ldc-1 are never touched.
+__device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_M][2], const Params& P, int m0, int n0,
+                                               int warp_m, int warp_n, int lane) {
+  const int r = lane >> 2, q = lane & 3;
+  const int mq = map_m(2 * q);  // 0, 8, 2, 10
+  const double alpha = P.alpha, beta = P.beta;
+  const bool use_c = beta != 0.0;
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++) {
+    const int n = n0 + warp_n * WN + i * 8 + perm_n(r);
+    if (n >= P.N) continue;
+    double* col = P.C + (long long)n * P.ldc;
+    const int mbase = m0 + warp_m * WM + mq;
+    double c0[FRAG_M], c1[FRAG_M];
+    if (use_c) {
+#pragma unroll
+      for (int j = 0; j < FRAG_M; j++) {
+        const int m = mbase + (j >> 1) * 16 + (j & 1) * 4;
+        c0[j] = c1[j] = 0.0;
+        if (P.c_vec2 && m + 1 < P.M) {
+          double2 v = *reinterpret_cast<const double2*>(col + m);
+          c0[j] = v.x; c1[j] = v.y;
+        } else {
+          if (m < P.M) c0[j] = col[m];
+          if (m + 1 < P.M) c1[j] = col[m + 1];
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++) {
+      const int m = mbase + (j >> 1) * 16 + (j & 1) * 4;
+      double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
+      if (use_c) { v0 = fma(beta, c0[j], v0); v1 = fma(beta, c1[j], v1); }
+      if (P.c_vec2 && m + 1 < P.M) {
+        *reinterpret_cast<double2*>(col + m) = make_double2(v0, v1);
+      } else {
+        if (m < P.M) col[m] = v0;
+        if (m + 1 < P.M) col[m + 1] = v1;
+      }
+    }
+  }
+}
+
+// split-K: dump / reload raw accumulators in [reg][thread] order (fully coalesced 16-byte accesses)
+__device__ __forceinline__ void store_partial(const double (&acc)[FRAG_N][FRAG_M][2], double* ws, int tid) {
+  double2* p = reinterpret_cast<double2*>(ws) + tid;
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++) p[(i * FRAG_M + j) * CONSUMER_THREADS] = make_double2(acc[i][j][0], acc[i][j][1]);
+}
+__device__ __forceinline__ void add_partial(double (&acc)[FRAG_N][FRAG_M][2], const double* ws, int tid) {
+  const double2* p = reinterpret_cast<const double2*>(ws) + tid;
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++) {
+      double2 v = p[(i * FRAG_M + j) * CONSUMER_THREADS];
+      acc[i][j][0] += v.x; acc[i][j][1] += v.y;
+    }
+}
+
+// work unit -> (tile_m, tile_n, split).  Units are ordered tile-major inside rasterisation bands of group_m
+// tile-rows so that the CTAs resident at any moment share A row-panels and B column-panels in L2.
+struct Unit { int tm, tn, split, k_begin, k_end; };
+__device__ __forceinline__ Unit decode_unit(const Params& P, int u) {
+  Unit w;
+  const int tile = u / P.splits;
+  w.split = u - tile * P.splits;
+  const int band_tiles = P.group_m * P.tiles_n;
+  const int band = tile / band_tiles;
+  const int in_band = tile - band * band_tiles;
+  const int gh = min(P.group_m, P.tiles_m - band * P.group_m);
+  w.tn = in_band / gh;
+  w.tm = band * P.group_m + (in_band - w.tn * gh);
+  w.k_begin = w.split * P.k_tiles_per_split;
+  w.k_end = min(P.k_tiles, w.k_begin + P.k_tiles_per_split);
+  return w;
+}
+
+}  // namespace dg

@@ -1,0 +1,24 @@
+// dgemm_host.h — internal interface between the kernel launchers (dgemm_kernels.cu) and the C-ABI (dgemm_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace dg {
+
+struct Params;
+
+enum Variant {
+  VARIANT_AUTO = 0,       // TMA when the operands allow a tensor map, else cp.async 8-byte
+  VARIANT_TMA = 1,        // dgemm_tma_ws_kernel (needs 16-byte aligned A, B and even lda, ldb)
+  VARIANT_CPASYNC8 = 2,   // dgemm_cpasync_kernel<1>: any alignment, any leading dimension
+  VARIANT_CPASYNC16 = 3,  // dgemm_cpasync_kernel<2>: same eligibility as TMA
+};
+
+bool tma_eligible(const Params& P);
+cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
+cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
+cudaError_t launch_fill_signed(double* X, int rows, int cols, long long ld, unsigned long long seed,
+                               unsigned long long row0, unsigned long long col0, int num_sms, cudaStream_t stream);
+int launch_count();
+void reset_launch_count();
+
+}  // namespace dg

@@ -1,0 +1,325 @@
+// dgemm_kernels.cu — the sm_100a kernels of the DGEMM hot path and their launchers.
+//
+//   dgemm_tma_ws_kernel     persistent, warp-specialised: 1 TMA producer warp + 8 DMMA consumer warps, N-stage
+//                           mbarrier ring (full/empty), fused alpha/beta epilogue.  The performance path.
+//                           Plays the role of mydgemm_cpu_v18's N->K->M blocking loops + packing + macro kernel
+//                           (include/kernel18.h:629-671) and of kernel19's thread-band driver (kernel19.h:678-755).
+//   dgemm_cpasync_kernel    same tile math, operands staged by cp.async (8- or 16-byte, zero-filled at the
+//                           edges).  Needed because TMA requires 16-byte aligned bases and strides: an odd LDA/LDB
+//                           (e.g. the 1000x1003x997 config) or an odd element offset cannot be described by a
+//                           tensor map.  Device-side — there is no CPU fallback.
+//   splitk_reduce_kernel    deterministic ordered sum of split-K partial tiles + the fused epilogue.
+//   scale_c_kernel          C = beta*C for the degenerate alpha == 0 / K == 0 calls (kernel18.h:644-645 order).
+//   fill_signed_kernel      counter-based U(-1,1) generator (same formula as oracle_signed_value) for benches.
+#include "dgemm_device.cuh"
+#include "dgemm_host.h"
+
+#include <cuda.h>
+#include <cstdio>
+
+namespace dg {
+
+// =========================================================================================================
+// TMA + mbarrier, warp-specialised, persistent
+// =========================================================================================================
+// 12 warps: two consumer warpgroups (8 warps) + one producer warpgroup (warp 8 issues TMA, warps 9-11 only
+// donate their registers).  Registers are allocated to a CTA in units of 4 warps, so a 9-warp block costs as
+// much as a 12-warp one; the block is compiled at 65536/384 -> 168 regs/thread and re-balanced with setmaxnreg:
+// producer warpgroup 168 -> 40, consumer warpgroups 168 -> 232 (4*32*40 + 8*32*232 = 64512 <= 65536), which
+// keeps the 128 accumulator registers + double-buffered fragments out of local memory.
+constexpr int TMA_THREADS = CONSUMER_THREADS + 128;
+template <int STAGES>
+__global__ void __launch_bounds__(TMA_THREADS, 1)
+dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params P,
+                    int num_units) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by SWIZZLE_128B; dynamic smem base is only guaranteed 16 B -> round up
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = smem_base + STAGES * STAGE_BYTES;  // full[STAGES] then empty[STAGES], 8 B each
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(bars + 8 * s, 1);                          // full: one arrive (the producer's expect_tx)
+      mbar_init(bars + 8 * (STAGES + s), CONSUMER_WARPS);  // empty: one arrive per consumer warp
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  if (warp >= CONSUMER_WARPS) {
+    // ------------------------------- producer warpgroup: one elected lane issues TMA --------------------------
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (warp == CONSUMER_WARPS && lane == 0) {
+      tma_prefetch_desc(&tmA);
+      tma_prefetch_desc(&tmB);
+      uint32_t it = 0;
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const Unit w = decode_unit(P, u);
+        const int m0 = w.tm * BM, n0 = w.tn * BN;
+        for (int kt = w.k_begin; kt < w.k_end; kt++, it++) {
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+          mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
+          const uint32_t full = bars + 8 * s;
+          const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
+          mbar_arrive_expect_tx(full, STAGE_BYTES);
+          const int k0 = kt * BK;
+#pragma unroll
+          for (int sub = 0; sub < BM / 16; sub++)  // A: 8 boxes of 16(m) x 16(k); OOB rows/cols arrive as zeros
+            tma_load_2d(dstA + sub * 2048, &tmA, full, m0 + sub * 16, k0);
+          tma_load_2d(dstB, &tmB, full, k0, n0);   // B: one box of 16(k) x 128(n)
+        }
+      }
+    }
+  } else {
+    // ------------------------------- consumer warps: DMMA main loop + epilogue -------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    const int warp_m = warp % WARPS_M, warp_n = warp / WARPS_M;
+    const LaneOffsets lo = make_lane_offsets(lane, warp_m, warp_n);
+    double acc[FRAG_N][FRAG_M][2];
+    uint32_t it = 0;
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      const Unit w = decode_unit(P, u);
+      zero_acc(acc);
+      for (int kt = w.k_begin; kt < w.k_end; kt++, it++) {
+        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+        mbar_wait(bars + 8 * s, ph);  // TMA bytes have landed
+        const uint32_t sA = smem_base + s * STAGE_BYTES;
+        mma_stage(acc, sA, sA + A_STAGE_BYTES, lo);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bars + 8 * (STAGES + s));  // release the slot to the producer
+      }
+      if (P.splits == 1)
+        epilogue_store(acc, P, w.tm * BM, w.tn * BN, warp_m, warp_n, lane);
+      else
+        store_partial(acc, P.workspace + (size_t)u * (BM * BN), tid);
+    }
+  }
+}
+
+// =========================================================================================================
+// generic loader: cp.async multistage, one CTA per work unit
+// =========================================================================================================
+template <int VEC>  // doubles per cp.async: 1 (any alignment) or 2 (16-byte aligned operands)
+__device__ __forceinline__ void cpasync_load_stage(const Params& P, uint32_t sA, uint32_t sB, int m0, int n0, int k0,
+                                                   int tid) {
+  constexpr int BYTES = VEC * 8;
+  // A tile: 16 k-columns of 128 consecutive rows (m fastest across threads -> coalesced)
+  constexpr int A_ROW_T = BM / VEC;                   // threads covering one k-column
+  constexpr int A_K_STEP = CONSUMER_THREADS / A_ROW_T;  // k-columns covered per pass
+#pragma unroll
+  for (int e = 0; e < BK / A_K_STEP; e++) {
+    const int ml = (tid % A_ROW_T) * VEC, kl = tid / A_ROW_T + e * A_K_STEP;
+    const int m = m0 + ml, k = k0 + kl;
+    const bool ok = (m + VEC <= P.M) && (k < P.K);  // VEC==2: M is even-reachable only when aligned; tail handled below
+    const double* src = ok ? P.A + (long long)k * P.lda + m : P.A;
+    int bytes = ok ? BYTES : 0;
+    if (VEC == 2 && !ok && m < P.M && k < P.K) { src = P.A + (long long)k * P.lda + m; bytes = 8; }  // odd M tail
+    cp_async_zfill<BYTES>(sA + a_smem_off(ml, kl), src, bytes);
+  }
+  // B tile: 128 n-columns of 16 consecutive k (k fastest across threads)
+  constexpr int B_COL_T = BK / VEC;
+  constexpr int B_N_STEP = CONSUMER_THREADS / B_COL_T;
+#pragma unroll
+  for (int e = 0; e < BN / B_N_STEP; e++) {
+    const int kl = (tid % B_COL_T) * VEC, nl = tid / B_COL_T + e * B_N_STEP;
+    const int k = k0 + kl, n = n0 + nl;
+    const bool ok = (k + VEC <= P.K) && (n < P.N);
+    const double* src = ok ? P.B + (long long)n * P.ldb + k : P.B;
+    int bytes = ok ? BYTES : 0;
+    if (VEC == 2 && !ok && k < P.K && n < P.N) { src = P.B + (long long)n * P.ldb + k; bytes = 8; }  // odd K tail
+    cp_async_zfill<BYTES>(sB + b_smem_off(kl, nl), src, bytes);
+  }
+}
+
+template <int VEC, int STAGES>
+__global__ void __launch_bounds__(CONSUMER_THREADS, 1) dgemm_cpasync_kernel(const Params P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int warp_m = warp % WARPS_M, warp_n = warp / WARPS_M;
+  const LaneOffsets lo = make_lane_offsets(lane, warp_m, warp_n);
+  const Unit w = decode_unit(P, blockIdx.x);
+  const int m0 = w.tm * BM, n0 = w.tn * BN;
+  const int nk = w.k_end - w.k_begin;
+
+  double acc[FRAG_N][FRAG_M][2];
+  zero_acc(acc);
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; s++) {  // prologue: STAGES-1 tiles in flight
+    if (s < nk) {
+      const uint32_t sA = smem_base + s * STAGE_BYTES;
+      cpasync_load_stage<VEC>(P, sA, sA + A_STAGE_BYTES, m0, n0, (w.k_begin + s) * BK, tid);
+    }
+    cp_async_commit();
+  }
+  for (int i = 0; i < nk; i++) {
+    cp_async_wait<STAGES - 2>();  // tile i has landed (for this thread's copies) ...
+    __syncthreads();              // ... and for everyone's; also: everyone finished reading tile i-1's slot
+    const int nxt = i + STAGES - 1;
+    if (nxt < nk) {
+      const uint32_t sA = smem_base + (nxt % STAGES) * STAGE_BYTES;
+      cpasync_load_stage<VEC>(P, sA, sA + A_STAGE_BYTES, m0, n0, (w.k_begin + nxt) * BK, tid);
+    }
+    cp_async_commit();
+    const uint32_t sA = smem_base + (i % STAGES) * STAGE_BYTES;
+    mma_stage(acc, sA, sA + A_STAGE_BYTES, lo);
+  }
+  cp_async_wait<0>();
+  if (P.splits == 1)
+    epilogue_store(acc, P, m0, n0, warp_m, warp_n, lane);
+  else
+    store_partial(acc, P.workspace + (size_t)blockIdx.x * (BM * BN), tid);
+}
+
+// =========================================================================================================
+// split-K fix-up, degenerate scaling, generators
+// =========================================================================================================
+__global__ void __launch_bounds__(CONSUMER_THREADS) splitk_reduce_kernel(const Params P) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int warp_m = warp % WARPS_M, warp_n = warp / WARPS_M;
+  Params Q = P;
+  Q.splits = 1;
+  const Unit w = decode_unit(Q, blockIdx.x);  // blockIdx.x = tile index in rasterised order
+  double acc[FRAG_N][FRAG_M][2];
+  zero_acc(acc);
+  for (int s = 0; s < P.splits; s++)  // fixed ascending order -> run-to-run deterministic
+    add_partial(acc, P.workspace + ((size_t)blockIdx.x * P.splits + s) * (BM * BN), tid);
+  epilogue_store(acc, P, w.tm * BM, w.tn * BN, warp_m, warp_n, lane);
+}
+
+__global__ void scale_c_kernel(double* C, int M, int N, long long ldc, double beta) {
+  const long long total = (long long)M * N;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long j = idx / M, i = idx - j * M;
+    double* p = C + j * ldc + i;
+    *p = (beta == 0.0) ? 0.0 : *p * beta;
+  }
+}
+
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__global__ void fill_signed_kernel(double* X, int rows, int cols, long long ld, unsigned long long seed,
+                                   unsigned long long row0, unsigned long long col0) {
+  const long long total = (long long)rows * cols;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long j = idx / rows, i = idx - j * rows;
+    const unsigned long long h = splitmix64(seed * 0xD1342543DE82EF95ull + ((row0 + i) + ((col0 + j) << 32)));
+    X[j * ld + i] = (double)(long long)(h >> 11) * (1.0 / 4503599627370496.0) - 1.0;
+  }
+}
+
+// =========================================================================================================
+// host-side launchers
+// =========================================================================================================
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+// 2-D FP64 tensor map over a column-major matrix: dim0 = rows (contiguous), dim1 = cols, stride = ld*8 bytes.
+static bool make_tmap(CUtensorMap* tm, const double* base, long long rows, long long cols, long long ld, int box_rows,
+                      int box_cols) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)rows, (cuuint64_t)cols};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 8};
+  cuuint32_t box[2] = {(cuuint32_t)box_rows, (cuuint32_t)box_cols};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)base, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+bool tma_eligible(const Params& P) {
+  return ((uintptr_t)P.A % 16 == 0) && ((uintptr_t)P.B % 16 == 0) && (P.lda % 2 == 0) && (P.ldb % 2 == 0) &&
+         P.lda * 8 < (1ll << 40) && P.ldb * 8 < (1ll << 40);
+}
+
+static int g_launches = 0;
+int launch_count() { return g_launches; }
+void reset_launch_count() { g_launches = 0; }
+
+constexpr int TMA_STAGES = 6;
+constexpr int CPA_STAGES = 4;
+
+template <typename Kern>
+static cudaError_t set_smem(Kern k, int bytes) {
+  return cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream) {
+  const int tiles = P.tiles_m * P.tiles_n;
+  const int units = tiles * P.splits;
+  cudaError_t err = cudaSuccess;
+  if (variant == VARIANT_TMA) {
+    CUtensorMap tmA, tmB;
+    if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN))
+      return cudaErrorInvalidValue;
+    const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 1024;
+    static bool attr_done = false;
+    if (!attr_done) {
+      if ((err = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem)) != cudaSuccess) return err;
+      attr_done = true;
+    }
+    const int grid = units < num_sms ? units : num_sms;
+    dgemm_tma_ws_kernel<TMA_STAGES><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmB, P, units);
+  } else {
+    const int smem = CPA_STAGES * STAGE_BYTES + 1024;
+    static bool attr_done = false;
+    if (!attr_done) {
+      if ((err = set_smem(dgemm_cpasync_kernel<1, CPA_STAGES>, smem)) != cudaSuccess) return err;
+      if ((err = set_smem(dgemm_cpasync_kernel<2, CPA_STAGES>, smem)) != cudaSuccess) return err;
+      attr_done = true;
+    }
+    if (variant == VARIANT_CPASYNC16)
+      dgemm_cpasync_kernel<2, CPA_STAGES><<<units, CONSUMER_THREADS, smem, stream>>>(P);
+    else
+      dgemm_cpasync_kernel<1, CPA_STAGES><<<units, CONSUMER_THREADS, smem, stream>>>(P);
+  }
+  g_launches++;
+  if ((err = cudaGetLastError()) != cudaSuccess) return err;
+  if (P.splits > 1) {
+    splitk_reduce_kernel<<<tiles, CONSUMER_THREADS, 0, stream>>>(P);
+    g_launches++;
+    err = cudaGetLastError();
+  }
+  return err;
+}
+
+cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || beta == 1.0) return cudaSuccess;
+  scale_c_kernel<<<num_sms * 4, 256, 0, stream>>>(C, M, N, ldc, beta);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_fill_signed(double* X, int rows, int cols, long long ld, unsigned long long seed,
+                               unsigned long long row0, unsigned long long col0, int num_sms, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return cudaSuccess;
+  fill_signed_kernel<<<num_sms * 8, 256, 0, stream>>>(X, rows, cols, ld, seed, row0, col0);
+  return cudaGetLastError();
+}
+
+}  // namespace dg

@@ -1,0 +1,304 @@
+// dgemm_multi.cu — single-process multi-GPU layer behind mydgemm_gpu_v21 (the reference signature,
+// include/kernel19.h:678-689; kernel19 shards ROW bands over OpenMP threads with B shared, kernel19.h:700 —
+// here COLUMN panels of B and C are sharded over GPUs with A shared, because column panels of column-major
+// matrices are contiguous).
+//
+//   GPU g owns columns [n_g, n_g+1) of B and C (multiples of the 128-wide CTA tile).
+//   A (M x K) is cut into G K-slabs (contiguous column ranges).  GPU g copies slab g from the host over its OWN
+//   PCIe link, then the slabs are exchanged GPU<->GPU over NVLink with one ncclBroadcast per slab (an
+//   all-gather with uneven counts).  Each GPU starts computing on its own slab at once and consumes the other
+//   slabs as their broadcasts complete:  C_g = beta*C_g + alpha*A[:,slab]*B_g[slab,:]  for the first slab,
+//   C_g += alpha*A[:,slab]*B_g[slab,:] for the rest.  No reduction: column panels are independent.
+//
+// NCCL is resolved with dlopen at first use so the library loads on boxes without NCCL (v21 then fails with
+// DGEMM_B200_ERR_NCCL; v20 is unaffected).
+#include "../../include/dgemm_b200.h"
+#include "dgemm_device.cuh"
+#include "dgemm_host.h"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <future>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+int dgemm_b200_internal_fail(int status, const char* msg);
+int dgemm_b200_internal_ok();
+int dgemm_b200_internal_run_on(int dev, int M, int N, int K, double alpha, const double* dA, long long lda,
+                               const double* dB, long long ldb, double beta, double* dC, long long ldc,
+                               cudaStream_t stream);
+
+void dgemm_b200_multi_shutdown();
+
+namespace {
+
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  bool load() {
+    if (handle) return true;
+    handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!handle) handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!handle) return false;
+#define SYM(field, name) field = (decltype(field))dlsym(handle, name)
+    SYM(CommInitAll, "ncclCommInitAll");
+    SYM(CommDestroy, "ncclCommDestroy");
+    SYM(GroupStart, "ncclGroupStart");
+    SYM(GroupEnd, "ncclGroupEnd");
+    SYM(Broadcast, "ncclBroadcast");
+    SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+    return CommInitAll && CommDestroy && GroupStart && GroupEnd && Broadcast && GetErrorString;
+  }
+};
+
+struct DevState {
+  cudaStream_t s_h2d = nullptr, s_comm = nullptr, s_compute = nullptr, s_d2h = nullptr;
+  double *a = nullptr, *b = nullptr, *c = nullptr;
+  size_t a_cap = 0, b_cap = 0, c_cap = 0;
+  cudaEvent_t ev_slab = nullptr, ev_bc = nullptr, ev_done = nullptr;
+  std::vector<cudaEvent_t> ev_bcast;  // per slab
+};
+
+struct MultiCtx {
+  int g = 0;
+  NcclApi nccl;
+  std::vector<ncclComm_t> comms;
+  std::vector<DevState> dev;
+} g_multi;
+
+#define MCU(expr)                                                                                       \
+  do {                                                                                                  \
+    cudaError_t e_ = (expr);                                                                            \
+    if (e_ != cudaSuccess) {                                                                            \
+      char buf[384];                                                                                    \
+      snprintf(buf, sizeof(buf), "%s: %s", #expr, cudaGetErrorString(e_));                              \
+      return dgemm_b200_internal_fail(e_ == cudaErrorMemoryAllocation ? DGEMM_B200_ERR_OOM : DGEMM_B200_ERR_CUDA, buf); \
+    }                                                                                                   \
+  } while (0)
+#define MNCCL(expr)                                                                \
+  do {                                                                             \
+    ncclResult_t r_ = (expr);                                                      \
+    if (r_ != ncclSuccess) {                                                       \
+      char buf[384];                                                               \
+      snprintf(buf, sizeof(buf), "%s: %s", #expr, g_multi.nccl.GetErrorString(r_)); \
+      return dgemm_b200_internal_fail(DGEMM_B200_ERR_NCCL, buf);                   \
+    }                                                                              \
+  } while (0)
+
+int ensure_multi(int g) {
+  MultiCtx& m = g_multi;
+  if (m.g == g) return DGEMM_B200_OK;
+  if (m.g != 0) {
+    dgemm_b200_multi_shutdown();
+  }
+  if (!m.nccl.load()) return dgemm_b200_internal_fail(DGEMM_B200_ERR_NCCL, "libnccl.so.2 not found (dlopen)");
+  m.comms.assign(g, nullptr);
+  std::vector<int> devs(g);
+  for (int i = 0; i < g; i++) devs[i] = i;
+  MNCCL(m.nccl.CommInitAll(m.comms.data(), g, devs.data()));
+  m.dev.assign(g, DevState());
+  for (int d = 0; d < g; d++) {
+    MCU(cudaSetDevice(d));
+    DevState& s = m.dev[d];
+    MCU(cudaStreamCreateWithFlags(&s.s_h2d, cudaStreamNonBlocking));
+    MCU(cudaStreamCreateWithFlags(&s.s_comm, cudaStreamNonBlocking));
+    MCU(cudaStreamCreateWithFlags(&s.s_compute, cudaStreamNonBlocking));
+    MCU(cudaStreamCreateWithFlags(&s.s_d2h, cudaStreamNonBlocking));
+    MCU(cudaEventCreateWithFlags(&s.ev_slab, cudaEventDisableTiming));
+    MCU(cudaEventCreateWithFlags(&s.ev_bc, cudaEventDisableTiming));
+    MCU(cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
+    s.ev_bcast.resize(g);
+    for (int k = 0; k < g; k++) MCU(cudaEventCreateWithFlags(&s.ev_bcast[k], cudaEventDisableTiming));
+  }
+  m.g = g;
+  return DGEMM_B200_OK;
+}
+
+int grow_dev(double** p, size_t* cap, size_t bytes) {
+  if (*cap >= bytes) return DGEMM_B200_OK;
+  if (*p) {
+    MCU(cudaDeviceSynchronize());
+    cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+  }
+  MCU(cudaMalloc(p, bytes));
+  *cap = bytes;
+  return DGEMM_B200_OK;
+}
+
+}  // namespace
+
+void dgemm_b200_multi_shutdown() {
+  MultiCtx& m = g_multi;
+  if (m.g == 0) return;
+  for (int d = 0; d < m.g; d++) {
+    cudaSetDevice(d);
+    cudaDeviceSynchronize();
+    DevState& s = m.dev[d];
+    if (s.a) cudaFree(s.a);
+    if (s.b) cudaFree(s.b);
+    if (s.c) cudaFree(s.c);
+    cudaStreamDestroy(s.s_h2d); cudaStreamDestroy(s.s_comm); cudaStreamDestroy(s.s_compute); cudaStreamDestroy(s.s_d2h);
+    cudaEventDestroy(s.ev_slab); cudaEventDestroy(s.ev_bc); cudaEventDestroy(s.ev_done);
+    for (auto e : s.ev_bcast) cudaEventDestroy(e);
+    if (m.comms[d]) m.nccl.CommDestroy(m.comms[d]);
+  }
+  m.dev.clear();
+  m.comms.clear();
+  m.g = 0;
+  cudaSetDevice(0);
+}
+
+// column / K partition shared by every rank: boundaries are multiples of `align` except the last
+static void partition(int total, int parts, int align, std::vector<int>& begin) {
+  begin.assign(parts + 1, total);
+  int per = ((total + parts - 1) / parts + align - 1) / align * align;
+  for (int i = 0; i <= parts; i++) begin[i] = std::min(total, i * per);
+}
+
+int dgemm_b200_run_host_multi(int M, int N, int K, double alpha, const double* A, int LDA, const double* B, int LDB,
+                              double beta, double* C, int LDC, int G) {
+  if (M == 0 || N == 0) return dgemm_b200_internal_ok();
+  int st = ensure_multi(G);
+  if (st) return st;
+  MultiCtx& m = g_multi;
+  const bool need_ab = !(alpha == 0.0 || K == 0);
+  const bool need_c_in = beta != 0.0;
+  const long long ldaD = (M + 1) & ~1ll, ldbD = (K + 1) & ~1ll, ldcD = (M + 1) & ~1ll;
+  std::vector<int> nb, kb;
+  partition(N, G, dg::BN, nb);
+  partition(K, G, dg::BK, kb);
+
+  for (int d = 0; d < G; d++) {
+    MCU(cudaSetDevice(d));
+    DevState& s = m.dev[d];
+    const int ncols = nb[d + 1] - nb[d];
+    if (need_ab) {
+      if ((st = grow_dev(&s.a, &s.a_cap, (size_t)ldaD * K * 8))) return st;
+      if ((st = grow_dev(&s.b, &s.b_cap, (size_t)ldbD * std::max(ncols, 1) * 8))) return st;
+    }
+    if ((st = grow_dev(&s.c, &s.c_cap, (size_t)ldcD * std::max(ncols, 1) * 8))) return st;
+  }
+
+  // phase 1: every GPU pulls its A slab, B panel and C panel over its own PCIe link (one host thread per GPU,
+  // so pageable sources do not serialise the devices); slab-ready events feed the NVLink exchange
+  std::vector<std::promise<int>> slab_recorded(G);
+  std::vector<std::future<int>> slab_fut;
+  for (auto& p : slab_recorded) slab_fut.push_back(p.get_future());
+  std::vector<int> thread_status(G, 0);
+  std::vector<std::thread> threads;
+  for (int d = 0; d < G; d++) {
+    threads.emplace_back([&, d]() {
+      DevState& s = m.dev[d];
+      cudaError_t e = cudaSetDevice(d);
+      const int k0 = kb[d], kc = kb[d + 1] - kb[d];
+      if (e == cudaSuccess && need_ab && kc > 0)
+        e = cudaMemcpy2DAsync(s.a + (size_t)k0 * ldaD, ldaD * 8, A + (size_t)k0 * LDA, (size_t)LDA * 8, (size_t)M * 8, kc,
+                              cudaMemcpyHostToDevice, s.s_h2d);
+      if (e == cudaSuccess) e = cudaEventRecord(s.ev_slab, s.s_h2d);
+      slab_recorded[d].set_value(e == cudaSuccess ? 0 : 1);
+      const int n0 = nb[d], nc = nb[d + 1] - nb[d];
+      if (e == cudaSuccess && need_ab && nc > 0)
+        e = cudaMemcpy2DAsync(s.b, ldbD * 8, B + (size_t)n0 * LDB, (size_t)LDB * 8, (size_t)K * 8, nc,
+                              cudaMemcpyHostToDevice, s.s_h2d);
+      if (e == cudaSuccess && need_c_in && nc > 0)
+        e = cudaMemcpy2DAsync(s.c, ldcD * 8, C + (size_t)n0 * LDC, (size_t)LDC * 8, (size_t)M * 8, nc,
+                              cudaMemcpyHostToDevice, s.s_h2d);
+      if (e == cudaSuccess) e = cudaEventRecord(s.ev_bc, s.s_h2d);
+      thread_status[d] = (e == cudaSuccess) ? 0 : (int)e;
+    });
+  }
+  // NVLink exchange: slab g is broadcast from GPU g to everyone (grouped -> one collective per slab)
+  int nccl_rc = 0;
+  if (need_ab) {
+    for (int g = 0; g < G && !nccl_rc; g++) {
+      if (slab_fut[g].get() != 0) { nccl_rc = -1; break; }
+      const size_t count = (size_t)(kb[g + 1] - kb[g]) * ldaD;
+      cudaSetDevice(g);
+      cudaStreamWaitEvent(m.dev[g].s_comm, m.dev[g].ev_slab, 0);  // root's slab must have landed
+      if (count > 0) {
+        ncclResult_t r = m.nccl.GroupStart();
+        for (int d = 0; d < G && r == ncclSuccess; d++) {
+          double* p = m.dev[d].a + (size_t)kb[g] * ldaD;
+          r = m.nccl.Broadcast(p, p, count, ncclDouble, g, m.comms[d], m.dev[d].s_comm);
+        }
+        ncclResult_t r2 = m.nccl.GroupEnd();
+        if (r != ncclSuccess || r2 != ncclSuccess) nccl_rc = (int)(r != ncclSuccess ? r : r2);
+      }
+      for (int d = 0; d < G; d++) {
+        cudaSetDevice(d);
+        cudaEventRecord(m.dev[d].ev_bcast[g], m.dev[d].s_comm);
+      }
+    }
+  } else {
+    for (int g = 0; g < G; g++) slab_fut[g].get();
+  }
+  for (auto& t : threads) t.join();
+  for (int d = 0; d < G; d++)
+    if (thread_status[d])
+      return dgemm_b200_internal_fail(DGEMM_B200_ERR_CUDA, cudaGetErrorString((cudaError_t)thread_status[d]));
+  if (nccl_rc)
+    return dgemm_b200_internal_fail(DGEMM_B200_ERR_NCCL,
+                                    nccl_rc > 0 ? m.nccl.GetErrorString((ncclResult_t)nccl_rc) : "slab copy failed");
+
+  // phase 2: per GPU, own slab first, then the others in ring order as their broadcasts complete
+  for (int d = 0; d < G; d++) {
+    MCU(cudaSetDevice(d));
+    DevState& s = m.dev[d];
+    const int nc = nb[d + 1] - nb[d];
+    if (nc <= 0) continue;
+    MCU(cudaStreamWaitEvent(s.s_compute, s.ev_bc, 0));
+    if (!need_ab) {
+      if ((st = dgemm_b200_internal_run_on(d, M, nc, K, alpha, s.a, ldaD, s.b, ldbD, beta, s.c, ldcD, s.s_compute)))
+        return st;
+    } else {
+      bool first = true;
+      for (int i = 0; i < G; i++) {
+        const int g = (d + i) % G;
+        const int kc = kb[g + 1] - kb[g];
+        if (kc <= 0) continue;
+        if (g != d) MCU(cudaStreamWaitEvent(s.s_compute, s.ev_bcast[g], 0));
+        if ((st = dgemm_b200_internal_run_on(d, M, nc, kc, alpha, s.a + (size_t)kb[g] * ldaD, ldaD, s.b + kb[g], ldbD,
+                                             first ? beta : 1.0, s.c, ldcD, s.s_compute)))
+          return st;
+        first = false;
+      }
+    }
+    MCU(cudaEventRecord(s.ev_done, s.s_compute));
+  }
+  // phase 3: D2H of every C panel, again one host thread per GPU (a pageable destination blocks its caller)
+  threads.clear();
+  for (int d = 0; d < G; d++) {
+    threads.emplace_back([&, d]() {
+      DevState& s = m.dev[d];
+      const int nc = nb[d + 1] - nb[d];
+      cudaError_t e = cudaSetDevice(d);
+      if (e == cudaSuccess && nc > 0) {
+        e = cudaStreamWaitEvent(s.s_d2h, s.ev_done, 0);
+        if (e == cudaSuccess)
+          e = cudaMemcpy2DAsync(C + (size_t)nb[d] * LDC, (size_t)LDC * 8, s.c, ldcD * 8, (size_t)M * 8, nc,
+                                cudaMemcpyDeviceToHost, s.s_d2h);
+      }
+      for (cudaStream_t q : {s.s_d2h, s.s_compute, s.s_comm, s.s_h2d})
+        if (e == cudaSuccess) e = cudaStreamSynchronize(q);
+      thread_status[d] = (e == cudaSuccess) ? 0 : (int)e;
+    });
+  }
+  for (auto& t : threads) t.join();
+  for (int d = 0; d < G; d++)
+    if (thread_status[d])
+      return dgemm_b200_internal_fail(DGEMM_B200_ERR_CUDA, cudaGetErrorString((cudaError_t)thread_status[d]));
+  cudaSetDevice(0);
+  return dgemm_b200_internal_ok();
+}

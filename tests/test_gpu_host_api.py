@@ -1,0 +1,66 @@
+"""-m gpu: the 11-argument reference signature (host pointers) and the Python mirror of test_kernel."""
+import numpy as np
+import pytest
+
+import gpu_util as gu
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("shape,pad,alpha,beta", [
+    ((512, 512, 512), (0, 0, 0), 1.0, 1.0),
+    ((2048, 2048, 2048), (0, 0, 0), 1.0, 1.0),       # BASELINE config 1
+    ((2048, 2048, 2048), (0, 0, 0), 2.0, 0.0),       # the harness' own pair (test.c:25)
+    ((1000, 1003, 997), (0, 0, 0), 2.5, 0.5),        # LDB = 997 odd on the host; staged compactly on the device
+    ((1000, 1003, 997), (7, 7, 7), 2.5, 0.5),
+    ((1001, 1003, 997), (1, 2, 3), -1.0, 1.0),
+    ((300, 5000, 64), (0, 0, 0), 1.0, 0.5),          # many column panels
+    ((64, 64, 0), (0, 0, 0), 1.0, 0.5),              # K == 0 -> C = beta*C
+    ((64, 64, 64), (0, 0, 0), 0.0, 0.5),             # alpha == 0 -> C = beta*C (kernel18 order, not kernel19's)
+])
+def test_v20_host_pointers(dg, shape, pad, alpha, beta):
+    M, N, K = shape
+    A, B, C0 = gu.make_inputs(M, N, K, pad)
+    A_before, B_before = A.copy(order="F"), B.copy(order="F")
+    Cg = C0.copy(order="F")
+    dg.mydgemm_gpu_v20(M, N, K, alpha, A, A.shape[0], B, B.shape[0], beta, Cg, Cg.shape[0])
+    gu.check(M, N, K, alpha, A, B, beta, C0, Cg)
+    assert np.array_equal(A, A_before) and np.array_equal(B, B_before)  # A and B are read-only
+
+
+def test_test_kernel_dispatch(dg):
+    m = n = k = 400
+    A, B, C0 = gu.make_inputs(m, n, k, dist="reference")
+    Cg = C0.copy(order="F")
+    dg.test_kernel(20, m, n, k, 2.0, A, B, 0.0, Cg)   # utils.c:159-165 fixes LDA=m, LDB=k, LDC=m
+    gu.check(m, n, k, 2.0, A, B, 0.0, C0, Cg)
+    with pytest.raises(ValueError):
+        dg.test_kernel(18, m, n, k, 2.0, A, B, 0.0, Cg)
+
+
+def test_bad_arguments_set_status(dg):
+    A, B, C0 = gu.make_inputs(64, 64, 64)
+    with pytest.raises(dg.DgemmError) as e:
+        dg.mydgemm_gpu_v20(64, 64, 64, 1.0, A, 32, B, 64, 0.0, C0, 64)   # LDA < M
+    assert e.value.status == dg.ERR_BAD_ARG
+    with pytest.raises(dg.DgemmError):
+        dg.mydgemm_gpu_v20(-1, 64, 64, 1.0, A, 64, B, 64, 0.0, C0, 64)
+    # and the next good call clears it
+    Cg = C0.copy(order="F")
+    dg.mydgemm_gpu_v20(64, 64, 64, 1.0, A, 64, B, 64, 1.0, Cg, 64)
+    assert dg.last_status() == dg.OK
+
+
+@pytest.mark.skipif(not ol.have_ref(), reason="oracle/_ref/libref.so (the compiled reference) not present")
+def test_against_the_reference_itself(dg):
+    """GPU vs the UNMODIFIED reference kernel18 and kernel19 (oracle/_ref) on identical inputs."""
+    M = N = K = 1024
+    A, B, C0 = gu.make_inputs(M, N, K)
+    Cg = C0.copy(order="F")
+    dg.mydgemm_gpu_v20(M, N, K, 1.0, A, M, B, K, 1.0, Cg, M)
+    for name, nthr in (("mydgemm_cpu_v18", 1), ("mydgemm_cpu_v19", 4)):
+        Cr = C0.copy(order="F")
+        ol.ref().ref_set_num_threads(nthr)
+        ol.call_gemm(getattr(ol.ref(), name), M, N, K, 1.0, A, B, 1.0, Cr)
+        gu.check(M, N, K, 1.0, A, B, 1.0, C0, Cg, Cref=Cr)

@@ -1,0 +1,115 @@
+"""-m gpu: the CUDA path (through the C ABI) against the oracle on identical seeded inputs.
+
+Tolerance (BASELINE.json north_star): |C - C_ref| <= c*K*eps*(|alpha||A||B| + |beta*C0|) elementwise with
+c = 2, eps = 2^-52.  Shapes follow BASELINE.json configs 1-3 / SURVEY.md 8(d): squares, the 1000x1003x997
+edge shape with dense / padded / rounded leading dimensions, odd M and N (which the reference itself drops,
+SURVEY.md F1), alpha in {0, 2.5, -1}, beta in {0, 0.5, 1}, K = 0, tiny M / N, tall-skinny split-K.
+"""
+import numpy as np
+import pytest
+
+import gpu_util as gu
+
+pytestmark = pytest.mark.gpu
+
+TMA, CPA8, CPA16 = 1, 2, 3
+
+
+@pytest.mark.parametrize("variant", [TMA, CPA8, CPA16])
+@pytest.mark.parametrize("size", [128, 256, 384, 512, 1024])
+def test_square_all_variants(dg, variant, size):
+    gu.run_device(dg, size, size, size, 1.0, 1.0, variant=variant)
+
+
+@pytest.mark.parametrize("size", [100, 200, 300, 700, 1000, 1500, 2048])
+def test_square_reference_harness_sizes(dg, size):
+    """test.c:12-14 style sizes with the harness' own (alpha, beta) = (2, 0) and its value distribution."""
+    gu.run_device(dg, size, size, size, 2.0, 0.0, dist="reference")
+    gu.run_device(dg, size, size, size, 1.0, 1.0, dist="reference")
+
+
+@pytest.mark.parametrize("pad", [(0, 0, 0), (7, 7, 7), (24, 27, 24), (1, 0, 3)])
+@pytest.mark.parametrize("shape", [(1000, 1003, 997), (1001, 1003, 997), (1000, 1002, 997)])
+def test_edge_shapes_and_leading_dims(dg, shape, pad):
+    M, N, K = shape
+    gu.run_device(dg, M, N, K, 2.5, 0.5, pad=pad)
+
+
+@pytest.mark.parametrize("variant", [TMA, CPA16])
+def test_edge_shape_aligned_variants(dg, variant):
+    # LD rounded to 1024: TMA-eligible although M, N, K are not tile multiples (TMA zero-fills the edges)
+    gu.run_device(dg, 1000, 1003, 997, 2.5, 0.5, pad=(24, 27, 24), variant=variant)
+    gu.run_device(dg, 1001, 1003, 999, -1.0, 1.0, pad=(23, 25, 23), variant=variant)
+
+
+@pytest.mark.parametrize("alpha", [0.0, 2.5, -1.0, 1.0])
+@pytest.mark.parametrize("beta", [0.0, 0.5, 1.0])
+def test_alpha_beta_grid(dg, alpha, beta):
+    gu.run_device(dg, 260, 250, 300, alpha, beta, pad=(4, 2, 6))
+
+
+def test_beta_zero_ignores_nan_in_c(dg):
+    for variant in (TMA, CPA8):
+        gu.run_device(dg, 256, 192, 128, 1.5, 0.0, variant=variant, c_fill=np.nan)
+    gu.run_device(dg, 256, 192, 0, 1.5, 0.0, c_fill=np.nan)    # K == 0 -> C = 0
+    gu.run_device(dg, 256, 192, 64, 0.0, 0.0, c_fill=np.inf)   # alpha == 0 -> C = 0
+
+
+@pytest.mark.parametrize("K", [0, 1, 3, 15, 16, 17, 383, 385])
+def test_k_edges(dg, K):
+    gu.run_device(dg, 130, 70, K, 1.25, 0.75)
+
+
+@pytest.mark.parametrize("mn", [(1, 1), (1, 300), (300, 1), (7, 9), (8, 8), (9, 7), (127, 129), (129, 127)])
+def test_tiny_m_n(dg, mn):
+    M, N = mn
+    gu.run_device(dg, M, N, 200, -0.5, 2.0, pad=(3, 1, 5))
+
+
+def test_empty_is_noop(dg):
+    gu.run_device(dg, 0, 5, 5, 1.0, 0.0)
+    gu.run_device(dg, 5, 0, 5, 1.0, 0.0)
+
+
+@pytest.mark.parametrize("offset", [(1, 0, 0), (0, 1, 0), (0, 0, 1), (1, 1, 1)])
+def test_unaligned_base_pointers(dg, offset):
+    """8-byte (not 16-byte) aligned operands: no tensor map possible -> device-side cp.async loader."""
+    gu.run_device(dg, 300, 260, 200, 1.0, 1.0, offset=offset)
+
+
+@pytest.mark.parametrize("variant", [TMA, CPA8])
+@pytest.mark.parametrize("splits", [2, 3, 9, 16])
+def test_split_k_forced(dg, variant, splits):
+    gu.run_device(dg, 256, 384, 1000, 2.0, 0.5, variant=variant, splits=splits)
+
+
+def test_tall_skinny_heuristic_uses_split_k(dg):
+    p = dg.plan(512, 512, 16384)
+    assert p["splits"] > 1, p
+    gu.run_device(dg, 512, 512, 16384, 1.0, 1.0)
+
+
+def test_split_k_is_deterministic(dg):
+    A, B, C0 = gu.make_inputs(256, 256, 4096)
+    outs = []
+    for _ in range(3):
+        dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+        dg.dgemm_device(256, 256, 4096, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, 0, 8)
+        dg.lib.dgemm_b200_sync(None)
+        outs.append(dC.to_host())
+        dA.free(); dB.free(); dC.free()
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
+def test_variants_agree_bitwise(dg):
+    """All loaders feed the same DMMA schedule -> identical bits (only the operand staging differs)."""
+    A, B, C0 = gu.make_inputs(520, 390, 777, pad=(0, 1, 0))
+    A2, B2, C2 = gu.make_inputs(520, 390, 777, pad=(0, 1, 0))
+    outs = []
+    for variant in (TMA, CPA8, CPA16):
+        dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+        dg.dgemm_device(520, 390, 777, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, variant, 1)
+        dg.lib.dgemm_b200_sync(None)
+        outs.append(dC.to_host())
+        dA.free(); dB.free(); dC.free()
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
