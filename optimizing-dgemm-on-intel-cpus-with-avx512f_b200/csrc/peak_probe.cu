@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(1024) dmma_kernel(double* out, Stamp* st, int 
   double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
   __syncthreads();
   unsigned long long c0 = clock64(), t0 = gtimer();
+#pragma unroll 1
   for (int it = 0; it < iters; it++) {
 #pragma unroll
     for (int i = 0; i < NACC; i++) dmma884(acc[i][0], acc[i][1], a, b);
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(1024) dfma_kernel(double* out, Stamp* st, int 
   double a = 1.0 + threadIdx.x * 1e-9, b = 1e-9;
   __syncthreads();
   unsigned long long c0 = clock64(), t0 = gtimer();
+#pragma unroll 1
   for (int it = 0; it < iters; it++) {
 #pragma unroll
     for (int i = 0; i < NACC; i++) asm volatile("fma.rn.f64 %0, %1, %0, %2;" : "+d"(acc[i]) : "d"(a), "d"(b));
@@ -121,17 +123,16 @@ int main(int argc, char** argv) {
   CK(cudaMalloc(&d_out, sizeof(double) * nsm * 1024));
   CK(cudaMalloc(&d_st, sizeof(Stamp) * nsm));
   // DMMA m8n8k4: 8*8*4*2 = 512 flop per warp instruction
-  run("dmma_m8n8k4", dmma_kernel<16>, 4, 16, 512.0, iters, nsm, d_out, d_st);
-  run("dmma_m8n8k4", dmma_kernel<16>, 8, 16, 512.0, iters, nsm, d_out, d_st);
-  run("dmma_m8n8k4", dmma_kernel<16>, 16, 16, 512.0, iters, nsm, d_out, d_st);
-  run("dmma_m8n8k4", dmma_kernel<32>, 8, 32, 512.0, iters / 2, nsm, d_out, d_st);
-  run("dmma_m8n8k4", dmma_kernel<4>, 4, 4, 512.0, iters * 2, nsm, d_out, d_st);
   run("dmma_m8n8k4", dmma_kernel<1>, 4, 1, 512.0, iters * 4, nsm, d_out, d_st);   // dependent chain = latency
+  run("dmma_m8n8k4", dmma_kernel<2>, 4, 2, 512.0, iters * 4, nsm, d_out, d_st);
+  run("dmma_m8n8k4", dmma_kernel<4>, 4, 4, 512.0, iters * 2, nsm, d_out, d_st);
+  run("dmma_m8n8k4", dmma_kernel<32>, 4, 32, 512.0, iters / 2, nsm, d_out, d_st);  // a 32-accumulator warp tile, 1 warp/SMSP
+  run("dmma_m8n8k4", dmma_kernel<32>, 8, 32, 512.0, iters / 2, nsm, d_out, d_st);  // ... 2 warps/SMSP (the GEMM's shape)
+  run("dmma_m8n8k4", dmma_kernel<8>, 16, 8, 512.0, iters, nsm, d_out, d_st);
   // DFMA: 32 lanes * 2 flop = 64 flop per warp instruction
+  run("dfma", dfma_kernel<1>, 4, 1, 64.0, iters * 8, nsm, d_out, d_st);            // dependent chain = latency
   run("dfma", dfma_kernel<16>, 4, 16, 64.0, iters * 4, nsm, d_out, d_st);
   run("dfma", dfma_kernel<16>, 8, 16, 64.0, iters * 4, nsm, d_out, d_st);
-  run("dfma", dfma_kernel<16>, 16, 16, 64.0, iters * 2, nsm, d_out, d_st);
   run("dfma", dfma_kernel<16>, 32, 16, 64.0, iters, nsm, d_out, d_st);
-  run("dfma", dfma_kernel<1>, 4, 1, 64.0, iters * 8, nsm, d_out, d_st);           // dependent chain = latency
   return 0;
 }
