@@ -66,13 +66,16 @@ int dgemm_b200_set_max_gpus(int n);       /* cap the GPUs v21 uses (0 = all visi
  * Asynchronous with respect to the host. Returns a status code. */
 int dgemm_b200_device(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
                       long long ldb, double beta, double *dC, long long ldc, void *stream);
-/* same, forcing a kernel variant and a split-K factor (0 = heuristic) */
+/* same, forcing a kernel variant and a K-decomposition: splits = 0 heuristic (TMA kernel: data-parallel waves +
+ * stream-K tail; cp.async kernel: split-K when there are too few tiles), 1 = pure data-parallel, > 1 = split-K
+ * with that many splits and a deterministic reduce pass */
 int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
                          long long ldb, double beta, double *dC, long long ldc, void *stream, int variant,
                          int splits);
-/* plan the heuristic would use: writes variant, split-K factor, CTA count; returns status */
+/* plan the heuristic would use: writes variant, split-K factor, CTA count and the number of output tiles handled
+ * by the stream-K tail (any out pointer may be NULL); returns status */
 int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const double *dB, long long ldb,
-                    int *variant, int *splits, int *ctas);
+                    int *variant, int *splits, int *ctas, int *sk_tiles);
 
 /* ---- helpers so a plain-C harness needs no CUDA headers -------------------------------------------------------- */
 void *dgemm_b200_malloc(size_t bytes);                 /* device memory on the current device (NULL on failure) */

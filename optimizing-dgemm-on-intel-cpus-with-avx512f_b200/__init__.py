@@ -65,7 +65,7 @@ _DEV_ARGS = [C.c_int, C.c_int, C.c_int, C.c_double, _vp, _ll, _vp, _ll, C.c_doub
 lib.dgemm_b200_device.argtypes = _DEV_ARGS + [_vp]
 lib.dgemm_b200_device_ex.argtypes = _DEV_ARGS + [_vp, C.c_int, C.c_int]
 lib.dgemm_b200_plan.argtypes = [C.c_int, C.c_int, C.c_int, _vp, _ll, _vp, _ll, C.POINTER(C.c_int),
-                                C.POINTER(C.c_int), C.POINTER(C.c_int)]
+                                C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
 lib.dgemm_b200_malloc.argtypes = [C.c_size_t]
 lib.dgemm_b200_malloc.restype = _vp
 lib.dgemm_b200_free.argtypes = [_vp]
@@ -153,11 +153,11 @@ def dgemm_device(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0, vari
 
 
 def plan(M, N, K, dA=0, lda=None, dB=0, ldb=None):
-    v, s, c = C.c_int(), C.c_int(), C.c_int()
+    v, s, c, k = C.c_int(), C.c_int(), C.c_int(), C.c_int()
     st = lib.dgemm_b200_plan(M, N, K, int(dA) or None, lda or max(M, 1), int(dB) or None, ldb or max(K, 1),
-                             C.byref(v), C.byref(s), C.byref(c))
+                             C.byref(v), C.byref(s), C.byref(c), C.byref(k))
     _check(st)
-    return {"variant": VARIANT_NAMES[v.value], "splits": s.value, "ctas": c.value}
+    return {"variant": VARIANT_NAMES[v.value], "splits": s.value, "ctas": c.value, "stream_k_tiles": k.value}
 
 
 def time_device(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, variant=VARIANT_AUTO, splits=0, warmup=3, reps=5,

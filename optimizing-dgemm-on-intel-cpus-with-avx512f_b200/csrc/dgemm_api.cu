@@ -53,7 +53,9 @@ struct DeviceCtx {
   int num_sms = 0;
   bool ready = false;
   cudaStream_t s_compute = nullptr, s_h2d = nullptr, s_d2h = nullptr;
-  Buf ws;                     // split-K workspace
+  Buf ws;                     // split-K / stream-K workspace
+  unsigned int* sk_flags = nullptr;  // stream-K: one flag per CTA range, compared against sk_epoch
+  unsigned int sk_epoch = 0;
   cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
   bool ws_used = false;
   Buf a, b, c;                // staging for the host-pointer entries
@@ -97,6 +99,8 @@ int ensure_ctx(int dev, DeviceCtx** out) {
     CU_TRY(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
     CU_TRY(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&c.ws_free, cudaEventDisableTiming));
+    CU_TRY(cudaMalloc(&c.sk_flags, 1024 * sizeof(unsigned int)));
+    CU_TRY(cudaMemset(c.sk_flags, 0, 1024 * sizeof(unsigned int)));
     c.ready = true;
     cudaSetDevice(prev);
   }
@@ -150,8 +154,31 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
   return best_s;
 }
 
+// Stream-K plan for the persistent TMA kernel: whole tiles go data-parallel in full waves; the last partial wave
+// plus one full wave ("two-tile" stream-K) is cut into equal (tile, k-tile) ranges, one per CTA, so every SM gets
+// the same number of k-tiles.  When there are fewer tiles than SMs the whole problem is stream-K (this is what
+// split-K was for: M=N=512, K=16384 has 16 tiles for 148 SMs).
+void plan_stream_k(dg::Params& P, int num_sms) {
+  const int tiles = P.tiles_m * P.tiles_n;
+  P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0;
+  if (P.k_tiles < 8) return;
+  const int full_waves = tiles / num_sms, rem = tiles % num_sms;
+  if (rem == 0) return;
+  if (full_waves >= 1) {
+    P.sk_tiles = rem + num_sms;
+    P.sk_grid = num_sms;
+  } else {
+    const long long iters = (long long)tiles * P.k_tiles;
+    const int g = (int)std::min<long long>(num_sms, iters / 8);  // at least 8 k-tiles (128 k) per CTA
+    if (g <= tiles) return;                                       // nothing to gain: one CTA per tile
+    P.sk_tiles = tiles;
+    P.sk_grid = g;
+  }
+  P.sk_tile0 = tiles - P.sk_tiles;
+}
+
 int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
-                long long ldb, double beta, double* dC, long long ldc, int splits, int num_sms) {
+                long long ldb, double beta, double* dC, long long ldc, int splits, int variant, int num_sms) {
   P.M = M; P.N = N; P.K = K;
   P.alpha = alpha; P.beta = beta;
   P.A = dA; P.lda = lda; P.B = dB; P.ldb = ldb; P.C = dC; P.ldc = ldc;
@@ -159,14 +186,21 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   P.tiles_n = (N + dg::BN - 1) / dg::BN;
   P.k_tiles = (K + dg::BK - 1) / dg::BK;
   const int tiles = P.tiles_m * P.tiles_n;
-  if (splits <= 0) splits = choose_splits(tiles, P.k_tiles, num_sms);
-  splits = std::max(1, std::min(splits, P.k_tiles));
-  P.k_tiles_per_split = (P.k_tiles + splits - 1) / splits;
-  P.splits = (P.k_tiles + P.k_tiles_per_split - 1) / P.k_tiles_per_split;  // no empty splits
+  P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
   // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
   P.group_m = std::min(P.tiles_m, 16);
   P.c_vec2 = ((uintptr_t)dC % 16 == 0) && (ldc % 2 == 0);
   P.workspace = nullptr;
+  if (splits <= 0 && variant == dg::VARIANT_TMA) {  // auto on the persistent kernel: stream-K, never split-K
+    P.splits = 1;
+    P.k_tiles_per_split = P.k_tiles;
+    plan_stream_k(P, num_sms);
+    return DGEMM_B200_OK;
+  }
+  if (splits <= 0) splits = choose_splits(tiles, P.k_tiles, num_sms);
+  splits = std::max(1, std::min(splits, P.k_tiles));
+  P.k_tiles_per_split = (P.k_tiles + splits - 1) / splits;
+  P.splits = (P.k_tiles + P.k_tiles_per_split - 1) / P.k_tiles_per_split;  // no empty splits
   return DGEMM_B200_OK;
 }
 
@@ -190,13 +224,16 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
     return ok();
   }
   dg::Params P;
-  fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, c.num_sms);
+  P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
   const bool tma_ok = dg::tma_eligible(P);
   if (variant == dg::VARIANT_AUTO) variant = tma_ok ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   if ((variant == dg::VARIANT_TMA || variant == dg::VARIANT_CPASYNC16) && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
-  if (P.splits > 1) {
-    const size_t need = (size_t)P.tiles_m * P.tiles_n * P.splits * dg::BM * dg::BN * sizeof(double);
+  fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
+  const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
+  if (uses_ws) {
+    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits : (size_t)P.sk_grid;
+    const size_t need = slots * dg::BM * dg::BN * sizeof(double);
     if (c.ws.cap < need) {
       int st = grow(c.ws, need);
       if (st) return st;
@@ -204,9 +241,13 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
     }
     if (c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream) done
     P.workspace = c.ws.p;
+    if (P.sk_tiles > 0) {
+      P.sk_flags = c.sk_flags;
+      P.sk_epoch = ++c.sk_epoch;
+    }
   }
   CU_TRY(dg::launch_gemm(P, variant, c.num_sms, stream));
-  if (P.splits > 1) {
+  if (uses_ws) {
     CU_TRY(cudaEventRecord(c.ws_free, stream));
     c.ws_used = true;
   }
@@ -390,6 +431,7 @@ int dgemm_b200_shutdown(void) {
     cudaStreamDestroy(c.s_h2d);
     cudaStreamDestroy(c.s_d2h);
     cudaEventDestroy(c.ws_free);
+    cudaFree(c.sk_flags);
     c = DeviceCtx();
   }
   if (g_ndev > 0) cudaSetDevice(prev);
@@ -412,18 +454,20 @@ int dgemm_b200_device(int M, int N, int K, double alpha, const double* dA, long 
 }
 
 int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const double* dB, long long ldb, int* variant,
-                    int* splits, int* ctas) {
+                    int* splits, int* ctas, int* sk_tiles) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);
   DeviceCtx* c;
   int st = current_ctx(&c);
   if (st) return st;
   dg::Params P;
-  fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, c->num_sms);
+  P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
   const int v = dg::tma_eligible(P) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms);
   if (variant) *variant = v;
   if (splits) *splits = P.splits;
+  if (sk_tiles) *sk_tiles = P.sk_tiles;
   const int units = P.tiles_m * P.tiles_n * P.splits;
-  if (ctas) *ctas = v == dg::VARIANT_TMA ? std::min(units, c->num_sms) : units;
+  if (ctas) *ctas = v == dg::VARIANT_TMA ? (P.sk_tiles > 0 ? P.sk_grid : std::min(units, c->num_sms)) : units;
   return ok();
 }
 

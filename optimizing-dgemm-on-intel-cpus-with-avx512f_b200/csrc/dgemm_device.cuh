@@ -50,7 +50,14 @@ struct Params {
   int k_tiles_per_split;  // ceil(k_tiles / splits)
   int group_m;            // rasterisation: tiles are walked in bands of group_m tile-rows
   int c_vec2;             // C base 16-byte aligned and ldc even -> 16-byte epilogue accesses
-  double* workspace;      // splits > 1: [split][tile][ACC_PER_THREAD][CONSUMER_THREADS] partial accumulators
+  double* workspace;      // splits > 1: [unit][ACC_PER_THREAD][CONSUMER_THREADS] partial accumulators;
+                          // stream-K: one such slot per CTA range
+  // ---- stream-K tail (TMA kernel only): tiles [sk_tile0, sk_tile0 + sk_tiles) are cut into gridDim.x equal
+  // ranges of (tile, k-tile) iterations instead of whole tiles
+  int sk_tile0, sk_tiles;
+  int sk_grid;                // CTAs launched when sk_tiles > 0 (every one of them must be co-resident)
+  unsigned int sk_epoch;      // flag value that means "partial of this launch is in the workspace"
+  unsigned int* sk_flags;     // one flag per CTA range
 };
 
 // ---- lane -> matrix index maps (see header comment) -------------------------------------------------------
@@ -62,9 +69,11 @@ __device__ __forceinline__ int map_m(int c) { return (c & 1) | ((c & 2) << 2) | 
 // ---- raw PTX wrappers ----------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// volatile + "memory": the front end must not move a fragment load above the mbarrier wait that guards its stage
+// (ptxas still schedules the resulting LDS freely between the DMMAs; try_wait has acquire semantics for it).
 __device__ __forceinline__ double lds_f64(uint32_t addr) {
   double v;
-  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
   return v;
 }
 
@@ -147,22 +156,37 @@ __device__ __forceinline__ LaneOffsets make_lane_offsets(int lane, int warp_m, i
   return lo;
 }
 
+// Register fragments of one k-step (4 k): 8 column fragments from A, 4 row fragments from B.
+struct Frags {
+  double a[FRAG_M];
+  double b[FRAG_N];
+};
+__device__ __forceinline__ void load_frags(Frags& f, uint32_t sA, uint32_t sB, const LaneOffsets& lo, int kk) {
+#pragma unroll
+  for (int j = 0; j < FRAG_M; j++)  // sub-tile j/2, half f = j&1; rows kk*4.. -> (kk>>1)*1024 + (kk&1)*512
+    f.a[j] = lds_f64(sA + lo.a[kk & 1][j & 1] + (kk >> 1) * 1024 + (j >> 1) * 2048);
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++) f.b[i] = lds_f64(sB + lo.b[kk] + i * 1024);
+}
+__device__ __forceinline__ void mma_frags(double (&acc)[FRAG_N][FRAG_M][2], const Frags& f) {
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++) dmma_8x8x4(acc[i][j][0], acc[i][j][1], f.b[i], f.a[j]);
+}
+
 // One pipeline stage (16 k) of the warp tile: 4 k-steps x (8 + 4 fragment loads, 32 DMMAs).
 __device__ __forceinline__ void mma_stage(double (&acc)[FRAG_N][FRAG_M][2], uint32_t sA, uint32_t sB,
                                           const LaneOffsets& lo) {
-#pragma unroll
-  for (int kk = 0; kk < BK / 4; kk++) {
-    double a[FRAG_M], b[FRAG_N];
-#pragma unroll
-    for (int j = 0; j < FRAG_M; j++)  // sub-tile j/2, half f = j&1; rows kk*4.. -> (kk>>1)*1024 + (kk&1)*512
-      a[j] = lds_f64(sA + lo.a[kk & 1][j & 1] + (kk >> 1) * 1024 + (j >> 1) * 2048);
-#pragma unroll
-    for (int i = 0; i < FRAG_N; i++) b[i] = lds_f64(sB + lo.b[kk] + i * 1024);
-#pragma unroll
-    for (int i = 0; i < FRAG_N; i++)
-#pragma unroll
-      for (int j = 0; j < FRAG_M; j++) dmma_8x8x4(acc[i][j][0], acc[i][j][1], b[i], a[j]);
-  }
+  Frags f0, f1;
+  load_frags(f0, sA, sB, lo, 0);
+  load_frags(f1, sA, sB, lo, 1);
+  mma_frags(acc, f0);
+  load_frags(f0, sA, sB, lo, 2);
+  mma_frags(acc, f1);
+  load_frags(f1, sA, sB, lo, 3);
+  mma_frags(acc, f0);
+  mma_frags(acc, f1);
 }
 
 __device__ __forceinline__ void zero_acc(double (&acc)[FRAG_N][FRAG_M][2]) {
@@ -234,6 +258,39 @@ __device__ __forceinline__ void add_partial(double (&acc)[FRAG_N][FRAG_M][2], co
       double2 v = p[(i * FRAG_M + j) * CONSUMER_THREADS];
       acc[i][j][0] += v.x; acc[i][j][1] += v.y;
     }
+}
+
+__device__ __forceinline__ void st_release_gpu(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// barrier among the 8 consumer warps only (the producer warpgroup never joins): named barrier 1
+__device__ __forceinline__ void consumer_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_THREADS) : "memory"); }
+
+// stream-K partial reload: L2-coherent loads (the slot was written by another SM during this launch)
+__device__ __forceinline__ void add_partial_cg(double (&acc)[FRAG_N][FRAG_M][2], const double* ws, int tid) {
+  const double2* p = reinterpret_cast<const double2*>(ws) + tid;
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+    for (int j = 0; j < FRAG_M; j++) {
+      double2 v = __ldcg(p + (i * FRAG_M + j) * CONSUMER_THREADS);
+      acc[i][j][0] += v.x; acc[i][j][1] += v.y;
+    }
+}
+
+// tile index (rasterised order) -> tile coordinates
+__device__ __forceinline__ void decode_tile(const Params& P, int tile, int& tm, int& tn) {
+  const int band_tiles = P.group_m * P.tiles_n;
+  const int band = tile / band_tiles;
+  const int in_band = tile - band * band_tiles;
+  const int gh = min(P.group_m, P.tiles_m - band * P.group_m);
+  tn = in_band / gh;
+  tm = band * P.group_m + (in_band - tn * gh);
 }
 
 // work unit -> (tile_m, tile_n, split).  Units are ordered tile-major inside rasterisation bands of group_m

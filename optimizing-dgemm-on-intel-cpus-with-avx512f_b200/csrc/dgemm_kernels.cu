@@ -28,6 +28,53 @@ namespace dg {
 // producer warpgroup 168 -> 40, consumer warpgroups 168 -> 232 (4*32*40 + 8*32*232 = 64512 <= 65536), which
 // keeps the 128 accumulator registers + double-buffered fragments out of local memory.
 constexpr int TMA_THREADS = CONSUMER_THREADS + 128;
+// A segment = a contiguous run of k-tiles of one output tile.  Phase 1 (data-parallel): whole tiles (or split-K
+// units) strided over the grid.  Phase 2 (stream-K): the iteration space sk_tiles x k_tiles is cut into gridDim.x
+// equal ranges; range ids run AGAINST blockIdx so that the CTA that finishes a tile (its owner, the range holding
+// k-tile 0) only ever waits for CTAs with a lower blockIdx, which the hardware dispatched earlier.
+struct Segment {
+  int tile, kb, ke;   // rasterised tile index, k-tile range [kb, ke)
+  int kind;           // see below
+  int slot;           // workspace slot (split-K: unit index; stream-K contributor: own range id)
+};
+enum { SEG_DIRECT = 0, SEG_SPLITK = 1, SEG_SK_OWNER = 2, SEG_SK_CONTRIB = 3 };
+
+struct SegmentWalker {
+  int u, num_units, stride;   // phase 1
+  long long it, end;          // phase 2
+  int rid;
+  __device__ SegmentWalker(const Params& P, int num_units_)
+      : u(blockIdx.x), num_units(num_units_), stride(gridDim.x) {
+    rid = gridDim.x - 1 - blockIdx.x;
+    const long long total = (long long)P.sk_tiles * P.k_tiles;
+    it = total * rid / gridDim.x;
+    end = total * (rid + 1) / gridDim.x;
+  }
+  __device__ bool next(const Params& P, Segment& sg) {
+    if (u < num_units) {
+      const int tile = u / P.splits, split = u - tile * P.splits;
+      sg.tile = tile;
+      sg.kb = split * P.k_tiles_per_split;
+      sg.ke = min(P.k_tiles, sg.kb + P.k_tiles_per_split);
+      sg.kind = P.splits == 1 ? SEG_DIRECT : SEG_SPLITK;
+      sg.slot = u;
+      u += stride;
+      return true;
+    }
+    if (it < end) {
+      const int t = (int)(it / P.k_tiles);
+      sg.tile = P.sk_tile0 + t;
+      sg.kb = (int)(it - (long long)t * P.k_tiles);
+      sg.ke = (int)min((long long)P.k_tiles, sg.kb + (end - it));
+      sg.kind = sg.kb > 0 ? SEG_SK_CONTRIB : (sg.ke == P.k_tiles ? SEG_DIRECT : SEG_SK_OWNER);
+      sg.slot = rid;
+      it += sg.ke - sg.kb;
+      return true;
+    }
+    return false;
+  }
+};
+
 template <int STAGES>
 __global__ void __launch_bounds__(TMA_THREADS, 1)
 dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params P,
@@ -55,12 +102,14 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == CONSUMER_WARPS && lane == 0) {
       tma_prefetch_desc(&tmA);
       tma_prefetch_desc(&tmB);
-      uint32_t it = 0;
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-        const Unit w = decode_unit(P, u);
-        const int m0 = w.tm * BM, n0 = w.tn * BN;
-        for (int kt = w.k_begin; kt < w.k_end; kt++, it++) {
-          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+      uint32_t s = 0, ph = 0;
+      SegmentWalker walk(P, num_units);
+      Segment sg;
+      while (walk.next(P, sg)) {
+        int tm, tn;
+        decode_tile(P, sg.tile, tm, tn);
+        const int m0 = tm * BM, n0 = tn * BN;
+        for (int kt = sg.kb; kt < sg.ke; kt++) {
           mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
           const uint32_t full = bars + 8 * s;
           const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
@@ -70,6 +119,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int sub = 0; sub < BM / 16; sub++)  // A: 8 boxes of 16(m) x 16(k); OOB rows/cols arrive as zeros
             tma_load_2d(dstA + sub * 2048, &tmA, full, m0 + sub * 16, k0);
           tma_load_2d(dstB, &tmB, full, k0, n0);   // B: one box of 16(k) x 128(n)
+          if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -79,22 +129,58 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int warp_m = warp % WARPS_M, warp_n = warp / WARPS_M;
     const LaneOffsets lo = make_lane_offsets(lane, warp_m, warp_n);
     double acc[FRAG_N][FRAG_M][2];
-    uint32_t it = 0;
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-      const Unit w = decode_unit(P, u);
+    Frags f0, f1;
+    uint32_t s = 0, ph = 0;
+    SegmentWalker walk(P, num_units);
+    Segment sg;
+    while (walk.next(P, sg)) {
       zero_acc(acc);
-      for (int kt = w.k_begin; kt < w.k_end; kt++, it++) {
-        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-        mbar_wait(bars + 8 * s, ph);  // TMA bytes have landed
-        const uint32_t sA = smem_base + s * STAGE_BYTES;
-        mma_stage(acc, sA, sA + A_STAGE_BYTES, lo);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bars + 8 * (STAGES + s));  // release the slot to the producer
+      if (sg.kb < sg.ke) {
+        // software pipeline over k-steps: the fragments of step i+1 are loaded while the 32 DMMAs of step i issue,
+        // INCLUDING across the stage boundary (wait on the next stage's barrier before the last DMMA group)
+        mbar_wait(bars + 8 * s, ph);
+        load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
+        for (int kt = sg.kb; kt < sg.ke; kt++) {
+          const uint32_t sA = smem_base + s * STAGE_BYTES, sB = sA + A_STAGE_BYTES;
+          const uint32_t cur_empty = bars + 8 * (STAGES + s);
+          load_frags(f1, sA, sB, lo, 1);
+          mma_frags(acc, f0);
+          load_frags(f0, sA, sB, lo, 2);
+          mma_frags(acc, f1);
+          load_frags(f1, sA, sB, lo, 3);
+          mma_frags(acc, f0);
+          if (++s == STAGES) { s = 0; ph ^= 1; }
+          if (kt + 1 < sg.ke) {
+            mbar_wait(bars + 8 * s, ph);  // TMA bytes of the next stage have landed (normally long ago)
+            load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
+          }
+          mma_frags(acc, f1);  // consumes the last fragments read from the current stage ...
+          __syncwarp();
+          if (lane == 0) mbar_arrive(cur_empty);  // ... so the slot can go back to the producer
+        }
       }
-      if (P.splits == 1)
-        epilogue_store(acc, P, w.tm * BM, w.tn * BN, warp_m, warp_n, lane);
-      else
-        store_partial(acc, P.workspace + (size_t)u * (BM * BN), tid);
+      int tm, tn;
+      decode_tile(P, sg.tile, tm, tn);
+      if (sg.kind == SEG_DIRECT) {
+        epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
+      } else if (sg.kind == SEG_SPLITK) {
+        store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
+      } else if (sg.kind == SEG_SK_CONTRIB) {
+        store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
+        __threadfence();
+        consumer_bar_sync();
+        if (tid == 0) st_release_gpu(P.sk_flags + sg.slot, P.sk_epoch);
+      } else {  // SEG_SK_OWNER: add the partials of the ranges that hold the rest of this tile, in range order
+        const long long total = (long long)P.sk_tiles * P.k_tiles;
+        const long long tile_end = (long long)(sg.tile - P.sk_tile0 + 1) * P.k_tiles;
+        for (int r = sg.slot + 1; r < (int)gridDim.x && total * r / gridDim.x < tile_end; r++) {
+          if (tid == 0)
+            while (ld_acquire_gpu(P.sk_flags + r) != P.sk_epoch) __nanosleep(64);
+          consumer_bar_sync();
+          add_partial_cg(acc, P.workspace + (size_t)r * (BM * BN), tid);
+        }
+        epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
+      }
     }
   }
 }
@@ -283,8 +369,10 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
       if ((err = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem)) != cudaSuccess) return err;
       attr_done = true;
     }
-    const int grid = units < num_sms ? units : num_sms;
-    dgemm_tma_ws_kernel<TMA_STAGES><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmB, P, units);
+    // data-parallel units first (tiles before sk_tile0, times splits), stream-K ranges after
+    const int dp_units = (P.sk_tiles > 0 ? P.sk_tile0 : tiles) * P.splits;
+    const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < num_sms ? dp_units : num_sms);
+    dgemm_tma_ws_kernel<TMA_STAGES><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmB, P, dp_units);
   } else {
     const int smem = CPA_STAGES * STAGE_BYTES + 1024;
     static bool attr_done = false;

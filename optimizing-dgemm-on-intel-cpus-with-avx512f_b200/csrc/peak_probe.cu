@@ -33,7 +33,7 @@ struct Stamp { unsigned long long cyc; unsigned long long ns; };
 
 // NACC independent accumulator pairs per warp; each loop trip issues NACC DMMAs.
 template <int NACC>
-__global__ void __launch_bounds__(1024) dmma_kernel(double* out, Stamp* st, int iters) {
+__global__ void __launch_bounds__(NACC >= 16 ? 256 : 1024) dmma_kernel(double* out, Stamp* st, int iters) {
   double acc[NACC][2];
 #pragma unroll
   for (int i = 0; i < NACC; i++) { acc[i][0] = 0.0; acc[i][1] = 0.0; }
@@ -128,7 +128,7 @@ int main(int argc, char** argv) {
   run("dmma_m8n8k4", dmma_kernel<4>, 4, 4, 512.0, iters * 2, nsm, d_out, d_st);
   run("dmma_m8n8k4", dmma_kernel<32>, 4, 32, 512.0, iters / 2, nsm, d_out, d_st);  // a 32-accumulator warp tile, 1 warp/SMSP
   run("dmma_m8n8k4", dmma_kernel<32>, 8, 32, 512.0, iters / 2, nsm, d_out, d_st);  // ... 2 warps/SMSP (the GEMM's shape)
-  run("dmma_m8n8k4", dmma_kernel<8>, 16, 8, 512.0, iters, nsm, d_out, d_st);
+  run("dmma_m8n8k4", dmma_kernel<8>, 16, 8, 512.0, iters, nsm, d_out, d_st);       // 4 warps/SMSP
   // DFMA: 32 lanes * 2 flop = 64 flop per warp instruction
   run("dfma", dfma_kernel<1>, 4, 1, 64.0, iters * 8, nsm, d_out, d_st);            // dependent chain = latency
   run("dfma", dfma_kernel<16>, 4, 16, 64.0, iters * 4, nsm, d_out, d_st);

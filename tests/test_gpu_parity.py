@@ -83,10 +83,37 @@ def test_split_k_forced(dg, variant, splits):
     gu.run_device(dg, 256, 384, 1000, 2.0, 0.5, variant=variant, splits=splits)
 
 
-def test_tall_skinny_heuristic_uses_split_k(dg):
+def test_tall_skinny_heuristic_fills_the_gpu(dg):
+    """M=N=512, K=16384 has 16 output tiles for 148 SMs: the plan must decompose K (stream-K on the TMA kernel,
+    split-K on the cp.async kernel) so that (nearly) every SM works."""
     p = dg.plan(512, 512, 16384)
-    assert p["splits"] > 1, p
+    assert p["ctas"] > 100 and (p["stream_k_tiles"] > 0 or p["splits"] > 1), p
     gu.run_device(dg, 512, 512, 16384, 1.0, 1.0)
+    gu.run_device(dg, 512, 512, 16384, 1.0, 1.0, pad=(1, 1, 1))   # odd LD -> cp.async kernel + split-K
+
+
+@pytest.mark.parametrize("shape", [(2048, 2048, 2048), (1920, 1664, 512), (1152, 1280, 4096), (640, 512, 8192),
+                                   (128, 128, 4096), (1000, 1003, 1000), (18944, 128, 256), (2304, 2048, 128)])
+def test_stream_k_shapes(dg, shape):
+    """Shapes whose tile count is not a multiple of 148: data-parallel waves + stream-K tail, or all stream-K."""
+    M, N, K = shape
+    pad = (0, 1, 0) if K % 2 else (0, 0, 0)
+    gu.run_device(dg, M, N, K, 1.5, 0.5, pad=pad, variant=TMA)
+
+
+def test_stream_k_is_deterministic_and_close_to_data_parallel(dg):
+    M, N, K = 1920, 1664, 768
+    A, B, C0 = gu.make_inputs(M, N, K)
+    outs = []
+    for splits in (0, 0, 1):   # auto (stream-K) twice, then forced pure data-parallel
+        dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, TMA, splits)
+        dg.lib.dgemm_b200_sync(None)
+        outs.append(dC.to_host())
+        dA.free(); dB.free(); dC.free()
+    assert np.array_equal(outs[0], outs[1])                       # run-to-run bit-identical
+    gu.check(M, N, K, 1.0, A, B, 1.0, C0, outs[0], Cref=None)     # and inside the bound
+    gu.check(M, N, K, 1.0, A, B, 1.0, C0, outs[2], Cref=None)
 
 
 def test_split_k_is_deterministic(dg):
@@ -108,7 +135,7 @@ def test_variants_agree_bitwise(dg):
     outs = []
     for variant in (TMA, CPA8, CPA16):
         dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
-        dg.dgemm_device(520, 390, 777, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, variant, 1)
+        dg.dgemm_device(520, 390, 777, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, variant, 1)  # pure DP
         dg.lib.dgemm_b200_sync(None)
         outs.append(dC.to_host())
         dA.free(); dB.free(); dC.free()
