@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--size", type=int, default=None, help="M=N=K override")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: how K-slabs of A reach the other GPUs (fused = pulled over NVLink by the GEMM kernel "
+                         "itself; nccl = ncclBroadcast per slab, the baseline)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cublas", action="store_true")
@@ -200,7 +203,7 @@ def main():
     import torch
     import torch.distributed as dist
     import dgemm_b200 as dg
-    from dgemm_b200.sharding import partition, sharded_dgemm_step
+    from dgemm_b200.sharding import partition, sharded_dgemm_step, sharded_dgemm_step_fused
 
     N = args.gpus
     rank = int(os.environ.get("RANK", "0"))
@@ -228,28 +231,51 @@ def main():
     kb = partition(K, N, 16)
     n0, n1 = nb[rank], nb[rank + 1]
     ncols = n1 - n0
-    A = torch.empty(M * K, dtype=torch.float64, device=dev)          # full A (M x K, ld = M) on every rank
+    fused = N > 1 and args.exchange == "fused"
+    ctx = {"peers": {}}
+    if fused:
+        # A lives in a plain cudaMalloc buffer (IPC-exportable); peers map it and the GEMM kernel pulls from it
+        A_ptr = dg.malloc(8 * M * K)
+        handles = [None] * N
+        dist.all_gather_object(handles, dg.ipc_export(A_ptr))
+        ctx["peers"] = {g: dg.ipc_open(handles[g]) for g in range(N) if g != rank}
+        A = None
+    else:
+        A = torch.empty(M * K, dtype=torch.float64, device=dev)      # full A (M x K, ld = M) on every rank
+        A_ptr = A.data_ptr()
     B = torch.empty(K * max(ncols, 1), dtype=torch.float64, device=dev)
     Cm = torch.empty(M * max(ncols, 1), dtype=torch.float64, device=dev)
     k0, k1 = kb[rank], kb[rank + 1]
     # only the rank's own K-slab of A is initialised locally; the rest arrives over NVLink inside each step
-    dg.fill_signed(A.data_ptr() + 8 * k0 * M, M, k1 - k0, M, 1, 0, k0, sptr)
+    dg.fill_signed(A_ptr + 8 * k0 * M, M, k1 - k0, M, 1, 0, k0, sptr)
     dg.fill_signed(B.data_ptr(), K, ncols, K, 2, 0, n0, sptr)
     dg.fill_signed(Cm.data_ptr(), M, ncols, M, 3, 0, n0, sptr)
     torch.cuda.synchronize()
+    if N > 1:
+        dist.barrier()
+
+    def gemm_fetch(kbeg, kc, b_eff, fetch):
+        src = dst = nbytes = 0
+        if fetch is not None:
+            owner, fk, fc = fetch
+            src, dst, nbytes = ctx["peers"][owner] + 8 * fk * M, A_ptr + 8 * fk * M, 8 * fc * M
+        dg.dgemm_device_fetch(M, ncols, kc, alpha, A_ptr + 8 * kbeg * M, M, B.data_ptr() + 8 * kbeg, K, b_eff,
+                              Cm.data_ptr(), M, sptr, src, dst, nbytes)
 
     def step():
-        """One pass over this rank's panel. N > 1: slab g of A is broadcast from rank g (NVLink) while the GEMM on
-        the previous slab runs; the own slab needs no transfer and goes first."""
+        """One pass over this rank's panel. N > 1: the own K-slab of A needs no transfer and goes first; every GEMM
+        call pulls the next slab over NVLink with its spare warps (fused) or waits for its ncclBroadcast (nccl)."""
         if N == 1:
-            dg.dgemm_device(M, Nn, K, alpha, A.data_ptr(), M, B.data_ptr(), K, beta, Cm.data_ptr(), M, sptr)
-            return
-        sharded_dgemm_step(
-            rank, N, kb, beta,
-            lambda g: dist.broadcast(A[kb[g] * M: kb[g + 1] * M], src=g, async_op=True),
-            lambda work: work.wait(),  # stream-level wait on the NCCL stream
-            lambda kbeg, kc, b_eff: dg.dgemm_device(M, ncols, kc, alpha, A.data_ptr() + 8 * kbeg * M, M,
-                                                    B.data_ptr() + 8 * kbeg, K, b_eff, Cm.data_ptr(), M, sptr))
+            dg.dgemm_device(M, Nn, K, alpha, A_ptr, M, B.data_ptr(), K, beta, Cm.data_ptr(), M, sptr)
+        elif fused:
+            sharded_dgemm_step_fused(rank, N, kb, beta, gemm_fetch)
+        else:
+            sharded_dgemm_step(
+                rank, N, kb, beta,
+                lambda g: dist.broadcast(A[kb[g] * M: kb[g + 1] * M], src=g, async_op=True),
+                lambda work: work.wait(),  # stream-level wait on the NCCL stream
+                lambda kbeg, kc, b_eff: dg.dgemm_device(M, ncols, kc, alpha, A_ptr + 8 * kbeg * M, M,
+                                                        B.data_ptr() + 8 * kbeg, K, b_eff, Cm.data_ptr(), M, sptr))
 
     def barrier():
         if N > 1:
@@ -288,7 +314,8 @@ def main():
     # ---- end to end through the reference-facing host-pointer entry (pinned host buffers) -----------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A, B, Cm, max(2, min(steps, 5)))
+        e2e = run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm,
+                      max(2, min(steps, 5)), fused, step)
 
     if rank != 0:
         if N > 1:
@@ -333,7 +360,9 @@ def main():
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"M=N=K={size} column-major DGEMM C=alpha*A*B+beta*C, alpha=1 beta=1, LD=dim",
                    "sharding": "single GPU" if N == 1 else
-                   f"column panels of B/C over {N} GPUs, A K-slabs replicated over NVLink (NCCL) inside the step",
+                   f"column panels of B/C over {N} GPUs; K-slabs of A replicated over NVLink inside the step, " +
+                   ("pulled from peer HBM by spare warps of the DGEMM kernel (fused)" if fused else
+                    "one ncclBroadcast per slab (baseline)"),
                    "l2": "operands (3 x %.1f GB) far exceed the 126 MB L2; no flush needed" % (8.0 * size * size / 1e9),
                    "inputs": "U(-1,1) 53-bit counter-based, generated on device (dgemm_b200_fill_signed)",
                    "timing": "CUDA events on the launching stream, max over ranks"},
@@ -373,18 +402,18 @@ def cublas_ceiling(torch, A, B, Cm, M, Nn, K):
     return {"tflops": 2.0 * M * Nn * K / ms / 1e9, "ms": ms, "note": "torch.matmul(float64) -> cublasDgemm; ceiling only"}
 
 
-def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A, B, Cm, reps):
+def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm, reps, fused, step):
     """Same metric through the public host-pointer API with HOST (pinned) buffers, copies inside the timed region.
     N = 1: mydgemm_gpu_v20 (the reference's 11-argument signature).  N > 1: each rank stages its own K-slab of A and
-    its B/C panels from pinned memory, A is exchanged over NVLink, C panel copied back."""
-    from dgemm_b200.sharding import sharded_dgemm_step
+    its B/C panels from pinned memory, runs the sharded step (A exchanged over NVLink), copies its C panel back."""
     n0, n1 = nb[rank], nb[rank + 1]
     ncols = n1 - n0
     k0, k1 = kb[rank], kb[rank + 1]
     hA = torch.empty(M * (k1 - k0), dtype=torch.float64).pin_memory()
     hB = torch.empty(K * ncols, dtype=torch.float64).pin_memory()
     hC = torch.empty(M * ncols, dtype=torch.float64).pin_memory()
-    hA.copy_(A[k0 * M: k1 * M])
+    dg._check(dg.lib.dgemm_b200_d2h(hA.data_ptr(), M, A_ptr + 8 * k0 * M, M, M, k1 - k0, None))
+    dg._check(dg.lib.dgemm_b200_sync(None))
     hB.copy_(B[: K * ncols])
     hC.copy_(Cm[: M * ncols])
     torch.cuda.synchronize()
@@ -392,20 +421,18 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A, B, 
     d2h = 8 * hC.numel()
     stream = torch.cuda.current_stream()
     sptr = stream.cuda_stream
+    token = torch.zeros(1, device=dev)
 
     def one():
         if N == 1:
             dg.mydgemm_gpu_v20(M, Nn, K, alpha, hA.data_ptr(), M, hB.data_ptr(), K, beta, hC.data_ptr(), M)
             return
-        dg._check(dg.lib.dgemm_b200_h2d(A.data_ptr() + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, sptr))
+        dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, sptr))
+        dist.all_reduce(token)  # stream-ordered barrier: every owner's K-slab is in its HBM before anyone pulls it
         dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr(), K, hB.data_ptr(), K, K, ncols, sptr))
         dg._check(dg.lib.dgemm_b200_h2d(Cm.data_ptr(), M, hC.data_ptr(), M, M, ncols, sptr))
-        sharded_dgemm_step(
-            rank, N, kb, beta,
-            lambda g: dist.broadcast(A[kb[g] * M: kb[g + 1] * M], src=g, async_op=True),
-            lambda work: work.wait(),
-            lambda kbeg, kc, b_eff: dg.dgemm_device(M, ncols, kc, alpha, A.data_ptr() + 8 * kbeg * M, M,
-                                                    B.data_ptr() + 8 * kbeg, K, b_eff, Cm.data_ptr(), M, sptr))
+        step()
+        dist.all_reduce(token)  # ... and nobody still reads a slab when its owner overwrites it in the next pass
         dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr(), M, Cm.data_ptr(), M, M, ncols, sptr))
         stream.synchronize()
 
@@ -428,7 +455,9 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A, B, 
     return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "unit": UNIT, "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps,
             "api": "mydgemm_gpu_v20(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC) with pinned host pointers" if N == 1 else
-                   "per-rank dgemm_b200_h2d + NCCL A exchange + dgemm_b200_device + dgemm_b200_d2h, pinned host buffers"}
+                   "per rank: dgemm_b200_h2d (own K-slab of A, B/C panels) + sharded step ("
+                   + ("dgemm_b200_device_fetch, fused NVLink pull" if fused else "ncclBroadcast + dgemm_b200_device")
+                   + ") + dgemm_b200_d2h, pinned host buffers"}
 
 
 if __name__ == "__main__":

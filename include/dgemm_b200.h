@@ -72,6 +72,19 @@ int dgemm_b200_device(int M, int N, int K, double alpha, const double *dA, long 
 int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
                          long long ldb, double beta, double *dC, long long ldc, void *stream, int variant,
                          int splits);
+/* DGEMM fused with an NVLink fetch: while the FP64 tensor-core warps compute this call, spare warps of the same
+ * kernel copy fetch_bytes from fetch_src to fetch_dst (16-byte aligned, multiple of 16).  fetch_src is normally a
+ * PEER GPU's buffer (dgemm_b200_ipc_open / peer access): the multi-GPU layer uses it to pull the NEXT K-slab of A
+ * while the current one is being multiplied, so the replication of A never waits for free SMs.  fetch_bytes = 0
+ * makes it identical to dgemm_b200_device.  The copy is complete when the call's kernel is (stream order). */
+int dgemm_b200_device_fetch(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
+                            long long ldb, double beta, double *dC, long long ldc, void *stream,
+                            const void *fetch_src, void *fetch_dst, size_t fetch_bytes);
+/* CUDA IPC plumbing for one-process-per-GPU launches: export a dgemm_b200_malloc'ed buffer as a 64-byte handle,
+ * open a peer's handle as a device pointer usable as fetch_src, close it */
+int dgemm_b200_ipc_export(const void *dptr, void *handle64);
+int dgemm_b200_ipc_open(const void *handle64, void **dptr);
+int dgemm_b200_ipc_close(void *dptr);
 /* plan the heuristic would use: writes variant, split-K factor, CTA count and the number of output tiles handled
  * by the stream-K tail (any out pointer may be NULL); returns status */
 int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const double *dB, long long ldb,

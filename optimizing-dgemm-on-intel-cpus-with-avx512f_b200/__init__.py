@@ -30,7 +30,8 @@ VARIANT_NAMES = {VARIANT_AUTO: "auto", VARIANT_TMA: "tma_ws", VARIANT_CPASYNC8: 
 EXPORTS = [
     "mydgemm_gpu_v20", "mydgemm_gpu_v21", "dgemm_b200_last_status", "dgemm_b200_last_error",
     "dgemm_b200_device_count", "dgemm_b200_init", "dgemm_b200_shutdown", "dgemm_b200_set_max_gpus",
-    "dgemm_b200_device", "dgemm_b200_device_ex", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
+    "dgemm_b200_device", "dgemm_b200_device_ex", "dgemm_b200_device_fetch", "dgemm_b200_ipc_export",
+    "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
     "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz",
@@ -64,6 +65,10 @@ lib.dgemm_b200_set_max_gpus.argtypes = [C.c_int]
 _DEV_ARGS = [C.c_int, C.c_int, C.c_int, C.c_double, _vp, _ll, _vp, _ll, C.c_double, _vp, _ll]
 lib.dgemm_b200_device.argtypes = _DEV_ARGS + [_vp]
 lib.dgemm_b200_device_ex.argtypes = _DEV_ARGS + [_vp, C.c_int, C.c_int]
+lib.dgemm_b200_device_fetch.argtypes = _DEV_ARGS + [_vp, _vp, _vp, C.c_size_t]
+lib.dgemm_b200_ipc_export.argtypes = [_vp, C.c_char_p]
+lib.dgemm_b200_ipc_open.argtypes = [C.c_char_p, C.POINTER(_vp)]
+lib.dgemm_b200_ipc_close.argtypes = [_vp]
 lib.dgemm_b200_plan.argtypes = [C.c_int, C.c_int, C.c_int, _vp, _ll, _vp, _ll, C.POINTER(C.c_int),
                                 C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
 lib.dgemm_b200_malloc.argtypes = [C.c_size_t]
@@ -150,6 +155,42 @@ def dgemm_device(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0, vari
     st = lib.dgemm_b200_device_ex(M, N, K, float(alpha), int(dA), lda, int(dB), ldb, float(beta), int(dC), ldc,
                                   int(stream) or None, variant, splits)
     _check(st)
+
+
+def dgemm_device_fetch(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0, fetch_src=0, fetch_dst=0,
+                       fetch_bytes=0):
+    """dgemm_device fused with an NVLink pull of fetch_bytes from fetch_src (peer memory) to fetch_dst."""
+    st = lib.dgemm_b200_device_fetch(M, N, K, float(alpha), int(dA), lda, int(dB), ldb, float(beta), int(dC), ldc,
+                                     int(stream) or None, int(fetch_src) or None, int(fetch_dst) or None, fetch_bytes)
+    _check(st)
+
+
+def ipc_export(dptr):
+    buf = C.create_string_buffer(64)
+    _check(lib.dgemm_b200_ipc_export(int(dptr), buf))
+    return buf.raw
+
+
+def ipc_open(handle):
+    out = _vp()
+    _check(lib.dgemm_b200_ipc_open(handle, C.byref(out)))
+    return out.value
+
+
+def ipc_close(dptr):
+    _check(lib.dgemm_b200_ipc_close(int(dptr)))
+
+
+def malloc(nbytes):
+    p = lib.dgemm_b200_malloc(nbytes)
+    if not p:
+        _check()
+        raise DgemmError(ERR_OOM, "dgemm_b200_malloc failed")
+    return p
+
+
+def free(dptr):
+    lib.dgemm_b200_free(int(dptr))
 
 
 def plan(M, N, K, dA=0, lda=None, dB=0, ldb=None):

@@ -187,6 +187,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   P.k_tiles = (K + dg::BK - 1) / dg::BK;
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
+  P.fetch_src = nullptr; P.fetch_dst = nullptr; P.fetch_bytes = 0;
   // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
   P.group_m = std::min(P.tiles_m, 16);
   P.c_vec2 = ((uintptr_t)dC % 16 == 0) && (ldc % 2 == 0);
@@ -216,11 +217,22 @@ int check_args(int M, int N, int K, const void* A, long long lda, const void* B,
 }
 
 // the device-side DGEMM on context c (current device must be c.dev)
+struct Fetch {
+  const void* src = nullptr;
+  void* dst = nullptr;
+  size_t bytes = 0;
+};
+
 int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
-               long long ldb, double beta, double* dC, long long ldc, cudaStream_t stream, int variant, int splits) {
-  if (M == 0 || N == 0) return ok();
-  if (alpha == 0.0 || K == 0) {  // C = beta*C only (kernel18.h:644-645)
-    CU_TRY(dg::launch_scale_c(dC, M, N, ldc, beta, c.num_sms, stream));
+               long long ldb, double beta, double* dC, long long ldc, cudaStream_t stream, int variant, int splits,
+               Fetch fetch = Fetch()) {
+  if (fetch.bytes && (((uintptr_t)fetch.src | (uintptr_t)fetch.dst | fetch.bytes) & 15))
+    return fail(DGEMM_B200_ERR_BAD_ARG, "fused fetch needs 16-byte aligned src/dst and a multiple of 16 bytes");
+  if (M == 0 || N == 0 || alpha == 0.0 || K == 0) {
+    // no GEMM kernel to fuse with: the copy engine does the fetch
+    if (fetch.bytes) CU_TRY(cudaMemcpyAsync(fetch.dst, fetch.src, fetch.bytes, cudaMemcpyDefault, stream));
+    if (M == 0 || N == 0) return ok();
+    CU_TRY(dg::launch_scale_c(dC, M, N, ldc, beta, c.num_sms, stream));  // C = beta*C only (kernel18.h:644-645)
     return ok();
   }
   dg::Params P;
@@ -246,6 +258,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
       P.sk_epoch = ++c.sk_epoch;
     }
   }
+  P.fetch_src = fetch.src; P.fetch_dst = fetch.dst; P.fetch_bytes = fetch.bytes;
   CU_TRY(dg::launch_gemm(P, variant, c.num_sms, stream));
   if (uses_ws) {
     CU_TRY(cudaEventRecord(c.ws_free, stream));
@@ -358,11 +371,13 @@ int dgemm_b200_internal_ok() { return ok(); }
 std::recursive_mutex& dgemm_b200_internal_mutex() { return g_mu; }
 int dgemm_b200_internal_run_on(int dev, int M, int N, int K, double alpha, const double* dA, long long lda,
                                const double* dB, long long ldb, double beta, double* dC, long long ldc,
-                               cudaStream_t stream) {
+                               cudaStream_t stream, const void* fetch_src, void* fetch_dst, size_t fetch_bytes) {
   DeviceCtx* c = nullptr;
   int st = ensure_ctx(dev, &c);
   if (st) return st;
-  return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream, dg::VARIANT_AUTO, 0);
+  Fetch f;
+  f.src = fetch_src; f.dst = fetch_dst; f.bytes = fetch_bytes;
+  return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream, dg::VARIANT_AUTO, 0, f);
 }
 
 extern "C" {
@@ -446,6 +461,37 @@ int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double* dA, lo
   DeviceCtx* c;
   if ((st = current_ctx(&c))) return st;
   return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, (cudaStream_t)stream, variant, splits);
+}
+
+int dgemm_b200_device_fetch(int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
+                            long long ldb, double beta, double* dC, long long ldc, void* stream, const void* fetch_src,
+                            void* fetch_dst, size_t fetch_bytes) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  int st = check_args(M, N, K, dA, lda, dB, ldb, dC, ldc);
+  if (st) return st;
+  DeviceCtx* c;
+  if ((st = current_ctx(&c))) return st;
+  Fetch f;
+  f.src = fetch_src; f.dst = fetch_dst; f.bytes = fetch_bytes;
+  return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, (cudaStream_t)stream, dg::VARIANT_AUTO, 0, f);
+}
+
+int dgemm_b200_ipc_export(const void* dptr, void* handle64) {
+  cudaIpcMemHandle_t h;
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  CU_TRY(cudaIpcGetMemHandle(&h, const_cast<void*>(dptr)));
+  memcpy(handle64, &h, 64);
+  return ok();
+}
+int dgemm_b200_ipc_open(const void* handle64, void** dptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  CU_TRY(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return ok();
+}
+int dgemm_b200_ipc_close(void* dptr) {
+  CU_TRY(cudaIpcCloseMemHandle(dptr));
+  return ok();
 }
 
 int dgemm_b200_device(int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,

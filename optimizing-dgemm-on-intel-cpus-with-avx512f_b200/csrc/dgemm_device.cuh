@@ -58,6 +58,12 @@ struct Params {
   int sk_grid;                // CTAs launched when sk_tiles > 0 (every one of them must be co-resident)
   unsigned int sk_epoch;      // flag value that means "partial of this launch is in the workspace"
   unsigned int* sk_flags;     // one flag per CTA range
+  // ---- fused NVLink fetch (TMA kernel only): while the DMMA warps work on this call's K-slab, the three spare
+  // warps of the producer warpgroup copy fetch_bytes from fetch_src (normally a PEER GPU's copy of the next K-slab
+  // of A, mapped through CUDA IPC / peer access) to fetch_dst in local HBM.  16-byte aligned, multiple of 16.
+  const void* fetch_src;
+  void* fetch_dst;
+  unsigned long long fetch_bytes;
 };
 
 // ---- lane -> matrix index maps (see header comment) -------------------------------------------------------
@@ -268,6 +274,18 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// streaming 16-byte copy primitives for the fused fetch: peer loads bypass L1 allocation, stores go straight to L2
+__device__ __forceinline__ int4 ld_stream_16(const int4* p) {
+  int4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_stream_16(int4* p, const int4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
 // barrier among the 8 consumer warps only (the producer warpgroup never joins): named barrier 1
 __device__ __forceinline__ void consumer_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_THREADS) : "memory"); }
 

@@ -122,6 +122,25 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
+    } else if (warp > CONSUMER_WARPS && P.fetch_bytes) {
+      // ---------------- fetch warps (9..11): NVLink pull of the NEXT K-slab of A, overlapped with the math ----------
+      // every CTA copies one contiguous 1/gridDim.x share; 4 x 16 B per lane in flight
+      constexpr int FETCH_THREADS = 96, UNROLL = 4;
+      const unsigned long long n16 = P.fetch_bytes >> 4;
+      const unsigned long long per = (n16 + gridDim.x - 1) / gridDim.x;
+      const unsigned long long beg = per * blockIdx.x, end = beg + per < n16 ? beg + per : n16;
+      const int4* src = reinterpret_cast<const int4*>(P.fetch_src);
+      int4* dst = reinterpret_cast<int4*>(P.fetch_dst);
+      const int t = tid - (CONSUMER_THREADS + 32);
+      unsigned long long i = beg + t;
+      for (; i + (UNROLL - 1) * FETCH_THREADS < end; i += UNROLL * FETCH_THREADS) {
+        int4 v[UNROLL];
+#pragma unroll
+        for (int j = 0; j < UNROLL; j++) v[j] = ld_stream_16(src + i + j * FETCH_THREADS);
+#pragma unroll
+        for (int j = 0; j < UNROLL; j++) st_stream_16(dst + i + j * FETCH_THREADS, v[j]);
+      }
+      for (; i < end; i += FETCH_THREADS) st_stream_16(dst + i, ld_stream_16(src + i));
     }
   } else {
     // ------------------------------- consumer warps: DMMA main loop + epilogue -------------------------------
@@ -364,10 +383,12 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN))
       return cudaErrorInvalidValue;
     const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 1024;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static bool attr_done[64] = {};  // function attributes are per device
+    int dev = 0;
+    if ((err = cudaGetDevice(&dev)) != cudaSuccess) return err;
+    if (!attr_done[dev & 63]) {
       if ((err = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem)) != cudaSuccess) return err;
-      attr_done = true;
+      attr_done[dev & 63] = true;
     }
     // data-parallel units first (tiles before sk_tile0, times splits), stream-K ranges after
     const int dp_units = (P.sk_tiles > 0 ? P.sk_tile0 : tiles) * P.splits;
@@ -375,11 +396,17 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     dgemm_tma_ws_kernel<TMA_STAGES><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmB, P, dp_units);
   } else {
     const int smem = CPA_STAGES * STAGE_BYTES + 1024;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static bool attr_done[64] = {};
+    int dev = 0;
+    if ((err = cudaGetDevice(&dev)) != cudaSuccess) return err;
+    if (!attr_done[dev & 63]) {
       if ((err = set_smem(dgemm_cpasync_kernel<1, CPA_STAGES>, smem)) != cudaSuccess) return err;
       if ((err = set_smem(dgemm_cpasync_kernel<2, CPA_STAGES>, smem)) != cudaSuccess) return err;
-      attr_done = true;
+      attr_done[dev & 63] = true;
+    }
+    if (P.fetch_bytes) {  // no spare warps in this kernel: the copy engine does the fetch, stream-ordered before it
+      if ((err = cudaMemcpyAsync(P.fetch_dst, P.fetch_src, P.fetch_bytes, cudaMemcpyDefault, stream)) != cudaSuccess)
+        return err;
     }
     if (variant == VARIANT_CPASYNC16)
       dgemm_cpasync_kernel<2, CPA_STAGES><<<units, CONSUMER_THREADS, smem, stream>>>(P);

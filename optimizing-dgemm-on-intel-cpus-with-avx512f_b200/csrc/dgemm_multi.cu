@@ -5,13 +5,17 @@
 //
 //   GPU g owns columns [n_g, n_g+1) of B and C (multiples of the 128-wide CTA tile).
 //   A (M x K) is cut into G K-slabs (contiguous column ranges).  GPU g copies slab g from the host over its OWN
-//   PCIe link, then the slabs are exchanged GPU<->GPU over NVLink with one ncclBroadcast per slab (an
-//   all-gather with uneven counts).  Each GPU starts computing on its own slab at once and consumes the other
-//   slabs as their broadcasts complete:  C_g = beta*C_g + alpha*A[:,slab]*B_g[slab,:]  for the first slab,
-//   C_g += alpha*A[:,slab]*B_g[slab,:] for the rest.  No reduction: column panels are independent.
+//   PCIe link; the slabs then travel GPU<->GPU over NVLink.  Each GPU starts on its own slab at once:
+//   C_g = beta*C_g + alpha*A[:,slab]*B_g[slab,:] for the first slab, C_g += ... for the rest.  No reduction:
+//   column panels are independent.
 //
-// NCCL is resolved with dlopen at first use so the library loads on boxes without NCCL (v21 then fails with
-// DGEMM_B200_ERR_NCCL; v20 is unaffected).
+// Two exchange modes:
+//   fused (default when every GPU pair has peer access): the DGEMM kernel working on slab i pulls slab i+1 from
+//       its owner's HBM with its spare warps (dgemm_device.cuh, "fetch warps"), so the replication of A costs no
+//       SMs and no extra launches and is hidden behind the math.  A persistent kernel that owns every SM starves
+//       NCCL's own kernels (measured: 2 GPUs 57 TF with ncclBroadcast vs ~72 ideal), which is why this exists.
+//   nccl  (DGEMM_B200_EXCHANGE=nccl, or no peer access): one ncclBroadcast per slab on a side stream.
+// NCCL is resolved with dlopen at first use so the library loads on boxes without NCCL.
 #include "../../include/dgemm_b200.h"
 #include "dgemm_device.cuh"
 #include "dgemm_host.h"
@@ -21,6 +25,8 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <future>
 #include <mutex>
 #include <thread>
@@ -30,7 +36,7 @@ int dgemm_b200_internal_fail(int status, const char* msg);
 int dgemm_b200_internal_ok();
 int dgemm_b200_internal_run_on(int dev, int M, int N, int K, double alpha, const double* dA, long long lda,
                                const double* dB, long long ldb, double beta, double* dC, long long ldc,
-                               cudaStream_t stream);
+                               cudaStream_t stream, const void* fetch_src, void* fetch_dst, size_t fetch_bytes);
 
 void dgemm_b200_multi_shutdown();
 
@@ -71,6 +77,7 @@ struct DevState {
 
 struct MultiCtx {
   int g = 0;
+  bool fused = false;  // peer access everywhere -> in-kernel NVLink fetch instead of NCCL broadcasts
   NcclApi nccl;
   std::vector<ncclComm_t> comms;
   std::vector<DevState> dev;
@@ -101,11 +108,34 @@ int ensure_multi(int g) {
   if (m.g != 0) {
     dgemm_b200_multi_shutdown();
   }
-  if (!m.nccl.load()) return dgemm_b200_internal_fail(DGEMM_B200_ERR_NCCL, "libnccl.so.2 not found (dlopen)");
+  // peer access for every ordered pair -> fused exchange
+  const char* mode = getenv("DGEMM_B200_EXCHANGE");
+  bool want_fused = !(mode && strcmp(mode, "nccl") == 0);
+  if (want_fused) {
+    for (int a = 0; a < g && want_fused; a++)
+      for (int b = 0; b < g && want_fused; b++) {
+        if (a == b) continue;
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, a, b) != cudaSuccess || !can) want_fused = false;
+      }
+    for (int a = 0; a < g && want_fused; a++) {
+      MCU(cudaSetDevice(a));
+      for (int b = 0; b < g; b++) {
+        if (a == b) continue;
+        cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) { cudaGetLastError(); want_fused = false; break; }
+      }
+    }
+  }
+  m.fused = want_fused;
   m.comms.assign(g, nullptr);
-  std::vector<int> devs(g);
-  for (int i = 0; i < g; i++) devs[i] = i;
-  MNCCL(m.nccl.CommInitAll(m.comms.data(), g, devs.data()));
+  if (!m.fused) {
+    if (!m.nccl.load()) return dgemm_b200_internal_fail(DGEMM_B200_ERR_NCCL, "libnccl.so.2 not found (dlopen)");
+    std::vector<int> devs(g);
+    for (int i = 0; i < g; i++) devs[i] = i;
+    MNCCL(m.nccl.CommInitAll(m.comms.data(), g, devs.data()));
+  }
   m.dev.assign(g, DevState());
   for (int d = 0; d < g; d++) {
     MCU(cudaSetDevice(d));
@@ -152,7 +182,7 @@ void dgemm_b200_multi_shutdown() {
     cudaStreamDestroy(s.s_h2d); cudaStreamDestroy(s.s_comm); cudaStreamDestroy(s.s_compute); cudaStreamDestroy(s.s_d2h);
     cudaEventDestroy(s.ev_slab); cudaEventDestroy(s.ev_bc); cudaEventDestroy(s.ev_done);
     for (auto e : s.ev_bcast) cudaEventDestroy(e);
-    if (m.comms[d]) m.nccl.CommDestroy(m.comms[d]);
+    if (d < (int)m.comms.size() && m.comms[d]) m.nccl.CommDestroy(m.comms[d]);
   }
   m.dev.clear();
   m.comms.clear();
@@ -221,7 +251,7 @@ int dgemm_b200_run_host_multi(int M, int N, int K, double alpha, const double* A
   }
   // NVLink exchange: slab g is broadcast from GPU g to everyone (grouped -> one collective per slab)
   int nccl_rc = 0;
-  if (need_ab) {
+  if (need_ab && !m.fused) {
     for (int g = 0; g < G && !nccl_rc; g++) {
       if (slab_fut[g].get() != 0) { nccl_rc = -1; break; }
       const size_t count = (size_t)(kb[g + 1] - kb[g]) * ldaD;
@@ -260,17 +290,45 @@ int dgemm_b200_run_host_multi(int M, int N, int K, double alpha, const double* A
     if (nc <= 0) continue;
     MCU(cudaStreamWaitEvent(s.s_compute, s.ev_bc, 0));
     if (!need_ab) {
-      if ((st = dgemm_b200_internal_run_on(d, M, nc, K, alpha, s.a, ldaD, s.b, ldbD, beta, s.c, ldcD, s.s_compute)))
+      if ((st = dgemm_b200_internal_run_on(d, M, nc, K, alpha, s.a, ldaD, s.b, ldbD, beta, s.c, ldcD, s.s_compute,
+                                           nullptr, nullptr, 0)))
         return st;
     } else {
+      // non-empty slabs in ring order starting at the own one
+      std::vector<int> order;
+      for (int i = 0; i < G; i++)
+        if (kb[(d + i) % G + 1] - kb[(d + i) % G] > 0) order.push_back((d + i) % G);
       bool first = true;
-      for (int i = 0; i < G; i++) {
-        const int g = (d + i) % G;
+      if (m.fused && !order.empty() && order[0] != d) {
+        // own slab empty: a K = 0 call applies beta and fetches the first foreign slab (copy engine)
+        const int nx = order[0];
+        MCU(cudaStreamWaitEvent(s.s_compute, m.dev[nx].ev_slab, 0));
+        if ((st = dgemm_b200_internal_run_on(d, M, nc, 0, alpha, s.a, ldaD, s.b, ldbD, beta, s.c, ldcD, s.s_compute,
+                                             m.dev[nx].a + (size_t)kb[nx] * ldaD, s.a + (size_t)kb[nx] * ldaD,
+                                             (size_t)(kb[nx + 1] - kb[nx]) * ldaD * 8)))
+          return st;
+        first = false;
+      }
+      for (size_t i = 0; i < order.size(); i++) {
+        const int g = order[i];
         const int kc = kb[g + 1] - kb[g];
-        if (kc <= 0) continue;
-        if (g != d) MCU(cudaStreamWaitEvent(s.s_compute, s.ev_bcast[g], 0));
+        const void* fsrc = nullptr;
+        void* fdst = nullptr;
+        size_t fbytes = 0;
+        if (m.fused) {
+          if (i + 1 < order.size()) {  // pull the NEXT slab from its owner while this one is multiplied
+            const int nx = order[i + 1];
+            MCU(cudaStreamWaitEvent(s.s_compute, m.dev[nx].ev_slab, 0));  // owner's H2D of that slab is complete
+            fsrc = m.dev[nx].a + (size_t)kb[nx] * ldaD;
+            fdst = s.a + (size_t)kb[nx] * ldaD;
+            fbytes = (size_t)(kb[nx + 1] - kb[nx]) * ldaD * 8;
+          }
+          if (g == d) MCU(cudaStreamWaitEvent(s.s_compute, s.ev_slab, 0));
+        } else if (g != d) {
+          MCU(cudaStreamWaitEvent(s.s_compute, s.ev_bcast[g], 0));
+        }
         if ((st = dgemm_b200_internal_run_on(d, M, nc, kc, alpha, s.a + (size_t)kb[g] * ldaD, ldaD, s.b + kb[g], ldbD,
-                                             first ? beta : 1.0, s.c, ldcD, s.s_compute)))
+                                             first ? beta : 1.0, s.c, ldcD, s.s_compute, fsrc, fdst, fbytes)))
           return st;
         first = false;
       }

@@ -48,3 +48,29 @@ def sharded_dgemm_step(rank, world, kb, beta, start_exchange, wait_exchange, gem
     if first:  # K == 0: the call degenerates to C = beta*C (reference kernel18.h:644-645 order)
         gemm_slab(0, 0, beta)
     wait_exchange(handles[rank])
+
+
+def sharded_dgemm_step_fused(rank, world, kb, beta, gemm_slab):
+    """Same pass, exchange fused INTO the GEMM: the call that multiplies slab i also pulls slab i+1 from its
+    owner's memory (dgemm_b200_device_fetch), so no collective and no side stream is needed.
+
+    gemm_slab(k_begin, k_count, beta_eff, fetch)   fetch is None or (owner_rank, k_begin, k_count) of the slab to pull
+                                                   from owner_rank's copy of A while this GEMM runs
+    A slab is only ever multiplied after the call that fetched it has been issued (stream order makes it complete).
+    """
+    order = [g for g in slab_order(rank, world) if kb[g + 1] > kb[g]]
+    if not order:  # K == 0
+        gemm_slab(0, 0, beta, None)
+        return
+    applied_beta = False
+    if order[0] != rank:
+        # the own slab is empty (K smaller than the rank count allows): nothing local to start on, so a K = 0 call
+        # applies beta and fetches the first slab (no GEMM kernel to hide it behind: the copy engine does it)
+        g = order[0]
+        gemm_slab(0, 0, beta, (g, kb[g], kb[g + 1] - kb[g]))
+        applied_beta = True
+    for i, g in enumerate(order):
+        nxt = order[i + 1] if i + 1 < len(order) else None
+        fetch = (nxt, kb[nxt], kb[nxt + 1] - kb[nxt]) if nxt is not None else None
+        gemm_slab(kb[g], kb[g + 1] - kb[g], 1.0 if applied_beta else beta, fetch)
+        applied_beta = True

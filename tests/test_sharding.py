@@ -74,6 +74,35 @@ def test_sharded_equals_unsharded(dg, world, shape):
     assert ratio <= 2.0
 
 
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("K", [0, 16, 37, 200])
+def test_fused_order_never_uses_a_slab_before_it_was_fetched(dg, world, K):
+    """sharded_dgemm_step_fused: slab i+1 is pulled by the call that multiplies slab i; beta is applied once; every
+    non-empty slab is multiplied exactly once; the last call fetches nothing."""
+    from dgemm_b200.sharding import partition, sharded_dgemm_step_fused
+    kb = partition(K, world, 16)
+    for rank in range(world):
+        present = {rank}
+        used, betas, fetches = [], [], []
+
+        def gemm(kbeg, kc, b_eff, fetch):
+            if kc:
+                g = max(i for i in range(world) if kb[i] == kbeg and kb[i + 1] > kb[i])
+                assert g in present, f"rank {rank} multiplied slab {g} before it arrived"
+                used.append(g)
+            betas.append(b_eff)
+            fetches.append(fetch)
+            if fetch is not None:
+                owner, fk, fc = fetch
+                assert owner != rank and fk == kb[owner] and fc == kb[owner + 1] - kb[owner] and fc > 0
+                present.add(owner)
+
+        sharded_dgemm_step_fused(rank, world, kb, 0.5, gemm)
+        assert sorted(used) == [g for g in range(world) if kb[g + 1] > kb[g]]
+        assert betas[0] == 0.5 and all(b == 1.0 for b in betas[1:])
+        assert fetches[-1] is None
+
+
 def _gloo_worker(rank, world, port, M, N, K, alpha, beta, out_dir):
     sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
     import dgemm_b200  # noqa: F401
