@@ -34,7 +34,7 @@ EXPORTS = [
     "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
-    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline",
 ]
 
 
@@ -85,6 +85,7 @@ lib.dgemm_b200_sync.argtypes = [_vp]
 lib.dgemm_b200_fill_signed.argtypes = [_vp, C.c_int, C.c_int, _ll, C.c_ulonglong, C.c_ulonglong, C.c_ulonglong, _vp]
 lib.dgemm_b200_time_device.argtypes = _DEV_ARGS + [C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t]
 lib.dgemm_b200_time_device.restype = C.c_double
+lib.dgemm_b200_debug_timeline.argtypes = [_vp]
 lib.dgemm_b200_reset_launch_count.restype = None
 lib.dgemm_b200_sm_clock_mhz.restype = C.c_double
 

@@ -7,6 +7,7 @@
 #include "dgemm_host.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -65,6 +66,7 @@ constexpr int MAX_DEV = 16;
 DeviceCtx g_ctx[MAX_DEV];
 int g_ndev = -1;  // usable devices (compute capability 10.x), -1 = not probed
 int g_max_gpus = 0;
+unsigned long long* g_timeline = nullptr;  // debug: per-CTA phase stamps (dgemm_b200_debug_timeline)
 
 int probe_devices() {
   if (g_ndev >= 0) return g_ndev;
@@ -188,6 +190,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
   P.fetch_src = nullptr; P.fetch_dst = nullptr; P.fetch_bytes = 0;
+  P.timeline = g_timeline;
   // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
   P.group_m = std::min(P.tiles_m, 16);
   P.c_vec2 = ((uintptr_t)dC % 16 == 0) && (ldc % 2 == 0);
@@ -299,41 +302,71 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   }
   if ((st = grow(c.c, (size_t)ldcD * N * 8))) return st;
 
-  // panel width: multiple of the CTA tile, >= 4 panels for overlap when N allows, each panel >= ~1 wave of tiles
-  int panel = N;
-  if (need_ab && N >= 4 * dg::BN) {
-    const int tiles_m = (M + dg::BM - 1) / dg::BM;
-    int min_cols = ((c.num_sms + tiles_m - 1) / tiles_m) * dg::BN;  // one full wave of CTAs
-    panel = std::max(min_cols, ((N / 8 + dg::BN - 1) / dg::BN) * dg::BN);
-    panel = std::min(panel, N);
+  // 2-D pipeline: N is cut into P column panels and K into S slabs; the S*P device calls run on one compute stream in
+  // anti-diagonal order (s + p ascending), so A slabs AND C panels arrive gradually: call (s,p) needs A[:,slab s]
+  // (first use), C panel p (only when s == 0) and the B block (s,p).  After the first two diagonals the H2D stream
+  // stays ahead of the math (per diagonal ~ one A slab + one C panel + d B blocks vs d kernels), so only a few
+  // hundred MB are exposed before the first kernel instead of all of A.  C panel p goes back as soon as its last
+  // slab is done.  Each call is >= ~2 ms of work so the stream-K tails stay cheap.
+  int P = 1, S = 1;
+  if (need_ab) {
+    const double flops = 2.0 * M * (double)N * K;
+    const int want = (int)std::max(1.0, std::min(64.0, flops / 72e9));
+    P = std::max(1, std::min({(int)std::lround(std::sqrt((double)want)), N / 256, 8}));
+    S = std::max(1, std::min({want / P, K / 512, 8}));
   }
-  const int npanels = (N + panel - 1) / panel;
-  std::vector<cudaEvent_t> ev_in(npanels), ev_done(npanels);
-  for (int p = 0; p < npanels; p++) {
-    CU_TRY(cudaEventCreateWithFlags(&ev_in[p], cudaEventDisableTiming));
-    CU_TRY(cudaEventCreateWithFlags(&ev_done[p], cudaEventDisableTiming));
-  }
+  auto bounds = [](int total, int parts, int align) {
+    std::vector<int> b(parts + 1);
+    int per = ((total + parts - 1) / parts + align - 1) / align * align;
+    for (int i = 0; i <= parts; i++) b[i] = std::min(total, i * per);
+    return b;
+  };
+  const std::vector<int> nb = bounds(N, P, dg::BN), kb = bounds(K, S, dg::BK);
+  struct Item { int s, p; };
+  std::vector<Item> order;
+  for (int d = 0; d <= S + P - 2; d++)
+    for (int sI = 0; sI < S; sI++) {
+      const int pI = d - sI;
+      if (pI < 0 || pI >= P) continue;
+      if (nb[pI + 1] <= nb[pI]) continue;                       // empty panel
+      if (need_ab && kb[sI + 1] <= kb[sI]) continue;            // empty slab
+      order.push_back({sI, pI});
+    }
+  std::vector<int> last_slab(P, -1);                            // last non-empty slab index per panel
+  for (const Item& it : order) last_slab[it.p] = std::max(last_slab[it.p], it.s);
+  std::vector<cudaEvent_t> ev_in(order.size()), ev_done(P, nullptr);
+  for (auto& e : ev_in) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (auto& e : ev_done) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  std::vector<char> a_sent(S, 0), first_done(P, 0);
   int result = DGEMM_B200_OK;
   auto body = [&]() -> int {
-    if (need_ab)
-      CU_TRY(cudaMemcpy2DAsync(c.a.p, ldaD * 8, A, (size_t)LDA * 8, (size_t)M * 8, K, cudaMemcpyHostToDevice, c.s_h2d));
-    for (int p = 0; p < npanels; p++) {
-      const int n0 = p * panel, nb = std::min(panel, N - n0);
-      if (need_ab)
-        CU_TRY(cudaMemcpy2DAsync(c.b.p + (size_t)n0 * ldbD, ldbD * 8, B + (size_t)n0 * LDB, (size_t)LDB * 8,
-                                 (size_t)K * 8, nb, cudaMemcpyHostToDevice, c.s_h2d));
-      if (need_c_in)
+    for (size_t i = 0; i < order.size(); i++) {
+      const int sI = order[i].s, pI = order[i].p;
+      const int n0 = nb[pI], ncol = nb[pI + 1] - nb[pI];
+      const int k0 = kb[sI], kc = need_ab ? kb[sI + 1] - kb[sI] : K;
+      if (need_ab && !a_sent[sI]) {
+        CU_TRY(cudaMemcpy2DAsync(c.a.p + (size_t)k0 * ldaD, ldaD * 8, A + (size_t)k0 * LDA, (size_t)LDA * 8,
+                                 (size_t)M * 8, kc, cudaMemcpyHostToDevice, c.s_h2d));
+        a_sent[sI] = 1;
+      }
+      if (need_c_in && !first_done[pI])
         CU_TRY(cudaMemcpy2DAsync(c.c.p + (size_t)n0 * ldcD, ldcD * 8, C + (size_t)n0 * LDC, (size_t)LDC * 8,
-                                 (size_t)M * 8, nb, cudaMemcpyHostToDevice, c.s_h2d));
-      CU_TRY(cudaEventRecord(ev_in[p], c.s_h2d));
-      CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[p], 0));
-      int s2 = run_device(c, M, nb, K, alpha, c.a.p, ldaD, c.b.p + (size_t)n0 * ldbD, ldbD, beta,
-                          c.c.p + (size_t)n0 * ldcD, ldcD, c.s_compute, dg::VARIANT_AUTO, 0);
+                                 (size_t)M * 8, ncol, cudaMemcpyHostToDevice, c.s_h2d));
+      if (need_ab)
+        CU_TRY(cudaMemcpy2DAsync(c.b.p + (size_t)n0 * ldbD + k0, ldbD * 8, B + (size_t)n0 * LDB + k0, (size_t)LDB * 8,
+                                 (size_t)kc * 8, ncol, cudaMemcpyHostToDevice, c.s_h2d));
+      CU_TRY(cudaEventRecord(ev_in[i], c.s_h2d));
+      CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[i], 0));
+      int s2 = run_device(c, M, ncol, kc, alpha, c.a.p + (size_t)k0 * ldaD, ldaD, c.b.p + (size_t)n0 * ldbD + k0, ldbD,
+                          first_done[pI] ? 1.0 : beta, c.c.p + (size_t)n0 * ldcD, ldcD, c.s_compute, dg::VARIANT_AUTO, 0);
       if (s2) return s2;
-      CU_TRY(cudaEventRecord(ev_done[p], c.s_compute));
-      CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done[p], 0));
-      CU_TRY(cudaMemcpy2DAsync(C + (size_t)n0 * LDC, (size_t)LDC * 8, c.c.p + (size_t)n0 * ldcD, ldcD * 8,
-                               (size_t)M * 8, nb, cudaMemcpyDeviceToHost, c.s_d2h));
+      first_done[pI] = 1;
+      if (sI == last_slab[pI]) {
+        CU_TRY(cudaEventRecord(ev_done[pI], c.s_compute));
+        CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done[pI], 0));
+        CU_TRY(cudaMemcpy2DAsync(C + (size_t)n0 * LDC, (size_t)LDC * 8, c.c.p + (size_t)n0 * ldcD, ldcD * 8,
+                                 (size_t)M * 8, ncol, cudaMemcpyDeviceToHost, c.s_d2h));
+      }
     }
     CU_TRY(cudaStreamSynchronize(c.s_d2h));
     CU_TRY(cudaStreamSynchronize(c.s_compute));
@@ -341,10 +374,8 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
     return DGEMM_B200_OK;
   };
   result = body();
-  for (int p = 0; p < npanels; p++) {
-    cudaEventDestroy(ev_in[p]);
-    cudaEventDestroy(ev_done[p]);
-  }
+  for (auto e : ev_in) cudaEventDestroy(e);
+  for (auto e : ev_done) cudaEventDestroy(e);
   return result ? result : ok();
 }
 
@@ -613,6 +644,11 @@ double dgemm_b200_time_device(int M, int N, int K, double alpha, const double* d
     return -1.0;
   }
   return total_ms / std::max(1, reps);
+}
+
+int dgemm_b200_debug_timeline(unsigned long long* dbuf) {
+  g_timeline = dbuf;
+  return DGEMM_B200_OK;
 }
 
 int dgemm_b200_launch_count(void) { return dg::launch_count(); }

@@ -64,7 +64,18 @@ struct Params {
   const void* fetch_src;
   void* fetch_dst;
   unsigned long long fetch_bytes;
+  // ---- optional per-CTA timeline (debug / profiling aid; nullptr in normal use): 16 globaltimer stamps per CTA
+  unsigned long long* timeline;
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void stamp(const Params& P, int slot) {
+  if (P.timeline && slot < 16) P.timeline[blockIdx.x * 16 + slot] = globaltimer_ns();
+}
 
 // ---- lane -> matrix index maps (see header comment) -------------------------------------------------------
 // row fragment (from B): mma row r = lane/4 feeds n = 8*t + kPermN(r)
@@ -111,6 +122,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "DONE_%=:\n\t"
       "}" ::"r"(bar), "r"(parity)
       : "memory");
+}
+// Non-blocking probe: 1 when the phase with this parity has completed.  Issued a whole stage ahead of its use, so
+// its latency (~100+ clk) hides behind DMMAs instead of stalling both warps of a sub-partition at every stage edge.
+__device__ __forceinline__ uint32_t mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done;
 }
 // TMA: 2-D tiled load global -> shared, completion counted on an mbarrier.  SASS: UTMALDG.2D
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1) {
@@ -211,12 +237,42 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
   const int mq = map_m(2 * q);  // 0, 8, 2, 10
   const double alpha = P.alpha, beta = P.beta;
   const bool use_c = beta != 0.0;
+  const int mbase = m0 + warp_m * WM + mq;
+  // Fast path (warp tile fully inside C, 16-byte aligned columns): straight-line code, 16 independent 16-byte loads
+  // in flight per lane before the first use.  The predicated edge path below puts every load in its own basic
+  // block, which serialises the round trips (measured: ~9 us per tile instead of ~2).
+  const bool interior = P.c_vec2 && (m0 + warp_m * WM + WM <= P.M) && (n0 + warp_n * WN + WN <= P.N);
+  if (interior) {
+#pragma unroll
+    for (int ip = 0; ip < FRAG_N; ip += 2) {
+      double* col0 = P.C + (long long)(n0 + warp_n * WN + ip * 8 + perm_n(r)) * P.ldc + mbase;
+      double* col1 = col0 + 8 * P.ldc;
+      double2 c[2][FRAG_M];
+      if (use_c) {
+#pragma unroll
+        for (int j = 0; j < FRAG_M; j++) {
+          c[0][j] = *reinterpret_cast<const double2*>(col0 + (j >> 1) * 16 + (j & 1) * 4);
+          c[1][j] = *reinterpret_cast<const double2*>(col1 + (j >> 1) * 16 + (j & 1) * 4);
+        }
+      }
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        double* col = h ? col1 : col0;
+#pragma unroll
+        for (int j = 0; j < FRAG_M; j++) {
+          double v0 = alpha * acc[ip + h][j][0], v1 = alpha * acc[ip + h][j][1];
+          if (use_c) { v0 = fma(beta, c[h][j].x, v0); v1 = fma(beta, c[h][j].y, v1); }
+          *reinterpret_cast<double2*>(col + (j >> 1) * 16 + (j & 1) * 4) = make_double2(v0, v1);
+        }
+      }
+    }
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < FRAG_N; i++) {
     const int n = n0 + warp_n * WN + i * 8 + perm_n(r);
     if (n >= P.N) continue;
     double* col = P.C + (long long)n * P.ldc;
-    const int mbase = m0 + warp_m * WM + mq;
     double c0[FRAG_M], c1[FRAG_M];
     if (use_c) {
 #pragma unroll

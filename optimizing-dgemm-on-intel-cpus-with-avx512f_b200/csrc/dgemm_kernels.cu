@@ -83,8 +83,10 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // 1024-byte alignment is required by SWIZZLE_128B; dynamic smem base is only guaranteed 16 B -> round up
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = smem_base + STAGES * STAGE_BYTES;  // full[STAGES] then empty[STAGES], 8 B each
+  const uint32_t progress = bars + 16 * STAGES;            // segments the producer has started (paces the C prefetch)
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) stamp(P, 0);
 
   if (tid == 0) {
 #pragma unroll
@@ -92,6 +94,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(bars + 8 * s, 1);                          // full: one arrive (the producer's expect_tx)
       mbar_init(bars + 8 * (STAGES + s), CONSUMER_WARPS);  // empty: one arrive per consumer warp
     }
+    asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(progress), "r"(0u) : "memory");
     fence_mbar_init();
   }
   __syncthreads();
@@ -105,10 +108,12 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t s = 0, ph = 0;
       SegmentWalker walk(P, num_units);
       Segment sg;
+      uint32_t seg_idx = 0;
       while (walk.next(P, sg)) {
         int tm, tn;
         decode_tile(P, sg.tile, tm, tn);
         const int m0 = tm * BM, n0 = tn * BN;
+        asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(progress), "r"(++seg_idx) : "memory");
         for (int kt = sg.kb; kt < sg.ke; kt++) {
           mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
           const uint32_t full = bars + 8 * s;
@@ -122,16 +127,43 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
-    } else if (warp > CONSUMER_WARPS && P.fetch_bytes) {
-      // ---------------- fetch warps (9..11): NVLink pull of the NEXT K-slab of A, overlapped with the math ----------
+    } else if (warp == CONSUMER_WARPS + 1) {
+      // ---------------- warp 9: pull the C tile of every segment that ends in an epilogue into L2 -------------------
+      // Without it all CTAs hit their epilogue together and read 148 x 128 KB of C from DRAM in four dependent
+      // rounds (~9 us per tile, measured with the timeline stamps); prefetched, the rounds are L2 hits.  Paced by
+      // the producer's segment counter so the prefetch runs during the main loop of the same tile, never far ahead.
+      if (P.beta != 0.0) {
+        SegmentWalker walk(P, num_units);
+        Segment sg;
+        uint32_t seg_idx = 0;
+        while (walk.next(P, sg)) {
+          ++seg_idx;
+          if (sg.kind != SEG_DIRECT && sg.kind != SEG_SK_OWNER) continue;
+          uint32_t seen;
+          do {
+            asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(seen) : "r"(progress) : "memory");
+            if (seen < seg_idx) __nanosleep(256);
+          } while (seen < seg_idx);
+          int tm, tn;
+          decode_tile(P, sg.tile, tm, tn);
+          const int m0 = tm * BM, n0 = tn * BN;
+          for (int i = lane; i < BN * (BM / 16); i += 32) {   // one 128-byte line (16 doubles) per prefetch
+            const int n = n0 + (i >> 3), m = m0 + ((i & 7) << 4);
+            if (n < P.N && m < P.M)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(P.C + (long long)n * P.ldc + m));
+          }
+        }
+      }
+    } else if (warp > CONSUMER_WARPS + 1 && P.fetch_bytes) {
+      // ---------------- fetch warps (10, 11): NVLink pull of the NEXT K-slab of A, overlapped with the math ---------
       // every CTA copies one contiguous 1/gridDim.x share; 4 x 16 B per lane in flight
-      constexpr int FETCH_THREADS = 96, UNROLL = 4;
+      constexpr int FETCH_THREADS = 64, UNROLL = 4;
       const unsigned long long n16 = P.fetch_bytes >> 4;
       const unsigned long long per = (n16 + gridDim.x - 1) / gridDim.x;
       const unsigned long long beg = per * blockIdx.x, end = beg + per < n16 ? beg + per : n16;
       const int4* src = reinterpret_cast<const int4*>(P.fetch_src);
       int4* dst = reinterpret_cast<int4*>(P.fetch_dst);
-      const int t = tid - (CONSUMER_THREADS + 32);
+      const int t = tid - (CONSUMER_THREADS + 64);
       unsigned long long i = beg + t;
       for (; i + (UNROLL - 1) * FETCH_THREADS < end; i += UNROLL * FETCH_THREADS) {
         int4 v[UNROLL];
@@ -152,25 +184,32 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t s = 0, ph = 0;
     SegmentWalker walk(P, num_units);
     Segment sg;
+    int tslot = 1;
+    if (tid == 0) stamp(P, tslot++);
     while (walk.next(P, sg)) {
       zero_acc(acc);
       if (sg.kb < sg.ke) {
         // software pipeline over k-steps: the fragments of step i+1 are loaded while the 32 DMMAs of step i issue,
         // INCLUDING across the stage boundary (wait on the next stage's barrier before the last DMMA group)
         mbar_wait(bars + 8 * s, ph);
+        if (tid == 0) stamp(P, tslot++);   // first operands of the segment have landed
         load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
         for (int kt = sg.kb; kt < sg.ke; kt++) {
           const uint32_t sA = smem_base + s * STAGE_BYTES, sB = sA + A_STAGE_BYTES;
           const uint32_t cur_empty = bars + 8 * (STAGES + s);
+          if (++s == STAGES) { s = 0; ph ^= 1; }
+          const bool has_next = kt + 1 < sg.ke;
           load_frags(f1, sA, sB, lo, 1);
           mma_frags(acc, f0);
           load_frags(f0, sA, sB, lo, 2);
           mma_frags(acc, f1);
           load_frags(f1, sA, sB, lo, 3);
+          // probe the NEXT stage's barrier AFTER this stage's last loads (its acquire would hold them back) and
+          // consume the answer one DMMA group (32 x 16 clk) later
+          const uint32_t next_ready = has_next ? mbar_test_wait(bars + 8 * s, ph) : 0u;
           mma_frags(acc, f0);
-          if (++s == STAGES) { s = 0; ph ^= 1; }
-          if (kt + 1 < sg.ke) {
-            mbar_wait(bars + 8 * s, ph);  // TMA bytes of the next stage have landed (normally long ago)
+          if (has_next) {
+            if (!next_ready) mbar_wait(bars + 8 * s, ph);  // rare: the producer normally runs stages ahead
             load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
           }
           mma_frags(acc, f1);  // consumes the last fragments read from the current stage ...
@@ -180,6 +219,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       int tm, tn;
       decode_tile(P, sg.tile, tm, tn);
+      if (tid == 0) stamp(P, tslot++);     // main loop of the segment done
       if (sg.kind == SEG_DIRECT) {
         epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       } else if (sg.kind == SEG_SPLITK) {
@@ -200,6 +240,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       }
+      if (tid == 0) stamp(P, tslot++);     // epilogue / partial store / fix-up of the segment done
     }
   }
 }
@@ -382,7 +423,7 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     CUtensorMap tmA, tmB;
     if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN))
       return cudaErrorInvalidValue;
-    const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 1024;
+    const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
     static bool attr_done[64] = {};  // function attributes are per device
     int dev = 0;
     if ((err = cudaGetDevice(&dev)) != cudaSuccess) return err;

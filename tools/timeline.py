@@ -1,0 +1,33 @@
+"""Per-CTA phase timeline of one dgemm_tma_ws_kernel launch (dgemm_b200_debug_timeline):
+    python tools/timeline.py M N K [splits]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import dgemm_b200 as dg
+M, N, K = (int(x) for x in sys.argv[1:4])
+splits = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+dA, dB, dC = dg.malloc(8 * M * K), dg.malloc(8 * K * N), dg.malloc(8 * M * N)
+dg.fill_signed(dA, M, K, M, 1); dg.fill_signed(dB, K, N, K, 2); dg.fill_signed(dC, M, N, M, 3)
+tl = dg.malloc(8 * 148 * 16)
+host = np.zeros((148, 16), dtype=np.uint64)
+for rep in range(3):
+    dg.lib.dgemm_b200_h2d(tl, 148 * 16, host.ctypes.data, 148 * 16, 148 * 16, 1, None)
+    dg.lib.dgemm_b200_sync(None)
+    dg.lib.dgemm_b200_debug_timeline(tl)
+    dg.dgemm_device(M, N, K, 1.0, dA, M, dB, K, 1.0, dC, M, 0, 1, splits)
+    dg.lib.dgemm_b200_sync(None)
+    dg.lib.dgemm_b200_debug_timeline(None)
+out = np.zeros((148, 16), dtype=np.uint64)
+dg.lib.dgemm_b200_d2h(out.ctypes.data, 148 * 16, tl, 148 * 16, 148 * 16, 1, None)
+dg.lib.dgemm_b200_sync(None)
+act = out[out[:, 0] > 0]
+t0 = act[:, 0].min()
+rel = (act.astype(np.int64) - np.int64(t0)) / 1e3
+rel[act == 0] = np.nan
+print("plan", dg.plan(M, N, K, dA, M, dB, K), "ctas", len(act))
+names = ["entry", "cons.start"] + [f"seg{i//3}.{['landed','loop','epi'][i%3]}" for i in range(14)]
+for j in range(16):
+    col = rel[:, j]
+    if np.all(np.isnan(col)): continue
+    print(f"{names[j]:12s} min {np.nanmin(col):8.2f}  median {np.nanmedian(col):8.2f}  max {np.nanmax(col):8.2f} us  (n={np.sum(~np.isnan(col))})")
+print("kernel span (first entry -> last stamp): %.2f us" % np.nanmax(rel))
