@@ -160,9 +160,10 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
 // plus one full wave ("two-tile" stream-K) is cut into equal (tile, k-tile) ranges, one per CTA, so every SM gets
 // the same number of k-tiles.  When there are fewer tiles than SMs the whole problem is stream-K (this is what
 // split-K was for: M=N=512, K=16384 has 16 tiles for 148 SMs).
+static int SK_MIN_ITERS = getenv("DGEMM_B200_SK_MIN_ITERS") ? atoi(getenv("DGEMM_B200_SK_MIN_ITERS")) : 4;
 void plan_stream_k(dg::Params& P, int num_sms) {
   const int tiles = P.tiles_m * P.tiles_n;
-  P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0;
+  P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0;
   if (P.k_tiles < 8) return;
   const int full_waves = tiles / num_sms, rem = tiles % num_sms;
   if (rem == 0) return;
@@ -171,10 +172,12 @@ void plan_stream_k(dg::Params& P, int num_sms) {
     P.sk_grid = num_sms;
   } else {
     const long long iters = (long long)tiles * P.k_tiles;
-    const int g = (int)std::min<long long>(num_sms, iters / 8);  // at least 8 k-tiles (128 k) per CTA
+    const int g = (int)std::min<long long>(num_sms, iters / SK_MIN_ITERS);  // at least SK_MIN_ITERS k-tiles per CTA
     if (g <= tiles) return;                                       // nothing to gain: one CTA per tile
     P.sk_tiles = tiles;
     P.sk_grid = g;
+    // >= 3 ranges per tile on average: reduce the partials in parallel instead of serially in the tile's owner
+    P.sk_parallel = (long long)g * 1 >= 3ll * tiles ? 1 : 0;
   }
   P.sk_tile0 = tiles - P.sk_tiles;
 }
@@ -188,7 +191,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   P.tiles_n = (N + dg::BN - 1) / dg::BN;
   P.k_tiles = (K + dg::BK - 1) / dg::BK;
   const int tiles = P.tiles_m * P.tiles_n;
-  P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
+  P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
   P.fetch_src = nullptr; P.fetch_dst = nullptr; P.fetch_bytes = 0;
   P.timeline = g_timeline;
   // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
@@ -247,7 +250,8 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   if (uses_ws) {
-    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits : (size_t)P.sk_grid;
+    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits
+                                      : (size_t)P.sk_grid * (P.sk_parallel ? 2 : 1);
     const size_t need = slots * dg::BM * dg::BN * sizeof(double);
     if (c.ws.cap < need) {
       int st = grow(c.ws, need);
@@ -307,11 +311,12 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   // (first use), C panel p (only when s == 0) and the B block (s,p).  After the first two diagonals the H2D stream
   // stays ahead of the math (per diagonal ~ one A slab + one C panel + d B blocks vs d kernels), so only a few
   // hundred MB are exposed before the first kernel instead of all of A.  C panel p goes back as soon as its last
-  // slab is done.  Each call is >= ~2 ms of work so the stream-K tails stay cheap.
+  // slab is done.  Below ~8000^3 the call is PCIe-bound (24 n^2 bytes in vs 2 n^3 flops), so the pieces are kept small (>= ~60 us of
+  // math each, at most 8 x 8) to hide compute and D2H behind the H2D stream.
   int P = 1, S = 1;
   if (need_ab) {
     const double flops = 2.0 * M * (double)N * K;
-    const int want = (int)std::max(1.0, std::min(64.0, flops / 72e9));
+    const int want = (int)std::max(1.0, std::min(64.0, flops / 2e9));  // pieces of >= ~60 us of math, at most 8 x 8
     P = std::max(1, std::min({(int)std::lround(std::sqrt((double)want)), N / 256, 8}));
     S = std::max(1, std::min({want / P, K / 512, 8}));
   }
@@ -352,7 +357,7 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
       if (need_c_in && !first_done[pI])
         CU_TRY(cudaMemcpy2DAsync(c.c.p + (size_t)n0 * ldcD, ldcD * 8, C + (size_t)n0 * LDC, (size_t)LDC * 8,
                                  (size_t)M * 8, ncol, cudaMemcpyHostToDevice, c.s_h2d));
-      if (need_ab)
+      if (need_ab)  // B block (s,p); sending whole B panels at s == 0 front-loads the stream (measured 6 % slower)
         CU_TRY(cudaMemcpy2DAsync(c.b.p + (size_t)n0 * ldbD + k0, ldbD * 8, B + (size_t)n0 * LDB + k0, (size_t)LDB * 8,
                                  (size_t)kc * 8, ncol, cudaMemcpyHostToDevice, c.s_h2d));
       CU_TRY(cudaEventRecord(ev_in[i], c.s_h2d));

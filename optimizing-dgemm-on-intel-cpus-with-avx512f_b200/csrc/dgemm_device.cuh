@@ -56,6 +56,9 @@ struct Params {
   // ranges of (tile, k-tile) iterations instead of whole tiles
   int sk_tile0, sk_tiles;
   int sk_grid;                // CTAs launched when sk_tiles > 0 (every one of them must be co-resident)
+  int sk_parallel;            // 1: parallel fix-up (all-stream-K mode, many ranges per tile): every range stores its
+                              // partial (2 slots per range: head / tail) and each participant of a tile reduces a
+                              // 1/R slice of it; 0: the tile's owner adds the other ranges' partials serially
   unsigned int sk_epoch;      // flag value that means "partial of this launch is in the workspace"
   unsigned int* sk_flags;     // one flag per CTA range
   // ---- fused NVLink fetch (TMA kernel only): while the DMMA warps work on this call's K-slab, the three spare
@@ -300,6 +303,33 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
         if (m + 1 < P.M) col[m + 1] = v1;
       }
     }
+  }
+}
+
+// Epilogue for ONE fragment (i, j) of the lane: used by the parallel stream-K fix-up, where a CTA finishes only a
+// slice of the tile.  Fully predicated (edges, unaligned C).
+__device__ __forceinline__ void epilogue_frag(double a0, double a1, const Params& P, int m0, int n0, int warp_m,
+                                              int warp_n, int lane, int i, int j) {
+  const int r = lane >> 2, q = lane & 3;
+  const int n = n0 + warp_n * WN + i * 8 + perm_n(r);
+  const int m = m0 + warp_m * WM + map_m(2 * q) + (j >> 1) * 16 + (j & 1) * 4;
+  if (n >= P.N || m >= P.M) return;
+  double* p = P.C + (long long)n * P.ldc + m;
+  double v0 = P.alpha * a0, v1 = P.alpha * a1;
+  const bool two = m + 1 < P.M;
+  if (P.c_vec2 && two) {
+    if (P.beta != 0.0) {
+      const double2 c = *reinterpret_cast<const double2*>(p);
+      v0 = fma(P.beta, c.x, v0); v1 = fma(P.beta, c.y, v1);
+    }
+    *reinterpret_cast<double2*>(p) = make_double2(v0, v1);
+  } else {
+    if (P.beta != 0.0) {
+      v0 = fma(P.beta, p[0], v0);
+      if (two) v1 = fma(P.beta, p[1], v1);
+    }
+    p[0] = v0;
+    if (two) p[1] = v1;
   }
 }
 

@@ -186,6 +186,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     Segment sg;
     int tslot = 1;
     if (tid == 0) stamp(P, tslot++);
+    int fix_tile[2] = {-1, -1};  // parallel fix-up: tiles this range holds a partial of (head, tail)
     while (walk.next(P, sg)) {
       zero_acc(acc);
       if (sg.kb < sg.ke) {
@@ -224,6 +225,14 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       } else if (sg.kind == SEG_SPLITK) {
         store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
+      } else if (P.sk_parallel) {
+        // parallel fix-up, phase A: every partial goes to the workspace (slot 2r = head, 2r+1 = tail of range r)
+        const int slot = 2 * sg.slot + (sg.kind == SEG_SK_OWNER ? 1 : 0);
+        store_partial(acc, P.workspace + (size_t)slot * (BM * BN), tid);
+        __threadfence();
+        consumer_bar_sync();
+        if (tid == 0) st_release_gpu(P.sk_flags + slot, P.sk_epoch);
+        fix_tile[sg.kind == SEG_SK_OWNER ? 1 : 0] = sg.tile;
       } else if (sg.kind == SEG_SK_CONTRIB) {
         store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
         __threadfence();
@@ -241,6 +250,82 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       }
       if (tid == 0) stamp(P, tslot++);     // epilogue / partial store / fix-up of the segment done
+    }
+    if (P.sk_parallel) {
+      // parallel fix-up, phase B: the R ranges that hold a piece of a tile each reduce fragments q = s, s+R, ... of it
+      // over all R partials (ascending range order -> deterministic) and finish those fragments.
+      const int G = gridDim.x, rid = G - 1 - (int)blockIdx.x;
+      const long long total = (long long)P.sk_tiles * P.k_tiles;
+      auto range_of = [&](long long x) {
+        int r = (int)(x * G / total);
+        while (r + 1 < G && total * (r + 1) / G <= x) r++;
+        while (r > 0 && total * r / G > x) r--;
+        return r;
+      };
+#pragma unroll 1
+      for (int h = 0; h < 2; h++) {
+        if (fix_tile[h] < 0) continue;
+        const long long x0 = (long long)(fix_tile[h] - P.sk_tile0) * P.k_tiles;
+        const int r_first = range_of(x0), r_last = range_of(x0 + P.k_tiles - 1);
+        const int R = r_last - r_first + 1, me = rid - r_first;
+        if (tid < R) {
+          const int r = r_first + tid;
+          const unsigned int* f = P.sk_flags + 2 * r + (r == r_first ? 1 : 0);
+          while (ld_acquire_gpu(f) != P.sk_epoch) __nanosleep(64);
+        }
+        consumer_bar_sync();
+        int tm, tn;
+        decode_tile(P, fix_tile[h], tm, tn);
+        // four fragments per pass so that 4 partial loads per range and 4 C loads are in flight together
+        const bool interior = P.c_vec2 && (tm * BM + BM <= P.M) && (tn * BN + BN <= P.N);
+        const int lr = lane >> 2, lq = lane & 3;
+#pragma unroll 1
+        for (int q0 = me; q0 < FRAG_N * FRAG_M; q0 += 4 * R) {
+          double s0[4] = {0.0, 0.0, 0.0, 0.0}, s1[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 4
+          for (int r = r_first; r <= r_last; r++) {
+            const int slot = 2 * r + (r == r_first ? 1 : 0);
+            const double2* base = reinterpret_cast<const double2*>(P.workspace + (size_t)slot * (BM * BN)) + tid;
+            double2 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              const int q = min(q0 + u * R, FRAG_N * FRAG_M - 1);  // clamped: the extra value is discarded below
+              v[u] = __ldcg(base + q * CONSUMER_THREADS);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) { s0[u] += v[u].x; s1[u] += v[u].y; }
+          }
+          if (interior) {
+            double* p[4];
+            double2 c[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              const int q = min(q0 + u * R, FRAG_N * FRAG_M - 1), i = q / FRAG_M, j = q % FRAG_M;
+              p[u] = P.C + (long long)(tn * BN + warp_n * WN + i * 8 + perm_n(lr)) * P.ldc + tm * BM + warp_m * WM +
+                     map_m(2 * lq) + (j >> 1) * 16 + (j & 1) * 4;
+              c[u] = make_double2(0.0, 0.0);
+            }
+            if (P.beta != 0.0) {
+#pragma unroll
+              for (int u = 0; u < 4; u++) c[u] = *reinterpret_cast<const double2*>(p[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              if (q0 + u * R < FRAG_N * FRAG_M)
+                *reinterpret_cast<double2*>(p[u]) =
+                    make_double2(fma(P.beta, c[u].x, P.alpha * s0[u]), fma(P.beta, c[u].y, P.alpha * s1[u]));
+            }
+          } else {
+#pragma unroll 1
+            for (int u = 0; u < 4; u++) {
+              const int q = q0 + u * R;
+              if (q < FRAG_N * FRAG_M)
+                epilogue_frag(s0[u], s1[u], P, tm * BM, tn * BN, warp_m, warp_n, lane, q / FRAG_M, q % FRAG_M);
+            }
+          }
+        }
+      }
+      if (tid == 0) stamp(P, 15);
     }
   }
 }
