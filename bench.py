@@ -299,6 +299,21 @@ def main():
     barrier()
     launches = dg.launch_count()
     clocks = sampler.stop() if rank == 0 else None
+    # spot check of the timed path: after n passes with alpha = beta = 1, C = C0 + n * A*B exactly up to rounding
+    import numpy as np
+    n_pass = warmup + steps
+    rng = np.random.default_rng(99 + rank)
+    idx = [(int(rng.integers(M)), int(rng.integers(ncols))) for _ in range(3)] + [(M - 1, ncols - 1)]
+    got = [float(Cm[j * M + i].item()) for i, j in idx]
+    c0 = [float(gen_signed(3, np.array([i]), np.array([n0 + j]))[0]) for i, j in idx]
+    # n passes of (C <- A*B + C): same as one pass with alpha = n on the original C (the bound scales with alpha)
+    value_check = spot_check(c0, got, idx, M, K, n0, float(n_pass), 1.0)
+    if N > 1:
+        vc = torch.tensor([value_check], dtype=torch.float64, device=dev)
+        dist.all_reduce(vc, op=dist.ReduceOp.MAX)
+        value_check = float(vc.item())
+    if not value_check <= 1.0:
+        raise SystemExit(f"bench.py: timed result is WRONG: max |err|/bound = {value_check}")
     total_ms = ev[0].elapsed_time(ev[steps])
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
     if N > 1:
@@ -315,7 +330,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         e2e = run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm,
-                      max(2, min(steps, 5)), fused, step)
+                      max(2, min(steps, 5)), fused, step, ctx["peers"])
 
     if rank != 0:
         if N > 1:
@@ -368,12 +383,43 @@ def main():
                    "timing": "CUDA events on the launching stream, max over ranks"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "cublas_ceiling": cublas,
+        "spot_check_max_err_over_bound": value_check,
         "pct_of_fp64_peak": 100.0 * value / (N * peak),
     }
     print(json.dumps(line), flush=True)
     if N > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def gen_signed(seed, rows, cols):
+    """numpy copy of the counter-based input generator (dgemm_b200_fill_signed): entry (i, j) = f(seed, i, j).
+    rows / cols are integer arrays of equal length; returns float64 values.  Used only to spot-check bench results."""
+    import numpy as np
+    with np.errstate(over="ignore"):
+        x = np.uint64(seed) * np.uint64(0xD1342543DE82EF95) + (rows.astype(np.uint64) + (cols.astype(np.uint64) << np.uint64(32)))
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    return (x >> np.uint64(11)).astype(np.int64).astype(np.float64) * (1.0 / 4503599627370496.0) - 1.0
+
+
+def spot_check(before, after, idx, M, K, n0, alpha, beta):
+    """after[i,j] must equal alpha * A[i,:].B[:,j] + beta * before[i,j] within the north-star bound; A and B rows /
+    columns are regenerated on the host from the counter-based generator.  Returns max |err| / bound."""
+    import numpy as np
+    worst = 0.0
+    kk = np.arange(K, dtype=np.int64)
+    for (i, j), b, a in zip(idx, before, after):
+        arow = gen_signed(1, np.full(K, i, dtype=np.int64), kk).astype(np.longdouble)
+        bcol = gen_signed(2, kk, np.full(K, n0 + j, dtype=np.int64)).astype(np.longdouble)
+        dot = float(np.sum(arow * bcol))
+        mag = float(np.sum(np.abs(arow * bcol)))
+        want = alpha * dot + beta * b
+        bound = 2.0 * K * 2.220446049250313e-16 * (abs(alpha) * mag + abs(beta * b))
+        worst = max(worst, abs(a - want) / bound)
+    return worst
 
 
 def load_profile_json(rel):
@@ -402,7 +448,7 @@ def cublas_ceiling(torch, A, B, Cm, M, Nn, K):
     return {"tflops": 2.0 * M * Nn * K / ms / 1e9, "ms": ms, "note": "torch.matmul(float64) -> cublasDgemm; ceiling only"}
 
 
-def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm, reps, fused, step):
+def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm, reps, fused, step, peers):
     """Same metric through the public host-pointer API with HOST (pinned) buffers, copies inside the timed region.
     N = 1: mydgemm_gpu_v20 (the reference's 11-argument signature).  N > 1: each rank stages its own K-slab of A and
     its B/C panels from pinned memory, runs the sharded step (A exchanged over NVLink), copies its C panel back."""
@@ -423,10 +469,7 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
     sptr = stream.cuda_stream
     token = torch.zeros(1, device=dev)
 
-    def one():
-        if N == 1:
-            dg.mydgemm_gpu_v20(M, Nn, K, alpha, hA.data_ptr(), M, hB.data_ptr(), K, beta, hC.data_ptr(), M)
-            return
+    def one_simple():
         dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, sptr))
         dist.all_reduce(token)  # stream-ordered barrier: every owner's K-slab is in its HBM before anyone pulls it
         dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr(), K, hB.data_ptr(), K, K, ncols, sptr))
@@ -436,7 +479,75 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
         dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr(), M, Cm.data_ptr(), M, M, ncols, sptr))
         stream.synchronize()
 
+    copy_s, d2h_s = torch.cuda.Stream(), torch.cuda.Stream()
+    from dgemm_b200.sharding import partition, slab_order
+    SP = 4 if ncols >= 4 * 256 else 1
+    sp = partition(ncols, SP, 128)
+    order = [g for g in slab_order(rank, N) if kb[g + 1] > kb[g]] if N > 1 else []
+
+    def one_pipelined():
+        """Rank-local 2-D pipeline: (K-slab, column sub-panel) calls in slab-major order on the compute stream; H2D of
+        the own A slab, the C sub-panels and the B blocks queued in need-order on a copy stream; every C sub-panel
+        goes back on a third stream as soon as its last slab is done.  The NVLink pull of slab i+1 rides on the first
+        call of slab i."""
+        cptr = copy_s.cuda_stream
+        copy_s.wait_stream(stream)
+        dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, cptr))
+        ev_a = copy_s.record_event()
+        ev_c, ev_b = [], {}
+        for j in range(SP):
+            c0, nc = sp[j], sp[j + 1] - sp[j]
+            dg._check(dg.lib.dgemm_b200_h2d(Cm.data_ptr() + 8 * c0 * M, M, hC.data_ptr() + 8 * c0 * M, M, M, nc, cptr))
+            ev_c.append(copy_s.record_event())
+        for i, g in enumerate(order):
+            for j in range(SP):
+                c0, nc = sp[j], sp[j + 1] - sp[j]
+                off = 8 * (c0 * K + kb[g])
+                dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr() + off, K, hB.data_ptr() + off, K, kb[g + 1] - kb[g], nc, cptr))
+                ev_b[(i, j)] = copy_s.record_event()
+        stream.wait_event(ev_a)
+        dist.all_reduce(token)  # every owner's K-slab is in its HBM before anyone pulls it
+        for i, g in enumerate(order):
+            kc = kb[g + 1] - kb[g]
+            for j in range(SP):
+                c0, nc = sp[j], sp[j + 1] - sp[j]
+                if nc <= 0:
+                    continue
+                stream.wait_event(ev_b[(i, j)])
+                if i == 0:
+                    stream.wait_event(ev_c[j])
+                src = dst = nbytes = 0
+                if j == 0 and i + 1 < len(order):
+                    nx = order[i + 1]
+                    src, dst = peers[nx] + 8 * kb[nx] * M, A_ptr + 8 * kb[nx] * M
+                    nbytes = 8 * (kb[nx + 1] - kb[nx]) * M
+                dg.dgemm_device_fetch(M, nc, kc, alpha, A_ptr + 8 * kb[g] * M, M, B.data_ptr() + 8 * (c0 * K + kb[g]), K,
+                                      beta if i == 0 else 1.0, Cm.data_ptr() + 8 * c0 * M, M, sptr, src, dst, nbytes)
+                if i == len(order) - 1:
+                    d2h_s.wait_event(stream.record_event())
+                    dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr() + 8 * c0 * M, M, Cm.data_ptr() + 8 * c0 * M, M, M, nc,
+                                                    d2h_s.cuda_stream))
+        dist.all_reduce(token)  # nobody still reads a slab when its owner overwrites it in the next pass
+        d2h_s.synchronize()
+        stream.synchronize()
+
+    def one():
+        if N == 1:
+            dg.mydgemm_gpu_v20(M, Nn, K, alpha, hA.data_ptr(), M, hB.data_ptr(), K, beta, hC.data_ptr(), M)
+        elif fused and os.environ.get("BENCH_E2E_SIMPLE") != "1":
+            one_pipelined()
+        else:
+            one_simple()
+
     one()  # warm-up (allocates the library's staging buffers)
+    # spot check of the end-to-end path itself: one more pass, a few entries recomputed on the host
+    import numpy as np
+    rng = np.random.default_rng(1234 + rank)
+    idx = [(int(rng.integers(M)), int(rng.integers(ncols))) for _ in range(6)] + [(M - 1, ncols - 1), (0, 0)]
+    before = [float(hC[j * M + i]) for i, j in idx]
+    one()
+    after = [float(hC[j * M + i]) for i, j in idx]
+    check = spot_check(before, after, idx, M, K, n0, alpha, beta)
     if N > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -452,11 +563,18 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
         b = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
         dist.all_reduce(b, op=dist.ReduceOp.SUM)
         h2d, d2h = int(b[0].item()), int(b[1].item())
-    return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "unit": UNIT, "h2d_bytes_per_step": h2d,
+        ck = torch.tensor([check], dtype=torch.float64, device=dev)
+        dist.all_reduce(ck, op=dist.ReduceOp.MAX)
+        check = float(ck.item())
+    if not check <= 1.0:
+        raise SystemExit(f"bench.py: end-to-end result is WRONG: max |err|/bound = {check}")
+    return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "spot_check_max_err_over_bound": check,
+            "spot_check": f"{len(idx)} entries per rank recomputed on the host in long double", "unit": UNIT, "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps,
             "api": "mydgemm_gpu_v20(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC) with pinned host pointers" if N == 1 else
                    "per rank: dgemm_b200_h2d (own K-slab of A, B/C panels) + sharded step ("
-                   + ("dgemm_b200_device_fetch, fused NVLink pull" if fused else "ncclBroadcast + dgemm_b200_device")
+                   + ("dgemm_b200_device_fetch, fused NVLink pull; (slab, sub-panel) calls pipelined against H2D/D2H "
+                      "on three streams" if fused else "ncclBroadcast + dgemm_b200_device")
                    + ") + dgemm_b200_d2h, pinned host buffers"}
 
 

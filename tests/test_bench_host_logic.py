@@ -33,3 +33,20 @@ def test_reference_arm_other_ranks_exit_quietly():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                        capture_output=True, text=True, env=env)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_bench_generator_matches_oracle_and_spot_check_catches_errors():
+    import numpy as np
+    import oracle_lib as ol
+    x = ol.fill_signed(7, 5, 7, 2, row0=3, col0=65530)
+    r, c = np.meshgrid(np.arange(3, 10), np.arange(65530, 65535), indexing="ij")
+    assert np.array_equal(x, bench.gen_signed(2, r.ravel(), c.ravel()).reshape(7, 5))
+    # spot_check: exact result passes, a 1e-9 relative error fails
+    M, N, K = 40, 24, 300
+    A = ol.fill_signed(M, K, M, 1); B = ol.fill_signed(K, N, K, 2, col0=128); C0 = ol.fill_signed(M, N, M, 3, col0=128)
+    C = C0.copy(order="F")
+    ol.oracle_k18(M, N, K, 1.0, A, B, 1.0, C)
+    idx = [(0, 0), (39, 23), (17, 5)]
+    before = [C0[i, j] for i, j in idx]; after = [C[i, j] for i, j in idx]
+    assert bench.spot_check(before, after, idx, M, K, 128, 1.0, 1.0) <= 1.0
+    assert bench.spot_check(before, [a * (1 + 1e-9) + 1e-9 for a in after], idx, M, K, 128, 1.0, 1.0) > 1.0
