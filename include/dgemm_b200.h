@@ -41,7 +41,9 @@ enum {
   DGEMM_B200_VARIANT_AUTO = 0,
   DGEMM_B200_VARIANT_TMA = 1,        /* TMA + mbarrier warp-specialised persistent kernel */
   DGEMM_B200_VARIANT_CPASYNC8 = 2,   /* cp.async 8-byte loader: any alignment / odd leading dimensions */
-  DGEMM_B200_VARIANT_CPASYNC16 = 3   /* cp.async 16-byte loader */
+  DGEMM_B200_VARIANT_CPASYNC16 = 3,  /* cp.async 16-byte loader */
+  DGEMM_B200_VARIANT_NAIVE = 4,      /* optimisation-ladder rung 1: one thread per entry (never auto-selected) */
+  DGEMM_B200_VARIANT_DFMA = 5        /* ladder rung 2: smem tiles + 8x8 register tile on the CUDA-core FP64 pipe */
 };
 
 /* ---- the reference's kernel signature (replaces mydgemm_cpu_v18 / v19 at utils.c:159-165) ---------------- */

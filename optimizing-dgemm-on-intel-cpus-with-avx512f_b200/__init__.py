@@ -22,9 +22,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libdgemm_b200.so")
 
 OK, ERR_NO_DEVICE, ERR_BAD_ARG, ERR_OOM, ERR_CUDA, ERR_NCCL = range(6)
-VARIANT_AUTO, VARIANT_TMA, VARIANT_CPASYNC8, VARIANT_CPASYNC16 = range(4)
+VARIANT_AUTO, VARIANT_TMA, VARIANT_CPASYNC8, VARIANT_CPASYNC16, VARIANT_NAIVE, VARIANT_DFMA = range(6)
 VARIANT_NAMES = {VARIANT_AUTO: "auto", VARIANT_TMA: "tma_ws", VARIANT_CPASYNC8: "cpasync8",
-                 VARIANT_CPASYNC16: "cpasync16"}
+                 VARIANT_CPASYNC16: "cpasync16", VARIANT_NAIVE: "naive", VARIANT_DFMA: "dfma_regtile"}
 
 # every symbol include/dgemm_b200.h declares (tests check the library exports all of them)
 EXPORTS = [

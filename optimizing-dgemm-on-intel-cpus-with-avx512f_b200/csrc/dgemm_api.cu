@@ -60,6 +60,9 @@ struct DeviceCtx {
   cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
   bool ws_used = false;
   Buf a, b, c;                // staging for the host-pointer entries
+  Buf ra, rb;                 // realigned copies of TMA-ineligible device operands (see run_device)
+  cudaEvent_t r_free = nullptr;  // recorded after the last kernel that read ra / rb
+  bool r_used = false;
   Buf flush;                  // L2 flush buffer for dgemm_b200_time_device
 };
 constexpr int MAX_DEV = 16;
@@ -101,6 +104,7 @@ int ensure_ctx(int dev, DeviceCtx** out) {
     CU_TRY(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
     CU_TRY(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&c.ws_free, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&c.r_free, cudaEventDisableTiming));
     CU_TRY(cudaMalloc(&c.sk_flags, 1024 * sizeof(unsigned int)));
     CU_TRY(cudaMemset(c.sk_flags, 0, 1024 * sizeof(unsigned int)));
     c.ready = true;
@@ -204,6 +208,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
     plan_stream_k(P, num_sms);
     return DGEMM_B200_OK;
   }
+  if (variant == dg::VARIANT_NAIVE || variant == dg::VARIANT_DFMA) splits = 1;  // ladder rungs: whole K per CTA
   if (splits <= 0) splits = choose_splits(tiles, P.k_tiles, num_sms);
   splits = std::max(1, std::min(splits, P.k_tiles));
   P.k_tiles_per_split = (P.k_tiles + splits - 1) / splits;
@@ -243,8 +248,40 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   }
   dg::Params P;
   P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
-  const bool tma_ok = dg::tma_eligible(P);
+  bool tma_ok = dg::tma_eligible(P);
+  bool realigned = false;
+  if (variant == dg::VARIANT_AUTO && !tma_ok && 2.0 * M * (double)N * K >= 2e10 && !getenv("DGEMM_B200_NO_REALIGN")) {
+    // Large operands that a tensor map cannot describe (odd leading dimension or an 8-byte-aligned base): copy the
+    // offending operand(s) once, device to device, into an even-LD scratch and run the TMA kernel (36 TF) instead of
+    // the cp.async kernel (31 TF).  The copy moves 16 bytes per element against 2*N (or 2*M) flops per element, ~1 %
+    // of the GEMM time at these sizes.  If the scratch cannot be allocated the cp.async kernel runs as before.
+    const bool a_bad = ((uintptr_t)dA % 16 != 0) || (lda % 2 != 0), b_bad = ((uintptr_t)dB % 16 != 0) || (ldb % 2 != 0);
+    const long long ldaR = (M + 1) & ~1ll, ldbR = (K + 1) & ~1ll;
+    const int saved_status = g_status;
+    bool got = true;
+    if (a_bad && grow(c.ra, (size_t)ldaR * K * 8) != DGEMM_B200_OK) got = false;
+    if (got && b_bad && grow(c.rb, (size_t)ldbR * N * 8) != DGEMM_B200_OK) got = false;
+    if (got) {
+      if (c.r_used) CU_TRY(cudaStreamWaitEvent(stream, c.r_free, 0));
+      if (a_bad) {
+        CU_TRY(cudaMemcpy2DAsync(c.ra.p, ldaR * 8, dA, (size_t)lda * 8, (size_t)M * 8, K, cudaMemcpyDeviceToDevice, stream));
+        dA = c.ra.p; lda = ldaR;
+      }
+      if (b_bad) {
+        CU_TRY(cudaMemcpy2DAsync(c.rb.p, ldbR * 8, dB, (size_t)ldb * 8, (size_t)K * 8, N, cudaMemcpyDeviceToDevice, stream));
+        dB = c.rb.p; ldb = ldbR;
+      }
+      P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
+      tma_ok = dg::tma_eligible(P);
+      realigned = true;
+    } else {
+      g_status = saved_status;  // out of memory for the scratch is not an error: fall through to cp.async
+      g_errmsg[0] = 0;
+      cudaGetLastError();
+    }
+  }
   if (variant == dg::VARIANT_AUTO) variant = tma_ok ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  if (variant < 0 || variant > dg::VARIANT_DFMA) return fail(DGEMM_B200_ERR_BAD_ARG, "unknown kernel variant %d", variant);
   if ((variant == dg::VARIANT_TMA || variant == dg::VARIANT_CPASYNC16) && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
@@ -270,6 +307,10 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (uses_ws) {
     CU_TRY(cudaEventRecord(c.ws_free, stream));
     c.ws_used = true;
+  }
+  if (realigned) {
+    CU_TRY(cudaEventRecord(c.r_free, stream));
+    c.r_used = true;
   }
   return ok();
 }
@@ -473,7 +514,7 @@ int dgemm_b200_shutdown(void) {
     if (!c.ready) continue;
     cudaSetDevice(d);
     cudaDeviceSynchronize();
-    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.flush}) {
+    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.flush, &c.ra, &c.rb}) {
       if (b->p) cudaFree(b->p);
       b->p = nullptr;
       b->cap = 0;
@@ -482,6 +523,7 @@ int dgemm_b200_shutdown(void) {
     cudaStreamDestroy(c.s_h2d);
     cudaStreamDestroy(c.s_d2h);
     cudaEventDestroy(c.ws_free);
+    cudaEventDestroy(c.r_free);
     cudaFree(c.sk_flags);
     c = DeviceCtx();
   }

@@ -244,7 +244,37 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
   // Fast path (warp tile fully inside C, 16-byte aligned columns): straight-line code, 16 independent 16-byte loads
   // in flight per lane before the first use.  The predicated edge path below puts every load in its own basic
   // block, which serialises the round trips (measured: ~9 us per tile instead of ~2).
-  const bool interior = P.c_vec2 && (m0 + warp_m * WM + WM <= P.M) && (n0 + warp_n * WN + WN <= P.N);
+  const bool inside = (m0 + warp_m * WM + WM <= P.M) && (n0 + warp_n * WN + WN <= P.N);
+  if (inside && !P.c_vec2) {
+    // same, for a C whose columns are only 8-byte aligned (odd LDC or base): scalar accesses, still branch-free
+#pragma unroll
+    for (int ip = 0; ip < FRAG_N; ip += 2) {
+      double* col0 = P.C + (long long)(n0 + warp_n * WN + ip * 8 + perm_n(r)) * P.ldc + mbase;
+      double* col1 = col0 + 8 * P.ldc;
+      double c[2][FRAG_M][2];
+      if (use_c) {
+#pragma unroll
+        for (int j = 0; j < FRAG_M; j++) {
+          const int o = (j >> 1) * 16 + (j & 1) * 4;
+          c[0][j][0] = col0[o]; c[0][j][1] = col0[o + 1];
+          c[1][j][0] = col1[o]; c[1][j][1] = col1[o + 1];
+        }
+      }
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        double* col = h ? col1 : col0;
+#pragma unroll
+        for (int j = 0; j < FRAG_M; j++) {
+          const int o = (j >> 1) * 16 + (j & 1) * 4;
+          double v0 = alpha * acc[ip + h][j][0], v1 = alpha * acc[ip + h][j][1];
+          if (use_c) { v0 = fma(beta, c[h][j][0], v0); v1 = fma(beta, c[h][j][1], v1); }
+          col[o] = v0; col[o + 1] = v1;
+        }
+      }
+    }
+    return;
+  }
+  const bool interior = P.c_vec2 && inside;
   if (interior) {
 #pragma unroll
     for (int ip = 0; ip < FRAG_N; ip += 2) {

@@ -11,10 +11,13 @@ enum Variant {
   VARIANT_TMA = 1,        // dgemm_tma_ws_kernel (needs 16-byte aligned A, B and even lda, ldb)
   VARIANT_CPASYNC8 = 2,   // dgemm_cpasync_kernel<1>: any alignment, any leading dimension
   VARIANT_CPASYNC16 = 3,  // dgemm_cpasync_kernel<2>: same eligibility as TMA
+  VARIANT_NAIVE = 4,      // ladder rung 1 (dgemm_ladder.cu): never chosen by VARIANT_AUTO
+  VARIANT_DFMA = 5,       // ladder rung 2: shared-memory tiles + 8x8 register tile on the CUDA-core FP64 pipe
 };
 
 bool tma_eligible(const Params& P);
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
+cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
 cudaError_t launch_fill_signed(double* X, int rows, int cols, long long ld, unsigned long long seed,
                                unsigned long long row0, unsigned long long col0, int num_sms, cudaStream_t stream);

@@ -504,6 +504,10 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
   const int tiles = P.tiles_m * P.tiles_n;
   const int units = tiles * P.splits;
   cudaError_t err = cudaSuccess;
+  if (variant == VARIANT_NAIVE || variant == VARIANT_DFMA) {
+    g_launches++;
+    return launch_ladder(P, variant, stream);
+  }
   if (variant == VARIANT_TMA) {
     CUtensorMap tmA, tmB;
     if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN))

@@ -140,3 +140,21 @@ def test_variants_agree_bitwise(dg):
         outs.append(dC.to_host())
         dA.free(); dB.free(); dC.free()
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("case", [((2200, 2304, 2100), (1, 0, 0), (0, 0, 0)),     # odd LDA only
+                                  ((2200, 2304, 2101), (0, 0, 0), (0, 0, 0)),     # odd LDB (= K) only
+                                  ((2049, 2051, 2305), (0, 0, 2), (0, 0, 0)),     # odd M -> odd LDA and LDC, odd LDB
+                                  ((2304, 2200, 2100), (0, 0, 0), (1, 1, 0))])    # 8-byte-aligned bases
+def test_large_unaligned_operands_are_realigned_on_device(dg, case):
+    """>= 2e10 flops and TMA-ineligible: D2D realign + TMA kernel. Same bound, A/B untouched, pad rows untouched."""
+    (M, N, K), pad, offset = case
+    gu.run_device(dg, M, N, K, 1.5, 0.5, pad=pad, offset=offset)
+
+
+@pytest.mark.parametrize("variant", [4, 5])   # ladder rungs: naive, DFMA register tile
+@pytest.mark.parametrize("case", [((256, 256, 256), (0, 0, 0), 1.0, 1.0), ((1000, 1003, 997), (0, 0, 0), 2.5, 0.5),
+                                  ((130, 70, 17), (3, 1, 5), -1.0, 0.0), ((1, 9, 200), (0, 0, 0), 1.0, 1.0)])
+def test_ladder_rungs(dg, variant, case):
+    (M, N, K), pad, alpha, beta = case
+    gu.run_device(dg, M, N, K, alpha, beta, pad=pad, variant=variant, c_fill=np.nan if beta == 0.0 else None)
