@@ -21,6 +21,11 @@ lib: $(LIB)
 $(LIB): $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
 
+# experimental build: 16 consumer warps (4 per SM sub-partition), 32x32 warp tiles; load with DGEMM_B200_LIB=...
+lib16: $(PKG)/libdgemm_b200_w16.so
+$(PKG)/libdgemm_b200_w16.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_WARPS_M=4 -DDG_WARPS_N=4 -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
 probe: $(PKG)/bin/peak_probe
 $(PKG)/bin/peak_probe: $(CSRC)/peak_probe.cu
 	mkdir -p $(PKG)/bin
@@ -41,4 +46,4 @@ sass: $(LIB)
 clean:
 	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
 	$(MAKE) -C oracle clean
-.PHONY: all build lib probe harness oracle sass clean
+.PHONY: all build lib lib16 probe harness oracle sass clean

@@ -19,7 +19,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdgemm_b200.so")
+LIB_PATH = os.environ.get("DGEMM_B200_LIB") or os.path.join(_HERE, "libdgemm_b200.so")  # env: experimental builds
 
 OK, ERR_NO_DEVICE, ERR_BAD_ARG, ERR_OOM, ERR_CUDA, ERR_NCCL = range(6)
 VARIANT_AUTO, VARIANT_TMA, VARIANT_CPASYNC8, VARIANT_CPASYNC16, VARIANT_NAIVE, VARIANT_DFMA = range(6)

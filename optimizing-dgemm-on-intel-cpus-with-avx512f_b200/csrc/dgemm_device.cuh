@@ -28,10 +28,23 @@ constexpr int BK = 16;
 constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-constexpr int CONSUMER_WARPS = 8;
+// Warp grid inside the CTA tile, a build-time switch (-DDG_WARPS_M=.. -DDG_WARPS_N=..):
+//   2 x 4 (default)  8 consumer warps, 64x32 warp tiles, 128 accumulator registers, 2 warps per SM sub-partition
+//   4 x 4            16 consumer warps, 32x32 warp tiles, 64 accumulator registers, 4 warps per SM sub-partition
+#ifndef DG_WARPS_M
+#define DG_WARPS_M 2
+#endif
+#ifndef DG_WARPS_N
+#define DG_WARPS_N 4
+#endif
+constexpr int WARPS_M = DG_WARPS_M;
+constexpr int WARPS_N = DG_WARPS_N;
+constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
 constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
-constexpr int WARPS_M = 2;  // warp grid inside the CTA tile: 2 (m) x 4 (n)
-constexpr int WARPS_N = 4;
+// register split between the producer warpgroup and the consumer warps (setmaxnreg); the CTA is compiled at
+// 65536 / (CONSUMER_THREADS + 128) registers per thread, rounded down to 8
+constexpr int PRODUCER_REGS = CONSUMER_WARPS == 8 ? 40 : 24;
+constexpr int CONSUMER_REGS = CONSUMER_WARPS == 8 ? 232 : 112;
 constexpr int WM = BM / WARPS_M;  // 64
 constexpr int WN = BN / WARPS_N;  // 32
 constexpr int FRAG_M = WM / 8;    // 8 column fragments (from A)

@@ -101,7 +101,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp >= CONSUMER_WARPS) {
     // ------------------------------- producer warpgroup: one elected lane issues TMA --------------------------
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PRODUCER_REGS));
     if (warp == CONSUMER_WARPS && lane == 0) {
       tma_prefetch_desc(&tmA);
       tma_prefetch_desc(&tmB);
@@ -176,7 +176,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else {
     // ------------------------------- consumer warps: DMMA main loop + epilogue -------------------------------
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
     const int warp_m = warp % WARPS_M, warp_n = warp / WARPS_M;
     const LaneOffsets lo = make_lane_offsets(lane, warp_m, warp_n);
     double acc[FRAG_N][FRAG_M][2];

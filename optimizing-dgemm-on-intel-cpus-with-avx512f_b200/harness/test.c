@@ -7,7 +7,9 @@
  * step 100, one verified call, then 3 timed calls through the 11-argument host-pointer entry (so the time INCLUDES
  * H2D/D2H, like any other kernel number), average reported with 2*m*n*k flops.  Additions: deterministic seeds,
  * sampled verification with a relative bound instead of MKL + abs 1e-2, a kernel-only line measured with CUDA
- * events on device-resident operands, and a non-zero exit status when the GPU call reports an error.
+ * events on device-resident operands, a non-zero exit status when the GPU call reports an error, and — replacing the
+ * reference's fixed-column scrape (data/data.sh:6, `cut -c 52-60`) — one JSON record per size appended to the file named
+ * by the environment variable DGEMM_B200_JSON.
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -38,6 +40,8 @@ int main(int argc, char *argv[]) {
   randomize_matrix(B, max_size, max_size, 2);
   randomize_matrix(C, max_size, max_size, 3);
   copy_matrix(C, C_ref, cap);
+  const char *json_path = getenv("DGEMM_B200_JSON");
+  FILE *json = json_path ? fopen(json_path, "a") : NULL;
   if (dgemm_b200_device_count() < 1) {
     printf("No usable B200 (sm_100) device: kernel %d has no CPU fallback. Exited.\n", kernel_num);
     exit(-5);
@@ -60,6 +64,7 @@ int main(int argc, char *argv[]) {
     double t1 = get_sec();
     printf("Average elasped time: %f second, performance: %f GFLOPS.\n", (t1 - t0) / N,
            2. * 1e-9 * N * m * n * k / (t1 - t0));
+    double kernel_ms = -1.0;
     if (kernel_num == 20) { /* kernel-only: operands resident in HBM, CUDA events */
       size_t bytes = sizeof(double) * (size_t)m * m;
       double *dA = (double *)dgemm_b200_malloc(bytes), *dB = (double *)dgemm_b200_malloc(bytes),
@@ -71,13 +76,24 @@ int main(int argc, char *argv[]) {
         dgemm_b200_sync(NULL);
         double ms = dgemm_b200_time_device(m, n, k, alpha, dA, m, dB, k, beta, dC, m, DGEMM_B200_VARIANT_AUTO, 0, 2, 5,
                                            (size_t)256 << 20);
+        kernel_ms = ms;
         if (ms > 0) printf("Kernel-only time: %f second, performance: %f GFLOPS (max |err|/bound %.3f).\n", ms * 1e-3,
                            2. * 1e-9 * m * n * k / (ms * 1e-3), ratio);
       }
       dgemm_b200_free(dA); dgemm_b200_free(dB); dgemm_b200_free(dC);
     }
+    if (json) {
+      fprintf(json, "{\"kernel\": %d, \"m\": %d, \"n\": %d, \"k\": %d, \"alpha\": %g, \"beta\": %g, "
+                    "\"e2e_seconds\": %.9f, \"e2e_gflops\": %.3f, \"kernel_seconds\": %.9f, \"kernel_gflops\": %.3f, "
+                    "\"max_err_over_bound\": %.4g}\n",
+              kernel_num, m, n, k, alpha, beta, (t1 - t0) / N, 2. * 1e-9 * N * m * n * k / (t1 - t0),
+              kernel_ms > 0 ? kernel_ms * 1e-3 : -1.0, kernel_ms > 0 ? 2. * 1e-9 * m * n * k / (kernel_ms * 1e-3) : -1.0,
+              ratio);
+      fflush(json);
+    }
     copy_matrix(C_ref, C, (size_t)m * n); /* restore C for the next size, as test.c:50 does */
   }
+  if (json) fclose(json);
   free(A); free(B); free(C); free(C_ref);
   dgemm_b200_shutdown();
   return 0;
