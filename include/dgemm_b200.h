@@ -92,6 +92,14 @@ int dgemm_b200_ipc_close(void *dptr);
 int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const double *dB, long long ldb,
                     int *variant, int *splits, int *ctas, int *sk_tiles);
 
+/* schedule mydgemm_gpu_v20 would use for this shape (no device needed, nothing is launched): the n_panels + 1
+ * column-panel boundaries, the n_slabs + 1 K-slab boundaries and the order of the (slab, panel) device calls as
+ * n_items pairs {slab, panel}.  Every array holds `cap` ints (any may be NULL); predicted_ms is the planner's model
+ * estimate of the whole call from pinned host memory.  Plays the role of the reference's N -> K -> M blocking
+ * loops (include/kernel18.h:652-669) when the operands start in host memory. */
+int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int *panels, int *n_panels, int *slabs,
+                         int *n_slabs, int *order, int *n_items, int cap, double *predicted_ms);
+
 /* ---- helpers so a plain-C harness needs no CUDA headers -------------------------------------------------------- */
 void *dgemm_b200_malloc(size_t bytes);                 /* device memory on the current device (NULL on failure) */
 void dgemm_b200_free(void *dptr);

@@ -34,7 +34,7 @@ EXPORTS = [
     "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
-    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_host_plan",
 ]
 
 
@@ -71,6 +71,9 @@ lib.dgemm_b200_ipc_open.argtypes = [C.c_char_p, C.POINTER(_vp)]
 lib.dgemm_b200_ipc_close.argtypes = [_vp]
 lib.dgemm_b200_plan.argtypes = [C.c_int, C.c_int, C.c_int, _vp, _ll, _vp, _ll, C.POINTER(C.c_int),
                                 C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+_ip = C.POINTER(C.c_int)
+lib.dgemm_b200_host_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _ip, _ip, _ip, _ip, _ip, _ip,
+                                     C.c_int, C.POINTER(C.c_double)]
 lib.dgemm_b200_malloc.argtypes = [C.c_size_t]
 lib.dgemm_b200_malloc.restype = _vp
 lib.dgemm_b200_free.argtypes = [_vp]
@@ -102,6 +105,17 @@ def _check(status=None):
     st = lib.dgemm_b200_last_status() if status is None else status
     if st != OK:
         raise DgemmError(st, last_error())
+
+
+def host_plan(M, N, K, alpha=1.0, beta=1.0, cap=4096):
+    """Schedule mydgemm_gpu_v20 uses for this shape: (panel bounds, slab bounds, [(slab, panel), ...], predicted ms).
+    Pure host logic — works without a GPU."""
+    nb, kb, od = (C.c_int * cap)(), (C.c_int * cap)(), (C.c_int * cap)()
+    n_p, n_s, n_i, ms = C.c_int(), C.c_int(), C.c_int(), C.c_double()
+    _check(lib.dgemm_b200_host_plan(M, N, K, alpha, beta, nb, C.byref(n_p), kb, C.byref(n_s), od, C.byref(n_i), cap,
+                                    C.byref(ms)))
+    return (list(nb[: n_p.value + 1]), list(kb[: n_s.value + 1]),
+            [(od[2 * i], od[2 * i + 1]) for i in range(n_i.value)], ms.value)
 
 
 def device_count():

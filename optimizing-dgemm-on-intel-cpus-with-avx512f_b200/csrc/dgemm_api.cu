@@ -347,39 +347,17 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   }
   if ((st = grow(c.c, (size_t)ldcD * N * 8))) return st;
 
-  // 2-D pipeline: N is cut into P column panels and K into S slabs; the S*P device calls run on one compute stream in
-  // anti-diagonal order (s + p ascending), so A slabs AND C panels arrive gradually: call (s,p) needs A[:,slab s]
-  // (first use), C panel p (only when s == 0) and the B block (s,p).  After the first two diagonals the H2D stream
-  // stays ahead of the math (per diagonal ~ one A slab + one C panel + d B blocks vs d kernels), so only a few
-  // hundred MB are exposed before the first kernel instead of all of A.  C panel p goes back as soon as its last
-  // slab is done.  Below ~8000^3 the call is PCIe-bound (24 n^2 bytes in vs 2 n^3 flops), so the pieces are kept small (>= ~60 us of
-  // math each, at most 8 x 8) to hide compute and D2H behind the H2D stream.
-  int P = 1, S = 1;
-  if (need_ab) {
-    const double flops = 2.0 * M * (double)N * K;
-    const int want = (int)std::max(1.0, std::min(64.0, flops / 2e9));  // pieces of >= ~60 us of math, at most 8 x 8
-    P = std::max(1, std::min({(int)std::lround(std::sqrt((double)want)), N / 256, 8}));
-    S = std::max(1, std::min({want / P, K / 512, 8}));
-  }
-  auto bounds = [](int total, int parts, int align) {
-    std::vector<int> b(parts + 1);
-    int per = ((total + parts - 1) / parts + align - 1) / align * align;
-    for (int i = 0; i <= parts; i++) b[i] = std::min(total, i * per);
-    return b;
-  };
-  const std::vector<int> nb = bounds(N, P, dg::BN), kb = bounds(K, S, dg::BK);
-  struct Item { int s, p; };
-  std::vector<Item> order;
-  for (int d = 0; d <= S + P - 2; d++)
-    for (int sI = 0; sI < S; sI++) {
-      const int pI = d - sI;
-      if (pI < 0 || pI >= P) continue;
-      if (nb[pI + 1] <= nb[pI]) continue;                       // empty panel
-      if (need_ab && kb[sI + 1] <= kb[sI]) continue;            // empty slab
-      order.push_back({sI, pI});
-    }
-  std::vector<int> last_slab(P, -1);                            // last non-empty slab index per panel
-  for (const Item& it : order) last_slab[it.p] = std::max(last_slab[it.p], it.s);
+  // 2-D pipeline: N is cut into column panels and K into slabs; the (slab, panel) device calls run on one compute
+  // stream in the planner's order (dgemm_hostplan.cpp: balanced growth of the resident rectangle, then the rest of
+  // A, then panel by panel with tapered last panels), the H2D copies are queued on a second stream in the order the
+  // calls first need them, and every C panel goes back on a third stream as soon as its last call is done.
+  const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, need_ab, need_c_in, c.num_sms);
+  const std::vector<int>& nb = plan.nb;
+  const std::vector<int>& kb = plan.kb;
+  const int P = (int)nb.size() - 1, S = (int)kb.size() - 1;
+  const std::vector<dg::HostPlanItem>& order = plan.order;
+  std::vector<int> last_item(P, -1);                            // index in `order` of the last call of every panel
+  for (size_t i = 0; i < order.size(); i++) last_item[order[i].p] = (int)i;
   std::vector<cudaEvent_t> ev_in(order.size()), ev_done(P, nullptr);
   for (auto& e : ev_in) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (auto& e : ev_done) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -407,7 +385,7 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
                           first_done[pI] ? 1.0 : beta, c.c.p + (size_t)n0 * ldcD, ldcD, c.s_compute, dg::VARIANT_AUTO, 0);
       if (s2) return s2;
       first_done[pI] = 1;
-      if (sI == last_slab[pI]) {
+      if ((int)i == last_item[pI]) {
         CU_TRY(cudaEventRecord(ev_done[pI], c.s_compute));
         CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done[pI], 0));
         CU_TRY(cudaMemcpy2DAsync(C + (size_t)n0 * LDC, (size_t)LDC * 8, c.c.p + (size_t)n0 * ldcD, ldcD * 8,
@@ -484,6 +462,25 @@ void mydgemm_gpu_v21(int M, int N, int K, double alpha, double* A, int LDA, doub
     return;
   }
   dgemm_b200_run_host_multi(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC, g);
+}
+
+int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* panels, int* n_panels, int* slabs,
+                         int* n_slabs, int* order, int* n_items, int cap, double* predicted_ms) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  if (M < 0 || N < 0 || K < 0) return fail(DGEMM_B200_ERR_BAD_ARG, "negative dimension M=%d N=%d K=%d", M, N, K);
+  const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, !(alpha == 0.0 || K == 0), beta != 0.0, 148);
+  if ((int)plan.nb.size() > cap || (int)plan.kb.size() > cap || 2 * (int)plan.order.size() > cap)
+    return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_host_plan: cap=%d ints is too small (%zu panels, %zu slabs, %zu calls)",
+                cap, plan.nb.size() - 1, plan.kb.size() - 1, plan.order.size());
+  if (panels) std::copy(plan.nb.begin(), plan.nb.end(), panels);
+  if (slabs) std::copy(plan.kb.begin(), plan.kb.end(), slabs);
+  if (order)
+    for (size_t i = 0; i < plan.order.size(); i++) { order[2 * i] = plan.order[i].s; order[2 * i + 1] = plan.order[i].p; }
+  if (n_panels) *n_panels = (int)plan.nb.size() - 1;
+  if (n_slabs) *n_slabs = (int)plan.kb.size() - 1;
+  if (n_items) *n_items = (int)plan.order.size();
+  if (predicted_ms) *predicted_ms = plan.predicted_ms;
+  return ok();
 }
 
 int dgemm_b200_last_status(void) { return g_status; }

@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <vector>
+
 namespace dg {
 
 struct Params;
@@ -21,6 +23,16 @@ cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
 cudaError_t launch_fill_signed(double* X, int rows, int cols, long long ld, unsigned long long seed,
                                unsigned long long row0, unsigned long long col0, int num_sms, cudaStream_t stream);
+// schedule of the host-pointer entry (dgemm_hostplan.cpp): column-panel / K-slab boundaries and the order of the
+// (slab, panel) device calls; the H2D copies are queued in the order the calls first need them
+struct HostPlanItem { int s, p; };
+struct HostPlan {
+  std::vector<int> nb, kb;
+  std::vector<HostPlanItem> order;
+  double predicted_ms = 0.0;  // the planner's own estimate of the whole call (model in dgemm_hostplan.cpp)
+};
+HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, int num_sms);
+
 int launch_count();
 void reset_launch_count();
 

@@ -11,5 +11,6 @@ for n in [int(x) for x in sys.argv[1:]] or [1024, 2048, 3072, 4096, 6144, 8192, 
         t0 = time.perf_counter()
         dg.mydgemm_gpu_v20(n, n, n, 1.0, h[0].data_ptr(), n, h[1].data_ptr(), n, 1.0, h[2].data_ptr(), n)
         best = min(best, time.perf_counter() - t0)
-    print(json.dumps({"n": n, "e2e_ms": round(best * 1e3, 3), "e2e_tflops": round(2.0 * n**3 / best / 1e12, 3),
+    nb, kb, od, pred = dg.host_plan(n, n, n)
+    print(json.dumps({"n": n, "plan": {"panels": len(nb) - 1, "slabs": len(kb) - 1, "calls": len(od), "model_ms": round(pred, 3)}, "e2e_ms": round(best * 1e3, 3), "e2e_tflops": round(2.0 * n**3 / best / 1e12, 3),
                       "pcie_floor_ms": round(24.0 * n * n / 55e9 * 1e3, 3)}), flush=True)
