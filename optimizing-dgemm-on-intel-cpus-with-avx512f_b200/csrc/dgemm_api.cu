@@ -351,7 +351,19 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   // stream in the planner's order (dgemm_hostplan.cpp: balanced growth of the resident rectangle, then the rest of
   // A, then panel by panel with tapered last panels), the H2D copies are queued on a second stream in the order the
   // calls first need them, and every C panel goes back on a third stream as soon as its last call is done.
-  const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, need_ab, need_c_in, c.num_sms);
+  // pageable caller memory (the reference harness mallocs its matrices, test.c:27-30) is staged through pinned slots
+  // by a team of host threads instead of the driver's single bounce buffer; small calls are not worth the threads
+  const double moved = 8.0 * ((need_ab ? (double)M * K + (double)K * N : 0.0) + (double)M * N);
+  const bool stage = moved >= (double)(8 << 20) && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
+  const bool pa = stage && need_ab && dg::host_pointer_is_pageable(A), pb = stage && need_ab && dg::host_pointer_is_pageable(B),
+             pc = stage && dg::host_pointer_is_pageable(C);
+  auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
+                 bool pageable) -> cudaError_t {
+    if (pageable) return dg::staged_h2d(dst, ldd, src, lds, rows, cols, c.s_h2d, dev);
+    return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
+                             cudaMemcpyHostToDevice, c.s_h2d);
+  };
+  const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, need_ab, need_c_in, c.num_sms, pa || pb || pc);
   const std::vector<int>& nb = plan.nb;
   const std::vector<int>& kb = plan.kb;
   const int P = (int)nb.size() - 1, S = (int)kb.size() - 1;
@@ -369,16 +381,13 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
       const int n0 = nb[pI], ncol = nb[pI + 1] - nb[pI];
       const int k0 = kb[sI], kc = need_ab ? kb[sI + 1] - kb[sI] : K;
       if (need_ab && !a_sent[sI]) {
-        CU_TRY(cudaMemcpy2DAsync(c.a.p + (size_t)k0 * ldaD, ldaD * 8, A + (size_t)k0 * LDA, (size_t)LDA * 8,
-                                 (size_t)M * 8, kc, cudaMemcpyHostToDevice, c.s_h2d));
+        CU_TRY(h2d(c.a.p + (size_t)k0 * ldaD, ldaD, A + (size_t)k0 * LDA, LDA, M, kc, pa));
         a_sent[sI] = 1;
       }
       if (need_c_in && !first_done[pI])
-        CU_TRY(cudaMemcpy2DAsync(c.c.p + (size_t)n0 * ldcD, ldcD * 8, C + (size_t)n0 * LDC, (size_t)LDC * 8,
-                                 (size_t)M * 8, ncol, cudaMemcpyHostToDevice, c.s_h2d));
+        CU_TRY(h2d(c.c.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc));
       if (need_ab)  // B block (s,p); sending whole B panels at s == 0 front-loads the stream (measured 6 % slower)
-        CU_TRY(cudaMemcpy2DAsync(c.b.p + (size_t)n0 * ldbD + k0, ldbD * 8, B + (size_t)n0 * LDB + k0, (size_t)LDB * 8,
-                                 (size_t)kc * 8, ncol, cudaMemcpyHostToDevice, c.s_h2d));
+        CU_TRY(h2d(c.b.p + (size_t)n0 * ldbD + k0, ldbD, B + (size_t)n0 * LDB + k0, LDB, kc, ncol, pb));
       CU_TRY(cudaEventRecord(ev_in[i], c.s_h2d));
       CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[i], 0));
       int s2 = run_device(c, M, ncol, kc, alpha, c.a.p + (size_t)k0 * ldaD, ldaD, c.b.p + (size_t)n0 * ldbD + k0, ldbD,
@@ -387,17 +396,24 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
       first_done[pI] = 1;
       if ((int)i == last_item[pI]) {
         CU_TRY(cudaEventRecord(ev_done[pI], c.s_compute));
-        CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done[pI], 0));
-        CU_TRY(cudaMemcpy2DAsync(C + (size_t)n0 * LDC, (size_t)LDC * 8, c.c.p + (size_t)n0 * ldcD, ldcD * 8,
-                                 (size_t)M * 8, ncol, cudaMemcpyDeviceToHost, c.s_d2h));
+        if (pc) {
+          CU_TRY(dg::staged_d2h_async(C + (size_t)n0 * LDC, LDC, c.c.p + (size_t)n0 * ldcD, ldcD, M, ncol, ev_done[pI],
+                                      c.s_d2h, dev));
+        } else {
+          CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done[pI], 0));
+          CU_TRY(cudaMemcpy2DAsync(C + (size_t)n0 * LDC, (size_t)LDC * 8, c.c.p + (size_t)n0 * ldcD, ldcD * 8,
+                                   (size_t)M * 8, ncol, cudaMemcpyDeviceToHost, c.s_d2h));
+        }
       }
     }
+    if (pc) CU_TRY(dg::staged_d2h_wait());
     CU_TRY(cudaStreamSynchronize(c.s_d2h));
     CU_TRY(cudaStreamSynchronize(c.s_compute));
     CU_TRY(cudaStreamSynchronize(c.s_h2d));
     return DGEMM_B200_OK;
   };
   result = body();
+  if (result && pc) dg::staged_d2h_wait();  // the D2H team may still hold ev_done events
   for (auto e : ev_in) cudaEventDestroy(e);
   for (auto e : ev_done) cudaEventDestroy(e);
   return result ? result : ok();
@@ -504,6 +520,7 @@ int dgemm_b200_set_max_gpus(int n) {
 int dgemm_b200_shutdown(void) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);
   dgemm_b200_multi_shutdown();
+  dg::staging_shutdown();
   int prev = 0;
   if (g_ndev > 0) cudaGetDevice(&prev);
   for (int d = 0; d < MAX_DEV; d++) {

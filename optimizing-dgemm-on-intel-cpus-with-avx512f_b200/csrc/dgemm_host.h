@@ -31,7 +31,17 @@ struct HostPlan {
   std::vector<HostPlanItem> order;
   double predicted_ms = 0.0;  // the planner's own estimate of the whole call (model in dgemm_hostplan.cpp)
 };
-HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, int num_sms);
+HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, int num_sms, bool pageable = false);
+
+// pageable host memory <-> HBM through per-thread pinned slots (dgemm_staging.cu)
+bool host_pointer_is_pageable(const void* p);
+bool staging_usable(int dev);
+cudaError_t staged_h2d(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
+                       cudaStream_t stream, int dev);
+cudaError_t staged_d2h_async(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
+                             cudaEvent_t ready, cudaStream_t stream, int dev);
+cudaError_t staged_d2h_wait();
+void staging_shutdown();
 
 int launch_count();
 void reset_launch_count();

@@ -28,6 +28,7 @@ namespace {
 
 struct Model {
   double h2d = 55e9, d2h = 55e9;  // bytes/s, pinned host memory, PCIe gen5 x16 (measured; tools/pcie_probe.py)
+  double h2d_pageable = 30e9, d2h_pageable = 30e9;  // pageable memory staged by dgemm_staging.cu (measured)
   double t_ktile = 2.13e-6;       // s per 128x128x16 k-tile per SM: 4096 clk at the DMMA issue limit, 1.965 GHz
   double t_epi = 2.2e-6;          // s per output tile per call: the fused epilogue reads and writes the C tile once per
                                   // K-slab, so thin slabs pay it more often (timeline stamps)
@@ -130,7 +131,7 @@ double simulate(const Model& m, int M, const std::vector<int>& nb, const std::ve
 
 struct CacheEntry {
   int M, N, K;
-  bool need_c_in;
+  bool need_c_in, pageable;
   HostPlan plan;
 };
 std::vector<CacheEntry> g_cache;
@@ -138,7 +139,7 @@ std::mutex g_cache_mu;
 
 }  // namespace
 
-HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, int num_sms) {
+HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, int num_sms, bool pageable) {
   HostPlan best;
   if (!need_ab || M <= 0 || N <= 0 || K <= 0) {  // C = beta*C only: one piece
     best.nb = {0, std::max(N, 0)};
@@ -150,10 +151,14 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
   {
     std::lock_guard<std::mutex> lk(g_cache_mu);
     for (const CacheEntry& e : g_cache)
-      if (e.M == M && e.N == N && e.K == K && e.need_c_in == need_c_in) return e.plan;
+      if (e.M == M && e.N == N && e.K == K && e.need_c_in == need_c_in && e.pageable == pageable) return e.plan;
   }
   Model m;
   if (num_sms > 0) m.sms = num_sms;
+  if (pageable) {  // staged through pinned slots by host threads (dgemm_staging.cu): bounded by the host's memcpy rate
+    m.h2d = std::min(m.h2d, m.h2d_pageable);
+    m.d2h = std::min(m.d2h, m.d2h_pageable);
+  }
   const double need_cols = 1.3 * 4.0 * m.flops_per_s() / m.h2d;
   best.predicted_ms = 1e300;
   static const int kLeadW[] = {0, 256, 512, 1024};
@@ -189,7 +194,7 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
   {
     std::lock_guard<std::mutex> lk(g_cache_mu);
     if (g_cache.size() >= 32) g_cache.erase(g_cache.begin());
-    g_cache.push_back({M, N, K, need_c_in, best});
+    g_cache.push_back({M, N, K, need_c_in, pageable, best});
   }
   return best;
 }

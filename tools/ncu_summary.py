@@ -13,7 +13,9 @@ KEYS = ['Kernel Name', 'Grid Size', 'Block Size', 'gpu__time_duration.sum', 'lau
         'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum',
         'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed', 'lts__t_sector_hit_rate.pct',
         'lts__t_bytes.sum', 'smsp__warps_active.avg.per_cycle_active', 'smsp__inst_executed.sum',
-        'sm__cycles_elapsed.avg', 'smsp__cycles_active.avg']
+        'sm__cycles_elapsed.avg', 'smsp__cycles_active.avg',
+        'SM_C.TriageCompute.smsp__pipe_tensor_subpipe_dmma_cycles_active.avg', 'TPC.TriageCompute.sm__cycles_active.avg',
+        'dram__bytes.sum.per_second']
 for vals in rows[2:]:
     d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
     o = {k: {"value": d[k][0], "unit": d[k][1]} for k in KEYS if k in d}
