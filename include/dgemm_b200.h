@@ -54,6 +54,19 @@ void mydgemm_gpu_v20(int M, int N, int K, double alpha, double *A, int LDA, doub
 void mydgemm_gpu_v21(int M, int N, int K, double alpha, double *A, int LDA, double *B, int LDB, double beta,
                      double *C, int LDC);
 
+/* ---- the CBLAS signature the reference harness calls for kernel 0 and for its own verification (reference
+ * test.c:38, utils.c:87-89: cblas_dgemm(CblasColMajor, CblasNoTrans, CblasNoTrans, m,n,k, alpha, A,m, B,k, beta, C,m)).
+ * Host pointers, single GPU.  layout: 101 row-major / 102 column-major; transa / transb: 111 NoTrans, 112 Trans,
+ * 113 ConjTrans (= Trans for real data) — the numeric values of CBLAS_LAYOUT / CBLAS_TRANSPOSE, so an `mkl.h`
+ * stand-in can forward cblas_dgemm to it unchanged (harness/mkl_b200/mkl.h).  NoTrans x NoTrans in either layout is
+ * the pipelined mydgemm_gpu_v20 path; a transposed operand is copied whole and transposed on the device first. */
+enum {
+  DGEMM_B200_ROW_MAJOR = 101, DGEMM_B200_COL_MAJOR = 102,
+  DGEMM_B200_NO_TRANS = 111, DGEMM_B200_TRANS = 112, DGEMM_B200_CONJ_TRANS = 113
+};
+void dgemm_b200_cblas_dgemm(int layout, int transa, int transb, int M, int N, int K, double alpha, const double *A,
+                            int lda, const double *B, int ldb, double beta, double *C, int ldc);
+
 int dgemm_b200_last_status(void);        /* status of the most recent call on this thread's process */
 const char *dgemm_b200_last_error(void); /* human-readable message for the last failure ("" if none) */
 
@@ -74,6 +87,11 @@ int dgemm_b200_device(int M, int N, int K, double alpha, const double *dA, long 
 int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
                          long long ldb, double beta, double *dC, long long ldc, void *stream, int variant,
                          int splits);
+/* C = alpha*op(A)*op(B) + beta*C on device pointers, same layout / transpose codes as dgemm_b200_cblas_dgemm.
+ * lda / ldb are the leading dimensions of A and B AS STORED. */
+int dgemm_b200_device_op(int layout, int transa, int transb, int M, int N, int K, double alpha, const double *dA,
+                         long long lda, const double *dB, long long ldb, double beta, double *dC, long long ldc,
+                         void *stream);
 /* DGEMM fused with an NVLink fetch: while the FP64 tensor-core warps compute this call, spare warps of the same
  * kernel copy fetch_bytes from fetch_src to fetch_dst (16-byte aligned, multiple of 16).  fetch_src is normally a
  * PEER GPU's buffer (dgemm_b200_ipc_open / peer access): the multi-GPU layer uses it to pull the NEXT K-slab of A

@@ -35,6 +35,7 @@ EXPORTS = [
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
     "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_host_plan",
+    "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op",
 ]
 
 
@@ -71,6 +72,10 @@ lib.dgemm_b200_ipc_open.argtypes = [C.c_char_p, C.POINTER(_vp)]
 lib.dgemm_b200_ipc_close.argtypes = [_vp]
 lib.dgemm_b200_plan.argtypes = [C.c_int, C.c_int, C.c_int, _vp, _ll, _vp, _ll, C.POINTER(C.c_int),
                                 C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+lib.dgemm_b200_cblas_dgemm.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, _vp, C.c_int,
+                                       _vp, C.c_int, C.c_double, _vp, C.c_int]
+lib.dgemm_b200_cblas_dgemm.restype = None
+lib.dgemm_b200_device_op.argtypes = [C.c_int, C.c_int, C.c_int] + _DEV_ARGS + [_vp]
 _ip = C.POINTER(C.c_int)
 lib.dgemm_b200_host_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _ip, _ip, _ip, _ip, _ip, _ip,
                                      C.c_int, C.POINTER(C.c_double)]
@@ -105,6 +110,22 @@ def _check(status=None):
     st = lib.dgemm_b200_last_status() if status is None else status
     if st != OK:
         raise DgemmError(st, last_error())
+
+
+ROW_MAJOR, COL_MAJOR, NO_TRANS, TRANS, CONJ_TRANS = 101, 102, 111, 112, 113
+
+
+def cblas_dgemm(layout, transa, transb, M, N, K, alpha, A, lda, B, ldb, beta, Cm, ldc):
+    """cblas_dgemm's own signature (reference test.c:38) on host arrays / raw host addresses, in place."""
+    pa = A.ctypes.data if isinstance(A, np.ndarray) else int(A)
+    pb = B.ctypes.data if isinstance(B, np.ndarray) else int(B)
+    pc = Cm.ctypes.data if isinstance(Cm, np.ndarray) else int(Cm)
+    lib.dgemm_b200_cblas_dgemm(layout, transa, transb, M, N, K, alpha, pa, lda, pb, ldb, beta, pc, ldc)
+    _check()
+
+
+def dgemm_device_op(layout, transa, transb, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0):
+    _check(lib.dgemm_b200_device_op(layout, transa, transb, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream))
 
 
 def host_plan(M, N, K, alpha=1.0, beta=1.0, cap=4096):

@@ -63,6 +63,9 @@ struct DeviceCtx {
   Buf ra, rb;                 // realigned copies of TMA-ineligible device operands (see run_device)
   cudaEvent_t r_free = nullptr;  // recorded after the last kernel that read ra / rb
   bool r_used = false;
+  Buf ta, tb;                 // transposed copies of op(A) = A^T / op(B) = B^T operands (run_device_op)
+  cudaEvent_t t_free = nullptr;  // recorded after the last kernel that read ta / tb
+  bool t_used = false;
   Buf flush;                  // L2 flush buffer for dgemm_b200_time_device
 };
 constexpr int MAX_DEV = 16;
@@ -105,6 +108,7 @@ int ensure_ctx(int dev, DeviceCtx** out) {
     CU_TRY(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&c.ws_free, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&c.r_free, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&c.t_free, cudaEventDisableTiming));
     CU_TRY(cudaMalloc(&c.sk_flags, 1024 * sizeof(unsigned int)));
     CU_TRY(cudaMemset(c.sk_flags, 0, 1024 * sizeof(unsigned int)));
     c.ready = true;
@@ -323,6 +327,48 @@ int current_ctx(DeviceCtx** out) {
   return ensure_ctx(dev, out);
 }
 
+// ---- op(A) / op(B): C = alpha * op(A) * op(B) + beta * C, column-major ---------------------------------------------
+// The reference only ever multiplies NoTrans x NoTrans (test.c:38, utils.c:88), and the DMMA kernel's shared-memory
+// layouts are built for exactly that (m contiguous for A, k contiguous for B).  A transposed operand is therefore
+// brought into that layout once, by an HBM-bound transpose pre-pass into a context-owned scratch (16 bytes per element
+// against the 2*N or 2*M flops the GEMM spends on the same element: ~1 % at 4096^3), and the same kernel runs.
+int check_args_op(bool ta, bool tb, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                  const void* C, long long ldc) {
+  if (M < 0 || N < 0 || K < 0) return fail(DGEMM_B200_ERR_BAD_ARG, "negative dimension M=%d N=%d K=%d", M, N, K);
+  const int ra = ta ? K : M, rb = tb ? N : K;
+  if (lda < std::max(1, ra)) return fail(DGEMM_B200_ERR_BAD_ARG, "LDA=%lld < max(1,%d)", lda, ra);
+  if (ldb < std::max(1, rb)) return fail(DGEMM_B200_ERR_BAD_ARG, "LDB=%lld < max(1,%d)", ldb, rb);
+  if (ldc < std::max(1, M)) return fail(DGEMM_B200_ERR_BAD_ARG, "LDC=%lld < max(1,M)=%d", ldc, std::max(1, M));
+  if (M > 0 && N > 0 && !C) return fail(DGEMM_B200_ERR_BAD_ARG, "C is NULL");
+  if (M > 0 && N > 0 && K > 0 && (!A || !B)) return fail(DGEMM_B200_ERR_BAD_ARG, "A or B is NULL");
+  return DGEMM_B200_OK;
+}
+
+int run_device_op(DeviceCtx& c, bool ta, bool tb, int M, int N, int K, double alpha, const double* dA, long long lda,
+                  const double* dB, long long ldb, double beta, double* dC, long long ldc, cudaStream_t stream) {
+  const bool degenerate = M == 0 || N == 0 || K == 0 || alpha == 0.0;  // A and B are not read at all
+  if (degenerate || (!ta && !tb))
+    return run_device(c, M, N, K, alpha, dA, degenerate ? std::max(1, M) : lda, dB, degenerate ? std::max(1, K) : ldb, beta,
+                      dC, ldc, stream, dg::VARIANT_AUTO, 0);
+  const long long ldaT = (M + 1) & ~1ll, ldbT = (K + 1) & ~1ll;
+  int st;
+  if (ta && (st = grow(c.ta, (size_t)ldaT * K * 8))) return st;
+  if (tb && (st = grow(c.tb, (size_t)ldbT * N * 8))) return st;
+  if (c.t_used) CU_TRY(cudaStreamWaitEvent(stream, c.t_free, 0));  // the previous reader (maybe another stream) is done
+  if (ta) {  // stored K x M, wanted M x K
+    CU_TRY(dg::launch_transpose(dA, lda, c.ta.p, ldaT, K, M, stream));
+    dA = c.ta.p; lda = ldaT;
+  }
+  if (tb) {  // stored N x K, wanted K x N
+    CU_TRY(dg::launch_transpose(dB, ldb, c.tb.p, ldbT, N, K, stream));
+    dB = c.tb.p; ldb = ldbT;
+  }
+  st = run_device(c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream, dg::VARIANT_AUTO, 0);
+  CU_TRY(cudaEventRecord(c.t_free, stream));
+  c.t_used = true;
+  return st;
+}
+
 // ---- host-pointer path: one GPU, column panels pipelined H2D -> DGEMM -> D2H ---------------------------------
 int run_host_single(int dev, int M, int N, int K, double alpha, const double* A, int LDA, const double* B, int LDB,
                     double beta, double* C, int LDC) {
@@ -419,6 +465,95 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   return result ? result : ok();
 }
 
+// ---- host-pointer path with op(A) / op(B): whole operands in, transpose pre-pass + DGEMM, C out ---------------------
+// (NoTrans x NoTrans goes through run_host_single and its pipelined schedule; the transposed forms are the BLAS
+// surface around the hot path, SURVEY.md section 8(f) rank 4, and are staged whole.)
+int run_host_op(int dev, bool ta, bool tb, int M, int N, int K, double alpha, const double* A, int LDA, const double* B,
+                int LDB, double beta, double* C, int LDC) {
+  if (!ta && !tb) return run_host_single(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
+  int st = check_args_op(ta, tb, M, N, K, A, LDA, B, LDB, C, LDC);
+  if (st) return st;
+  if (M == 0 || N == 0) return ok();
+  DeviceCtx* cp;
+  if ((st = ensure_ctx(dev, &cp))) return st;
+  DeviceCtx& c = *cp;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  CU_TRY(cudaSetDevice(dev));
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};
+  const bool need_ab = !(alpha == 0.0 || K == 0), need_c_in = beta != 0.0;
+  const int ra = ta ? K : M, ca = ta ? M : K, rb = tb ? N : K, cb = tb ? K : N;  // stored shapes of A and B
+  const long long ldaD = (ra + 1) & ~1ll, ldbD = (rb + 1) & ~1ll, ldcD = (M + 1) & ~1ll;
+  if (need_ab) {
+    if ((st = grow(c.a, (size_t)ldaD * ca * 8))) return st;
+    if ((st = grow(c.b, (size_t)ldbD * cb * 8))) return st;
+  }
+  if ((st = grow(c.c, (size_t)ldcD * N * 8))) return st;
+  const double moved = 8.0 * ((need_ab ? (double)M * K + (double)K * N : 0.0) + (double)M * N);
+  const bool stage = moved >= (double)(8 << 20) && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
+  auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols) {
+    if (stage && dg::host_pointer_is_pageable(src)) return dg::staged_h2d(dst, ldd, src, lds, rows, cols, c.s_h2d, dev);
+    return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
+                             cudaMemcpyHostToDevice, c.s_h2d);
+  };
+  cudaEvent_t ev_in = nullptr, ev_done = nullptr;
+  CU_TRY(cudaEventCreateWithFlags(&ev_in, cudaEventDisableTiming));
+  CU_TRY(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
+  const bool pc = stage && dg::host_pointer_is_pageable(C);
+  auto body = [&]() -> int {
+    if (need_ab) {
+      CU_TRY(h2d(c.a.p, ldaD, A, LDA, ra, ca));
+      CU_TRY(h2d(c.b.p, ldbD, B, LDB, rb, cb));
+    }
+    if (need_c_in) CU_TRY(h2d(c.c.p, ldcD, C, LDC, M, N));
+    CU_TRY(cudaEventRecord(ev_in, c.s_h2d));
+    CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in, 0));
+    int s2 = run_device_op(c, ta, tb, M, N, K, alpha, c.a.p, ldaD, c.b.p, ldbD, beta, c.c.p, ldcD, c.s_compute);
+    if (s2) return s2;
+    CU_TRY(cudaEventRecord(ev_done, c.s_compute));
+    if (pc) {
+      CU_TRY(dg::staged_d2h_async(C, LDC, c.c.p, ldcD, M, N, ev_done, c.s_d2h, dev));
+      CU_TRY(dg::staged_d2h_wait());
+    } else {
+      CU_TRY(cudaStreamWaitEvent(c.s_d2h, ev_done, 0));
+      CU_TRY(cudaMemcpy2DAsync(C, (size_t)LDC * 8, c.c.p, ldcD * 8, (size_t)M * 8, N, cudaMemcpyDeviceToHost, c.s_d2h));
+    }
+    CU_TRY(cudaStreamSynchronize(c.s_d2h));
+    CU_TRY(cudaStreamSynchronize(c.s_compute));
+    CU_TRY(cudaStreamSynchronize(c.s_h2d));
+    return DGEMM_B200_OK;
+  };
+  const int result = body();
+  if (result && pc) dg::staged_d2h_wait();
+  cudaEventDestroy(ev_in);
+  cudaEventDestroy(ev_done);
+  return result ? result : ok();
+}
+
+// CBLAS layout / transpose codes -> the column-major problem the kernels solve.  Row-major C = op(A) op(B) is the
+// column-major C^T = op(B)^T op(A)^T on the same bytes: swap the operands and M <-> N.
+struct ColMajorCall {
+  bool ta, tb;
+  int M, N;
+  const double *A, *B;
+  long long lda, ldb;
+};
+int to_col_major(int layout, int transa, int transb, int M, int N, const double* A, long long lda, const double* B,
+                 long long ldb, ColMajorCall* out) {
+  auto is_t = [](int t, bool* r) {
+    if (t == DGEMM_B200_NO_TRANS) { *r = false; return true; }
+    if (t == DGEMM_B200_TRANS || t == DGEMM_B200_CONJ_TRANS) { *r = true; return true; }  // real data: conj is a no-op
+    return false;
+  };
+  bool ta, tb;
+  if (!is_t(transa, &ta) || !is_t(transb, &tb))
+    return fail(DGEMM_B200_ERR_BAD_ARG, "transa=%d / transb=%d: expected 111 (NoTrans), 112 (Trans) or 113", transa, transb);
+  if (layout == DGEMM_B200_COL_MAJOR) *out = {ta, tb, M, N, A, B, lda, ldb};
+  else if (layout == DGEMM_B200_ROW_MAJOR) *out = {tb, ta, N, M, B, A, ldb, lda};
+  else return fail(DGEMM_B200_ERR_BAD_ARG, "layout=%d: expected 101 (row-major) or 102 (column-major)", layout);
+  return DGEMM_B200_OK;
+}
+
 __global__ void clock_probe_kernel(unsigned long long* out) {
   unsigned long long c0 = clock64(), t0, t1;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -480,6 +615,29 @@ void mydgemm_gpu_v21(int M, int N, int K, double alpha, double* A, int LDA, doub
   dgemm_b200_run_host_multi(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC, g);
 }
 
+void dgemm_b200_cblas_dgemm(int layout, int transa, int transb, int M, int N, int K, double alpha, const double* A,
+                            int lda, const double* B, int ldb, double beta, double* C, int ldc) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  ColMajorCall q = {};
+  if (to_col_major(layout, transa, transb, M, N, A, lda, B, ldb, &q)) return;
+  int dev = 0;
+  if (const char* e = getenv("DGEMM_B200_DEVICE")) dev = atoi(e);
+  run_host_op(dev, q.ta, q.tb, q.M, q.N, K, alpha, q.A, (int)q.lda, q.B, (int)q.ldb, beta, C, ldc);
+}
+
+int dgemm_b200_device_op(int layout, int transa, int transb, int M, int N, int K, double alpha, const double* dA,
+                         long long lda, const double* dB, long long ldb, double beta, double* dC, long long ldc,
+                         void* stream) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  ColMajorCall q = {};
+  int st = to_col_major(layout, transa, transb, M, N, dA, lda, dB, ldb, &q);
+  if (st) return st;
+  if ((st = check_args_op(q.ta, q.tb, q.M, q.N, K, q.A, q.lda, q.B, q.ldb, dC, ldc))) return st;
+  DeviceCtx* c;
+  if ((st = current_ctx(&c))) return st;
+  return run_device_op(*c, q.ta, q.tb, q.M, q.N, K, alpha, q.A, q.lda, q.B, q.ldb, beta, dC, ldc, (cudaStream_t)stream);
+}
+
 int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* panels, int* n_panels, int* slabs,
                          int* n_slabs, int* order, int* n_items, int cap, double* predicted_ms) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);
@@ -528,7 +686,7 @@ int dgemm_b200_shutdown(void) {
     if (!c.ready) continue;
     cudaSetDevice(d);
     cudaDeviceSynchronize();
-    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.flush, &c.ra, &c.rb}) {
+    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.flush, &c.ra, &c.rb, &c.ta, &c.tb}) {
       if (b->p) cudaFree(b->p);
       b->p = nullptr;
       b->cap = 0;
@@ -538,6 +696,7 @@ int dgemm_b200_shutdown(void) {
     cudaStreamDestroy(c.s_d2h);
     cudaEventDestroy(c.ws_free);
     cudaEventDestroy(c.r_free);
+    cudaEventDestroy(c.t_free);
     cudaFree(c.sk_flags);
     c = DeviceCtx();
   }

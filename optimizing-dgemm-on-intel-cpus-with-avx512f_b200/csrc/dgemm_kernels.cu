@@ -431,6 +431,30 @@ __global__ void scale_c_kernel(double* C, int M, int N, long long ldc, double be
   }
 }
 
+// dst (cols x rows, column-major, ldd) = transpose of src (rows x cols, column-major, lds).  Pre-pass for op(A) = A^T /
+// op(B) = B^T (dgemm_b200_device_op): 32 x 32 tiles through padded shared memory, both sides coalesced.  HBM-bound:
+// 16 bytes per element against the 2*N (or 2*M) flops the GEMM spends on it.
+constexpr int TR_TILE = 32, TR_ROWS = 8;
+__global__ void __launch_bounds__(TR_TILE * TR_ROWS)
+transpose_kernel(const double* __restrict__ src, long long lds, double* __restrict__ dst, long long ldd, int rows,
+                 int cols, int tiles_r) {
+  __shared__ double tile[TR_TILE][TR_TILE + 1];
+  const int tr = blockIdx.x % tiles_r, tc = blockIdx.x / tiles_r;
+  const int r0 = tr * TR_TILE, c0 = tc * TR_TILE;
+  const int tx = threadIdx.x % TR_TILE, ty = threadIdx.x / TR_TILE;
+#pragma unroll
+  for (int j = ty; j < TR_TILE; j += TR_ROWS) {
+    const int r = r0 + tx, c = c0 + j;
+    if (r < rows && c < cols) tile[j][tx] = src[(long long)c * lds + r];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = ty; j < TR_TILE; j += TR_ROWS) {
+    const int c = c0 + tx, r = r0 + j;   // dst element (c, r) = src (r, c)
+    if (r < rows && c < cols) dst[(long long)r * ldd + c] = tile[tx][j];
+  }
+}
+
 __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
   x += 0x9E3779B97F4A7C15ull;
   x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -556,6 +580,17 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || beta == 1.0) return cudaSuccess;
   scale_c_kernel<<<num_sms * 4, 256, 0, stream>>>(C, M, N, ldc, beta);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_transpose(const double* src, long long lds, double* dst, long long ldd, int rows, int cols,
+                             cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return cudaSuccess;
+  const long long tiles_r = (rows + TR_TILE - 1) / TR_TILE, tiles_c = (cols + TR_TILE - 1) / TR_TILE;
+  if (tiles_r * tiles_c > 0x7fffffffll) return cudaErrorInvalidValue;
+  transpose_kernel<<<(unsigned)(tiles_r * tiles_c), TR_TILE * TR_ROWS, 0, stream>>>(src, lds, dst, ldd, rows, cols,
+                                                                                     (int)tiles_r);
   g_launches++;
   return cudaGetLastError();
 }

@@ -95,3 +95,16 @@ def test_harness_binary_refuses_without_gpu(dg):
     if dg.device_count() == 0:
         r = subprocess.run([exe, "20", "100"], capture_output=True, text=True)
         assert r.returncode != 0 and "no CPU fallback" in r.stdout
+
+
+def test_cblas_entry_validates_codes_without_a_device(dg):
+    """Layout / transpose codes are checked before the device is touched; a valid call without a GPU fails loudly."""
+    A = np.zeros((4, 4), order="F"); B = np.zeros((4, 4), order="F"); Cm = np.ones((4, 4), order="F")
+    with pytest.raises(dg.DgemmError) as e:
+        dg.cblas_dgemm(7, dg.NO_TRANS, dg.NO_TRANS, 4, 4, 4, 1.0, A, 4, B, 4, 0.0, Cm, 4)
+    assert e.value.status == dg.ERR_BAD_ARG
+    if dg.device_count() == 0:
+        with pytest.raises(dg.DgemmError) as e:
+            dg.cblas_dgemm(dg.ROW_MAJOR, dg.TRANS, dg.NO_TRANS, 4, 4, 4, 1.0, A, 4, B, 4, 0.0, Cm, 4)
+        assert e.value.status == dg.ERR_NO_DEVICE
+        assert np.all(Cm == 1.0)   # C untouched: no CPU fallback
