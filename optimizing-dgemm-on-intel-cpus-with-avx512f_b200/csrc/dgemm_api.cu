@@ -289,26 +289,25 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if ((variant == dg::VARIANT_TMA || variant == dg::VARIANT_CPASYNC16) && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
-  const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
+  const bool uses_ws = P.splits > 1 || (P.sk_tiles > 0 && P.sk_parallel);  // chained stream-K updates C in place
+  const bool shares_ctx = uses_ws || P.sk_tiles > 0;  // workspace and / or the per-range flags: one launch at a time
+  if (shares_ctx && c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream)
+  if (P.sk_tiles > 0) {
+    P.sk_flags = c.sk_flags;
+    P.sk_epoch = ++c.sk_epoch;
+  }
   if (uses_ws) {
-    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits
-                                      : (size_t)P.sk_grid * (P.sk_parallel ? 2 : 1);
+    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits : (size_t)P.sk_grid * 2;
     const size_t need = slots * dg::BM * dg::BN * sizeof(double);
     if (c.ws.cap < need) {
       int st = grow(c.ws, need);
-      if (st) return st;
-      c.ws_used = false;
+      if (st) return st;   // (grow synchronises the device before it frees the old buffer)
     }
-    if (c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream) done
     P.workspace = c.ws.p;
-    if (P.sk_tiles > 0) {
-      P.sk_flags = c.sk_flags;
-      P.sk_epoch = ++c.sk_epoch;
-    }
   }
   P.fetch_src = fetch.src; P.fetch_dst = fetch.dst; P.fetch_bytes = fetch.bytes;
   CU_TRY(dg::launch_gemm(P, variant, c.num_sms, stream));
-  if (uses_ws) {
+  if (shares_ctx) {
     CU_TRY(cudaEventRecord(c.ws_free, stream));
     c.ws_used = true;
   }
