@@ -56,6 +56,7 @@ struct DeviceCtx {
   cudaStream_t s_compute = nullptr, s_h2d = nullptr, s_d2h = nullptr;
   Buf ws;                     // split-K / stream-K workspace
   unsigned int* sk_flags = nullptr;  // stream-K: one flag per CTA range, compared against sk_epoch
+  unsigned int* sync_ctr = nullptr;  // k-lockstep counters (SYNC_POINTS of them), zeroed before every launch that uses them
   unsigned int sk_epoch = 0;
   cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
   bool ws_used = false;
@@ -69,6 +70,7 @@ struct DeviceCtx {
   Buf flush;                  // L2 flush buffer for dgemm_b200_time_device
 };
 constexpr int MAX_DEV = 16;
+constexpr int SYNC_POINTS = 1 << 16;
 DeviceCtx g_ctx[MAX_DEV];
 int g_ndev = -1;  // usable devices (compute capability 10.x), -1 = not probed
 int g_max_gpus = 0;
@@ -111,6 +113,7 @@ int ensure_ctx(int dev, DeviceCtx** out) {
     CU_TRY(cudaEventCreateWithFlags(&c.t_free, cudaEventDisableTiming));
     CU_TRY(cudaMalloc(&c.sk_flags, 1024 * sizeof(unsigned int)));
     CU_TRY(cudaMemset(c.sk_flags, 0, 1024 * sizeof(unsigned int)));
+    CU_TRY(cudaMalloc(&c.sync_ctr, SYNC_POINTS * sizeof(unsigned int)));
     c.ready = true;
     cudaSetDevice(prev);
   }
@@ -201,9 +204,11 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
   P.fetch_src = nullptr; P.fetch_dst = nullptr; P.fetch_bytes = 0;
+  P.sync_ctr = nullptr; P.sync_waves = 0; P.sync_kt = 0;
   P.timeline = g_timeline;
   // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
-  P.group_m = std::min(P.tiles_m, 16);
+  static const int kGroupM = getenv("DGEMM_B200_GROUP_M") ? std::max(1, atoi(getenv("DGEMM_B200_GROUP_M"))) : 16;
+  P.group_m = std::min(P.tiles_m, kGroupM);
   P.c_vec2 = ((uintptr_t)dC % 16 == 0) && (ldc % 2 == 0);
   P.workspace = nullptr;
   if (splits <= 0 && variant == dg::VARIANT_TMA) {  // auto on the persistent kernel: stream-K, never split-K
@@ -289,21 +294,43 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if ((variant == dg::VARIANT_TMA || variant == dg::VARIANT_CPASYNC16) && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
-  const bool uses_ws = P.splits > 1 || (P.sk_tiles > 0 && P.sk_parallel);  // chained stream-K updates C in place
-  const bool shares_ctx = uses_ws || P.sk_tiles > 0;  // workspace and / or the per-range flags: one launch at a time
-  if (shares_ctx && c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream)
-  if (P.sk_tiles > 0) {
-    P.sk_flags = c.sk_flags;
-    P.sk_epoch = ++c.sk_epoch;
+  const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
+  // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
+  // there are at least two full waves; every CTA must be resident, i.e. the grid is one CTA per SM
+  static const bool kNoSync = getenv("DGEMM_B200_NO_LOCKSTEP") != nullptr;
+  static const int kSyncKt = getenv("DGEMM_B200_SYNC_KT") ? std::max(1, atoi(getenv("DGEMM_B200_SYNC_KT"))) : 64;
+  bool lockstep = false;
+  if (variant == dg::VARIANT_TMA && P.splits == 1 && !kNoSync) {
+    const int tiles = P.tiles_m * P.tiles_n;
+    const int dp_tiles = P.sk_tiles > 0 ? P.sk_tile0 : tiles;
+    const int full_waves = dp_tiles / c.num_sms;
+    const double operand_bytes = 8.0 * ((double)M * K + (double)K * N);
+    if (full_waves >= 2 && dp_tiles >= c.num_sms && operand_bytes > 96e6 && P.k_tiles >= 4 * kSyncKt) {
+      int kt = kSyncKt;
+      while ((long long)full_waves * ((P.k_tiles + kt - 1) / kt) > SYNC_POINTS) kt *= 2;
+      P.sync_ctr = c.sync_ctr; P.sync_waves = full_waves; P.sync_kt = kt;
+      lockstep = true;
+    }
   }
+  const bool shares_ctx = uses_ws || lockstep;  // workspace / flags / counters: one launch at a time
+  if (shares_ctx && c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream)
   if (uses_ws) {
-    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits : (size_t)P.sk_grid * 2;
+    const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits
+                                      : (size_t)P.sk_grid * (P.sk_parallel ? 2 : 1);
     const size_t need = slots * dg::BM * dg::BN * sizeof(double);
     if (c.ws.cap < need) {
       int st = grow(c.ws, need);
       if (st) return st;   // (grow synchronises the device before it frees the old buffer)
     }
     P.workspace = c.ws.p;
+    if (P.sk_tiles > 0) {
+      P.sk_flags = c.sk_flags;
+      P.sk_epoch = ++c.sk_epoch;
+    }
+  }
+  if (lockstep) {
+    const size_t points = (size_t)P.sync_waves * ((P.k_tiles + P.sync_kt - 1) / P.sync_kt);
+    CU_TRY(cudaMemsetAsync(c.sync_ctr, 0, points * sizeof(unsigned int), stream));
   }
   P.fetch_src = fetch.src; P.fetch_dst = fetch.dst; P.fetch_bytes = fetch.bytes;
   CU_TRY(dg::launch_gemm(P, variant, c.num_sms, stream));
@@ -697,6 +724,7 @@ int dgemm_b200_shutdown(void) {
     cudaEventDestroy(c.r_free);
     cudaEventDestroy(c.t_free);
     cudaFree(c.sk_flags);
+    cudaFree(c.sync_ctr);
     c = DeviceCtx();
   }
   if (g_ndev > 0) cudaSetDevice(prev);

@@ -64,17 +64,25 @@ struct Params {
   int group_m;            // rasterisation: tiles are walked in bands of group_m tile-rows
   int c_vec2;             // C base 16-byte aligned and ldc even -> 16-byte epilogue accesses
   double* workspace;      // splits > 1: [unit][ACC_PER_THREAD][CONSUMER_THREADS] partial accumulators;
-                          // parallel stream-K fix-up: two such slots per CTA range
+                          // stream-K: one such slot per CTA range
   // ---- stream-K tail (TMA kernel only): tiles [sk_tile0, sk_tile0 + sk_tiles) are cut into gridDim.x equal
   // ranges of (tile, k-tile) iterations instead of whole tiles
   int sk_tile0, sk_tiles;
   int sk_grid;                // CTAs launched when sk_tiles > 0 (every one of them must be co-resident)
   int sk_parallel;            // 1: parallel fix-up (all-stream-K mode, many ranges per tile): every range stores its
                               // partial (2 slots per range: head / tail) and each participant of a tile reduces a
-                              // 1/R slice of it; 0: chained — the ranges that share a tile update C in place one after
-                              // another, last K-range first (it runs first), no workspace
+                              // 1/R slice of it; 0: the tile's owner adds the other ranges' partials serially
   unsigned int sk_epoch;      // flag value that means "partial of this launch is in the workspace"
   unsigned int* sk_flags;     // one flag per CTA range
+  // ---- k-lockstep of the data-parallel waves (TMA kernel only).  Persistent CTAs have no reason to stay together: each
+  // walks its own tiles and nothing pulls a CTA that has fallen behind back.  But the 148 tiles of a wave share 16 row
+  // panels of A and ~9 column panels of B through L2 only while their CTAs read the same k at about the same time; once
+  // they drift further apart than the L2 can bridge, every panel is fetched from HBM several times (measured at
+  // 16384^3: 175 GB of DRAM reads against a 46 GB floor for this tile size).  Every sync_kt k-tiles the producer
+  // thread ticks a per-point counter and will not run more than SYNC_SLACK points ahead of the slowest CTA.
+  unsigned int* sync_ctr;     // one counter per sync point, zeroed before the launch; nullptr = off
+  int sync_waves;             // full waves (every CTA has a tile) covered by the lockstep
+  int sync_kt;                // k-tiles between sync points
   // ---- fused NVLink fetch (TMA kernel only): while the DMMA warps work on this call's K-slab, the three spare
   // warps of the producer warpgroup copy fetch_bytes from fetch_src (normally a PEER GPU's copy of the next K-slab
   // of A, mapped through CUDA IPC / peer access) to fetch_dst in local HBM.  16-byte aligned, multiple of 16.
@@ -248,25 +256,11 @@ __device__ __forceinline__ void zero_acc(double (&acc)[FRAG_N][FRAG_M][2]) {
 // Fused epilogue: C = alpha*acc + beta*C on the lanes' own entries, straight from registers.
 // beta == 0 never reads C (BLAS convention; NaN/Inf in C are overwritten).  Rows >= M / cols >= N are
 // predicated off, so padding rows M..ldc-1 are never touched.
-// `beta` is the factor applied to what C holds now: P.beta for the first (or only) update of a tile, 1.0 when a later
-// K-range of the same tile accumulates into it (chained stream-K).  COHERENT: C was written by another SM during this
-// launch -> read it through L2 (ld.global.cg), never from this SM's L1.
-template <bool COHERENT>
-__device__ __forceinline__ double2 ld_c2(const double* p) {
-  if constexpr (COHERENT) return __ldcg(reinterpret_cast<const double2*>(p));
-  else return *reinterpret_cast<const double2*>(p);
-}
-template <bool COHERENT>
-__device__ __forceinline__ double ld_c1(const double* p) {
-  if constexpr (COHERENT) return __ldcg(p);
-  else return *p;
-}
-template <bool COHERENT = false>
-__device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_M][2], const Params& P, double beta,
-                                               int m0, int n0, int warp_m, int warp_n, int lane) {
+__device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_M][2], const Params& P, int m0, int n0,
+                                               int warp_m, int warp_n, int lane) {
   const int r = lane >> 2, q = lane & 3;
   const int mq = map_m(2 * q);  // 0, 8, 2, 10
-  const double alpha = P.alpha;
+  const double alpha = P.alpha, beta = P.beta;
   const bool use_c = beta != 0.0;
   const int mbase = m0 + warp_m * WM + mq;
   // Fast path (warp tile fully inside C, 16-byte aligned columns): straight-line code, 16 independent 16-byte loads
@@ -284,8 +278,8 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
 #pragma unroll
         for (int j = 0; j < FRAG_M; j++) {
           const int o = (j >> 1) * 16 + (j & 1) * 4;
-          c[0][j][0] = ld_c1<COHERENT>(col0 + o); c[0][j][1] = ld_c1<COHERENT>(col0 + o + 1);
-          c[1][j][0] = ld_c1<COHERENT>(col1 + o); c[1][j][1] = ld_c1<COHERENT>(col1 + o + 1);
+          c[0][j][0] = col0[o]; c[0][j][1] = col0[o + 1];
+          c[1][j][0] = col1[o]; c[1][j][1] = col1[o + 1];
         }
       }
 #pragma unroll
@@ -312,8 +306,8 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
       if (use_c) {
 #pragma unroll
         for (int j = 0; j < FRAG_M; j++) {
-          c[0][j] = ld_c2<COHERENT>(col0 + (j >> 1) * 16 + (j & 1) * 4);
-          c[1][j] = ld_c2<COHERENT>(col1 + (j >> 1) * 16 + (j & 1) * 4);
+          c[0][j] = *reinterpret_cast<const double2*>(col0 + (j >> 1) * 16 + (j & 1) * 4);
+          c[1][j] = *reinterpret_cast<const double2*>(col1 + (j >> 1) * 16 + (j & 1) * 4);
         }
       }
 #pragma unroll
@@ -329,46 +323,39 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
     }
     return;
   }
-  // Edge tiles (and C that is neither interior nor 16-byte aligned): still branch-free on the load side.  Out-of-range
-  // entries are read from a clamped, always-valid address (the tile's first entry, value discarded) so that all 32
-  // loads of a column pair are in flight together; only the stores are predicated.
-  const double* safe = P.C + (long long)min(n0, P.N - 1) * P.ldc + min(m0, P.M - 1);
 #pragma unroll
-  for (int ip = 0; ip < FRAG_N; ip += 2) {
-    double c[2][FRAG_M][2];
+  for (int i = 0; i < FRAG_N; i++) {
+    const int n = n0 + warp_n * WN + i * 8 + perm_n(r);
+    if (n >= P.N) continue;
+    double* col = P.C + (long long)n * P.ldc;
+    double c0[FRAG_M], c1[FRAG_M];
     if (use_c) {
 #pragma unroll
-      for (int h = 0; h < 2; h++) {
-        const int n = n0 + warp_n * WN + (ip + h) * 8 + perm_n(r);
-        const double* col = P.C + (long long)n * P.ldc;
-#pragma unroll
-        for (int j = 0; j < FRAG_M; j++) {
-          const int m = mbase + (j >> 1) * 16 + (j & 1) * 4;
-          const bool ok0 = n < P.N && m < P.M, ok1 = n < P.N && m + 1 < P.M;
-          c[h][j][0] = ld_c1<COHERENT>(ok0 ? col + m : safe);
-          c[h][j][1] = ld_c1<COHERENT>(ok1 ? col + m + 1 : safe);
+      for (int j = 0; j < FRAG_M; j++) {
+        const int m = mbase + (j >> 1) * 16 + (j & 1) * 4;
+        c0[j] = c1[j] = 0.0;
+        if (P.c_vec2 && m + 1 < P.M) {
+          double2 v = *reinterpret_cast<const double2*>(col + m);
+          c0[j] = v.x; c1[j] = v.y;
+        } else {
+          if (m < P.M) c0[j] = col[m];
+          if (m + 1 < P.M) c1[j] = col[m + 1];
         }
       }
     }
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const int n = n0 + warp_n * WN + (ip + h) * 8 + perm_n(r);
-      double* col = P.C + (long long)n * P.ldc;
-#pragma unroll
-      for (int j = 0; j < FRAG_M; j++) {
-        const int m = mbase + (j >> 1) * 16 + (j & 1) * 4;
-        double v0 = alpha * acc[ip + h][j][0], v1 = alpha * acc[ip + h][j][1];
-        if (use_c) { v0 = fma(beta, c[h][j][0], v0); v1 = fma(beta, c[h][j][1], v1); }
-        if (n < P.N && m < P.M) col[m] = v0;
-        if (n < P.N && m + 1 < P.M) col[m + 1] = v1;
+    for (int j = 0; j < FRAG_M; j++) {
+      const int m = mbase + (j >> 1) * 16 + (j & 1) * 4;
+      double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
+      if (use_c) { v0 = fma(beta, c0[j], v0); v1 = fma(beta, c1[j], v1); }
+      if (P.c_vec2 && m + 1 < P.M) {
+        *reinterpret_cast<double2*>(col + m) = make_double2(v0, v1);
+      } else {
+        if (m < P.M) col[m] = v0;
+        if (m + 1 < P.M) col[m + 1] = v1;
       }
     }
   }
-}
-
-__device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_M][2], const Params& P, int m0, int n0,
-                                               int warp_m, int warp_n, int lane) {
-  epilogue_store<false>(acc, P, P.beta, m0, n0, warp_m, warp_n, lane);
 }
 
 // Epilogue for ONE fragment (i, j) of the lane: used by the parallel stream-K fix-up, where a CTA finishes only a
@@ -419,6 +406,14 @@ __device__ __forceinline__ void add_partial(double (&acc)[FRAG_N][FRAG_M][2], co
 
 __device__ __forceinline__ void st_release_gpu(unsigned int* p, unsigned int v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_relaxed_gpu(unsigned int* p, unsigned int v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_relaxed_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
 }
 __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   unsigned int v;

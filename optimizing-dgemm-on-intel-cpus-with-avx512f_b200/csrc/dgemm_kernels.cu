@@ -36,7 +36,9 @@ struct Segment {
   int tile, kb, ke;   // rasterised tile index, k-tile range [kb, ke)
   int kind;           // see below
   int slot;           // workspace slot (split-K: unit index; stream-K contributor: own range id)
+  int wave;           // phase 1: how many units this CTA has done before this one; -1 in phase 2
 };
+constexpr int SYNC_SLACK = 2;  // k-lockstep: a producer may run this many sync points ahead of the slowest CTA
 enum { SEG_DIRECT = 0, SEG_SPLITK = 1, SEG_SK_OWNER = 2, SEG_SK_CONTRIB = 3 };
 
 struct SegmentWalker {
@@ -58,6 +60,7 @@ struct SegmentWalker {
       sg.ke = min(P.k_tiles, sg.kb + P.k_tiles_per_split);
       sg.kind = P.splits == 1 ? SEG_DIRECT : SEG_SPLITK;
       sg.slot = u;
+      sg.wave = (u - (int)blockIdx.x) / stride;
       u += stride;
       return true;
     }
@@ -68,6 +71,7 @@ struct SegmentWalker {
       sg.ke = (int)min((long long)P.k_tiles, sg.kb + (end - it));
       sg.kind = sg.kb > 0 ? SEG_SK_CONTRIB : (sg.ke == P.k_tiles ? SEG_DIRECT : SEG_SK_OWNER);
       sg.slot = rid;
+      sg.wave = -1;
       it += sg.ke - sg.kb;
       return true;
     }
@@ -114,7 +118,17 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         decode_tile(P, sg.tile, tm, tn);
         const int m0 = tm * BM, n0 = tn * BN;
         asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(progress), "r"(++seg_idx) : "memory");
+        const bool lockstep = P.sync_ctr != nullptr && sg.wave >= 0 && sg.wave < P.sync_waves;
+        const int sync_per_tile = (P.k_tiles + P.sync_kt - 1) / max(P.sync_kt, 1);
+        int next_sync = sg.kb, point = sg.wave * sync_per_tile;
         for (int kt = sg.kb; kt < sg.ke; kt++) {
+          if (lockstep && kt == next_sync) {  // tick this point; wait for everyone at the point SYNC_SLACK back
+            red_add_relaxed_gpu(P.sync_ctr + point, 1u);
+            if (point >= SYNC_SLACK)
+              while (ld_relaxed_gpu(P.sync_ctr + point - SYNC_SLACK) < gridDim.x) __nanosleep(64);
+            point++;
+            next_sync += P.sync_kt;
+          }
           mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
           const uint32_t full = bars + 8 * s;
           const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
@@ -132,20 +146,13 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // Without it all CTAs hit their epilogue together and read 148 x 128 KB of C from DRAM in four dependent
       // rounds (~9 us per tile, measured with the timeline stamps); prefetched, the rounds are L2 hits.  Paced by
       // the producer's segment counter so the prefetch runs during the main loop of the same tile, never far ahead.
-      {
+      if (P.beta != 0.0) {
         SegmentWalker walk(P, num_units);
         Segment sg;
         uint32_t seg_idx = 0;
         while (walk.next(P, sg)) {
           ++seg_idx;
-          // does this segment's epilogue read C?  whole tiles and the beta-applying range: when beta != 0; a chained
-          // stream-K range that accumulates: always; split-K partials: never
-          bool reads_c;
-          if (sg.kind == SEG_DIRECT) reads_c = P.beta != 0.0;
-          else if (sg.kind == SEG_SPLITK) reads_c = false;
-          else if (P.sk_parallel) reads_c = sg.kind == SEG_SK_OWNER && P.beta != 0.0;
-          else reads_c = sg.ke == P.k_tiles ? P.beta != 0.0 : true;
-          if (!reads_c) continue;
+          if (sg.kind != SEG_DIRECT && sg.kind != SEG_SK_OWNER) continue;
           uint32_t seen;
           do {
             asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(seen) : "r"(progress) : "memory");
@@ -240,26 +247,21 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         consumer_bar_sync();
         if (tid == 0) st_release_gpu(P.sk_flags + slot, P.sk_epoch);
         fix_tile[sg.kind == SEG_SK_OWNER ? 1 : 0] = sg.tile;
-      } else {
-        // chained stream-K: the ranges that share this tile update C in place one after another, LAST K-range first —
-        // it is the first segment of its range, so it ran at the start of the kernel and the range before it (which
-        // reaches the same tile at the END of its own run) never waits in practice.  The last K-range applies beta,
-        // every other one accumulates (beta = 1) after the flag of the range behind it; fixed order -> deterministic.
-        // No partial tile ever goes through a workspace.
-        const bool last_k_range = sg.ke == P.k_tiles;
-        if (!last_k_range) {
+      } else if (sg.kind == SEG_SK_CONTRIB) {
+        store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
+        __threadfence();
+        consumer_bar_sync();
+        if (tid == 0) st_release_gpu(P.sk_flags + sg.slot, P.sk_epoch);
+      } else {  // SEG_SK_OWNER: add the partials of the ranges that hold the rest of this tile, in range order
+        const long long total = (long long)P.sk_tiles * P.k_tiles;
+        const long long tile_end = (long long)(sg.tile - P.sk_tile0 + 1) * P.k_tiles;
+        for (int r = sg.slot + 1; r < (int)gridDim.x && total * r / gridDim.x < tile_end; r++) {
           if (tid == 0)
-            while (ld_acquire_gpu(P.sk_flags + sg.slot + 1) != P.sk_epoch) __nanosleep(32);
+            while (ld_acquire_gpu(P.sk_flags + r) != P.sk_epoch) __nanosleep(64);
           consumer_bar_sync();
-          epilogue_store<true>(acc, P, 1.0, tm * BM, tn * BN, warp_m, warp_n, lane);
-        } else {
-          epilogue_store<false>(acc, P, P.beta, tm * BM, tn * BN, warp_m, warp_n, lane);
+          add_partial_cg(acc, P.workspace + (size_t)r * (BM * BN), tid);
         }
-        if (sg.kb > 0) {  // the range in front of this one is waiting for this update
-          __threadfence();
-          consumer_bar_sync();
-          if (tid == 0) st_release_gpu(P.sk_flags + sg.slot, P.sk_epoch);
-        }
+        epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       }
       if (tid == 0) stamp(P, tslot++);     // epilogue / partial store / fix-up of the segment done
     }
