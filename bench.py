@@ -495,13 +495,12 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
         dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, cptr))
         ev_a = copy_s.record_event()
         ev_c, ev_b = [], {}
-        for j in range(SP):
-            c0, nc = sp[j], sp[j + 1] - sp[j]
-            dg._check(dg.lib.dgemm_b200_h2d(Cm.data_ptr() + 8 * c0 * M, M, hC.data_ptr() + 8 * c0 * M, M, M, nc, cptr))
-            ev_c.append(copy_s.record_event())
         for i, g in enumerate(order):
             for j in range(SP):
                 c0, nc = sp[j], sp[j + 1] - sp[j]
+                if i == 0:  # C sub-panel j right before the first call that needs it, not all of C up front
+                    dg._check(dg.lib.dgemm_b200_h2d(Cm.data_ptr() + 8 * c0 * M, M, hC.data_ptr() + 8 * c0 * M, M, M, nc, cptr))
+                    ev_c.append(copy_s.record_event())
                 off = 8 * (c0 * K + kb[g])
                 dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr() + off, K, hB.data_ptr() + off, K, kb[g + 1] - kb[g], nc, cptr))
                 ev_b[(i, j)] = copy_s.record_event()

@@ -297,8 +297,8 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
   // there are at least two full waves; every CTA must be resident, i.e. the grid is one CTA per SM
-  static const bool kNoSync = getenv("DGEMM_B200_NO_LOCKSTEP") != nullptr;
-  static const int kSyncKt = getenv("DGEMM_B200_SYNC_KT") ? std::max(1, atoi(getenv("DGEMM_B200_SYNC_KT"))) : 64;
+  const bool kNoSync = getenv("DGEMM_B200_NO_LOCKSTEP") != nullptr;   // read per call: tests toggle it
+  const int kSyncKt = getenv("DGEMM_B200_SYNC_KT") ? std::max(1, atoi(getenv("DGEMM_B200_SYNC_KT"))) : 64;
   bool lockstep = false;
   if (variant == dg::VARIANT_TMA && P.splits == 1 && !kNoSync) {
     const int tiles = P.tiles_m * P.tiles_n;

@@ -158,3 +158,26 @@ def test_large_unaligned_operands_are_realigned_on_device(dg, case):
 def test_ladder_rungs(dg, variant, case):
     (M, N, K), pad, alpha, beta = case
     gu.run_device(dg, M, N, K, alpha, beta, pad=pad, variant=variant, c_fill=np.nan if beta == 0.0 else None)
+
+
+def test_k_lockstep_changes_no_bits(dg, monkeypatch):
+    """Large enough for the k-lockstep of the data-parallel waves (2 full waves, operands > 96 MB, K >= 4096): the
+    producers' pacing must not change a single bit, twice in a row (the counters are re-zeroed per launch), and the
+    result stays inside the bound."""
+    M, N, K = 3072, 3072, 4096
+    A, B, C0 = gu.make_inputs(M, N, K)
+    dA, dB = gu.DevMat(dg, A), gu.DevMat(dg, B)
+    outs = []
+    for no_lockstep in (None, None, "1"):
+        if no_lockstep:
+            monkeypatch.setenv("DGEMM_B200_NO_LOCKSTEP", no_lockstep)
+        else:
+            monkeypatch.delenv("DGEMM_B200_NO_LOCKSTEP", raising=False)
+        dC = gu.DevMat(dg, C0)
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, TMA, 0)
+        assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+        outs.append(dC.to_host())
+        dC.free()
+    dA.free(); dB.free()
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+    gu.check(M, N, K, 1.0, A, B, 1.0, C0, outs[0])
