@@ -188,14 +188,37 @@ def reference_arm(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthr, "kind": state["kind"], "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------------------------
 # the B200 arm
 # ------------------------------------------------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """Rank 0 must print exactly ONE line on stdout.  Libraries write there too (NCCL prints its version banner on
+    stdout when NCCL_DEBUG=VERSION is set on the box), so file descriptor 1 is pointed at stderr for the whole run and
+    the JSON line goes to a private duplicate of the original stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
     args = parse()
+    claim_stdout()
     if args.impl == "reference":
         reference_arm(args)
         return
@@ -386,7 +409,7 @@ def main():
         "spot_check_max_err_over_bound": value_check,
         "pct_of_fp64_peak": 100.0 * value / (N * peak),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if N > 1:
         dist.barrier()
         dist.destroy_process_group()
