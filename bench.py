@@ -152,7 +152,21 @@ def run_cpu_baseline(sample_n, reps):
     state = {}
     cpu_reference_step(sample_n, nthr, state)  # warm-up (first touch, thread team start)
     best = min(cpu_reference_step(sample_n, nthr, state) for _ in range(reps))
-    return {"value": 2.0 * sample_n ** 3 / best / 1e12, "unit": UNIT, "cores": nthr, "kind": state["kind"],
+    # and the serial kernel18 beside it (north_star: both reference kernels on the box's own cores), one core, 2048^3
+    k18 = None
+    try:
+        import oracle_lib as ol
+        if ol.have_ref():
+            m = 2048
+            a, b, c = ol.fill_signed(m, m, m, 21), ol.fill_signed(m, m, m, 22), ol.fill_signed(m, m, m, 23)
+            ol.call_gemm(ol.ref().mydgemm_cpu_v18, m, m, m, 1.0, a, b, 1.0, c)
+            t0 = time.perf_counter()
+            ol.call_gemm(ol.ref().mydgemm_cpu_v18, m, m, m, 1.0, a, b, 1.0, c)
+            dt = time.perf_counter() - t0
+            k18 = {"value": 2.0 * m ** 3 / dt / 1e12, "unit": UNIT, "cores": 1, "sample": f"M=N=K={m}, reference kernel18"}
+    except Exception as e:  # noqa: BLE001
+        k18 = {"value": None, "sample": repr(e)}
+    return {"value": 2.0 * sample_n ** 3 / best / 1e12, "unit": UNIT, "cores": nthr, "kind": state["kind"], "kernel18": k18,
             "sample": f"M=N=K={sample_n} alpha=1 beta=1, reference kernel19 (OpenMP, -O0 -march=skylake-avx512 as "
                       f"reference Makefile:3) best of {reps} after 1 warm-up, {nthr} threads on {cores} host cores "
                       f"({cpu_model()}); same 2MNK/t formula",
