@@ -172,6 +172,7 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
 // the same number of k-tiles.  When there are fewer tiles than SMs the whole problem is stream-K (this is what
 // split-K was for: M=N=512, K=16384 has 16 tiles for 148 SMs).
 static int SK_MIN_ITERS = getenv("DGEMM_B200_SK_MIN_ITERS") ? atoi(getenv("DGEMM_B200_SK_MIN_ITERS")) : 4;
+static int SK_ALIGNED_MIN_ITERS = getenv("DGEMM_B200_SK_ALIGNED_MIN_ITERS") ? std::max(1, atoi(getenv("DGEMM_B200_SK_ALIGNED_MIN_ITERS"))) : 2;
 void plan_stream_k(dg::Params& P, int num_sms) {
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0;
@@ -183,7 +184,19 @@ void plan_stream_k(dg::Params& P, int num_sms) {
     P.sk_grid = num_sms;
   } else {
     const long long iters = (long long)tiles * P.k_tiles;
-    const int g = (int)std::min<long long>(num_sms, iters / SK_MIN_ITERS);  // at least SK_MIN_ITERS k-tiles per CTA
+    int g = (int)std::min<long long>(num_sms, iters / SK_MIN_ITERS);  // at least SK_MIN_ITERS k-tiles per CTA
+    // Few tiles (>= 3 ranges each): give every tile the SAME whole number of ranges, so range boundaries fall on tile
+    // boundaries, every CTA holds one segment and stores one partial, and ranges may be as short as 2 k-tiles
+    // (measured: 256^3 25.2 -> 19.6 us, 384^3 27.3 -> 21.3 us; ragged ranges at 512^3: 31.8 us vs 25.4 aligned)
+    const int r_cap = num_sms / tiles;
+    if (r_cap >= 3 && !getenv("DGEMM_B200_SK_RAGGED")) {
+      // at most 64 ranges per tile (the parallel fix-up hands out the tile's 64 fragments; 128x128x4096: 64 ranges 4.25,
+      // 128 ranges 3.8 TFLOP/s), and no more ranges than it takes to reach the shortest longest range (512^3: 9 ranges
+      // of 3-4 k-tiles are slower than 8 ranges of 4: 10.2 vs 10.7 TFLOP/s)
+      const int r_max = std::max(1, std::min({r_cap, P.k_tiles / SK_ALIGNED_MIN_ITERS, 64}));
+      const int longest = (P.k_tiles + r_max - 1) / r_max;
+      g = tiles * ((P.k_tiles + longest - 1) / longest);
+    }
     if (g <= tiles) return;                                       // nothing to gain: one CTA per tile
     P.sk_tiles = tiles;
     P.sk_grid = g;
