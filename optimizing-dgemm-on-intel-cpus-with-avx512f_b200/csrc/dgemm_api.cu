@@ -272,11 +272,14 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
   bool tma_ok = dg::tma_eligible(P);
   bool realigned = false;
-  if (variant == dg::VARIANT_AUTO && !tma_ok && 2.0 * M * (double)N * K >= 2e10 && !getenv("DGEMM_B200_NO_REALIGN")) {
-    // Large operands that a tensor map cannot describe (odd leading dimension or an 8-byte-aligned base): copy the
-    // offending operand(s) once, device to device, into an even-LD scratch and run the TMA kernel (36 TF) instead of
-    // the cp.async kernel (31 TF).  The copy moves 16 bytes per element against 2*N (or 2*M) flops per element, ~1 %
-    // of the GEMM time at these sizes.  If the scratch cannot be allocated the cp.async kernel runs as before.
+  static const double kRealignMinFlops = getenv("DGEMM_B200_REALIGN_MIN_FLOPS") ? atof(getenv("DGEMM_B200_REALIGN_MIN_FLOPS")) : 1e8;
+  if (variant == dg::VARIANT_AUTO && !tma_ok && 2.0 * M * (double)N * K >= kRealignMinFlops && !getenv("DGEMM_B200_NO_REALIGN")) {
+    // Operands that a tensor map cannot describe (odd leading dimension or an 8-byte-aligned base): copy the offending
+    // operand(s) once, device to device (realign_kernel), into an even-LD scratch and run the TMA kernel instead of the
+    // cp.async kernel.  The copy moves 16 bytes per element against 2*N (or 2*M) flops per element; it pays from about
+    // 1e8 flops up (500x501x499: 5.9 -> 8.3, 1000x1003x997: 19.3 -> 20.7, 2001x2003x1999: 23.5 -> 30.1,
+    // 4097x4096x4095: 25.5 -> 34.0 TFLOP/s; tools/odd_ld_probe.py).  Below that, or if the scratch cannot be
+    // allocated, the cp.async kernel runs.
     const bool a_bad = ((uintptr_t)dA % 16 != 0) || (lda % 2 != 0), b_bad = ((uintptr_t)dB % 16 != 0) || (ldb % 2 != 0);
     const long long ldaR = (M + 1) & ~1ll, ldbR = (K + 1) & ~1ll;
     const int saved_status = g_status;
@@ -286,11 +289,11 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
     if (got) {
       if (c.r_used) CU_TRY(cudaStreamWaitEvent(stream, c.r_free, 0));
       if (a_bad) {
-        CU_TRY(cudaMemcpy2DAsync(c.ra.p, ldaR * 8, dA, (size_t)lda * 8, (size_t)M * 8, K, cudaMemcpyDeviceToDevice, stream));
+        CU_TRY(dg::launch_realign(dA, lda, c.ra.p, ldaR, M, K, c.num_sms, stream));
         dA = c.ra.p; lda = ldaR;
       }
       if (b_bad) {
-        CU_TRY(cudaMemcpy2DAsync(c.rb.p, ldbR * 8, dB, (size_t)ldb * 8, (size_t)K * 8, N, cudaMemcpyDeviceToDevice, stream));
+        CU_TRY(dg::launch_realign(dB, ldb, c.rb.p, ldbR, K, N, c.num_sms, stream));
         dB = c.rb.p; ldb = ldbR;
       }
       P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
@@ -798,7 +801,10 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
   if (st) return st;
   dg::Params P;
   P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
-  const int v = dg::tma_eligible(P) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  // (run_device realigns TMA-ineligible operands from 1e8 flops up and then runs the TMA kernel as well)
+  const bool realign = 2.0 * M * (double)N * K >= 1e8 && !getenv("DGEMM_B200_NO_REALIGN") &&
+                       !getenv("DGEMM_B200_REALIGN_MIN_FLOPS");
+  const int v = (dg::tma_eligible(P) || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms);
   if (variant) *variant = v;
   if (splits) *splits = P.splits;

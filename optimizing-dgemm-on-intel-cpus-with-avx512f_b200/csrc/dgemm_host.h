@@ -21,6 +21,9 @@ bool tma_eligible(const Params& P);
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
+// dst = src (rows x cols, column-major) with a new leading dimension
+cudaError_t launch_realign(const double* src, long long lds, double* dst, long long ldd, int rows, int cols, int num_sms,
+                           cudaStream_t stream);
 // dst (cols x rows, ldd) = src^T, src rows x cols with leading dimension lds, both column-major
 cudaError_t launch_transpose(const double* src, long long lds, double* dst, long long ldd, int rows, int cols,
                              cudaStream_t stream);

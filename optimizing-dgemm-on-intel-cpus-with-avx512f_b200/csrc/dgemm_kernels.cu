@@ -15,6 +15,7 @@
 #include "dgemm_host.h"
 
 #include <cuda.h>
+#include <algorithm>
 #include <cstdio>
 
 namespace dg {
@@ -445,6 +446,17 @@ __global__ void scale_c_kernel(double* C, int M, int N, long long ldc, double be
   }
 }
 
+// dst (rows x cols, ldd) = src (rows x cols, lds), column-major, 8-byte elements: brings an operand with an odd leading
+// dimension or an 8-byte-aligned base into a TMA-describable layout (run_device's realign pre-pass).  HBM-bound.
+__global__ void __launch_bounds__(256)
+realign_kernel(const double* __restrict__ src, long long lds, double* __restrict__ dst, long long ldd, int rows, int cols) {
+  for (int c = blockIdx.x; c < cols; c += gridDim.x) {
+    const double* s = src + (long long)c * lds;
+    double* d = dst + (long long)c * ldd;
+    for (int r = threadIdx.x; r < rows; r += 256) d[r] = s[r];
+  }
+}
+
 // dst (cols x rows, column-major, ldd) = transpose of src (rows x cols, column-major, lds).  Pre-pass for op(A) = A^T /
 // op(B) = B^T (dgemm_b200_device_op): 32 x 32 tiles through padded shared memory, both sides coalesced.  HBM-bound:
 // 16 bytes per element against the 2*N (or 2*M) flops the GEMM spends on it.
@@ -594,6 +606,14 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || beta == 1.0) return cudaSuccess;
   scale_c_kernel<<<num_sms * 4, 256, 0, stream>>>(C, M, N, ldc, beta);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_realign(const double* src, long long lds, double* dst, long long ldd, int rows, int cols, int num_sms,
+                           cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return cudaSuccess;
+  realign_kernel<<<std::min(cols, num_sms * 8), 256, 0, stream>>>(src, lds, dst, ldd, rows, cols);
   g_launches++;
   return cudaGetLastError();
 }
