@@ -189,7 +189,8 @@ void plan_stream_k(dg::Params& P, int num_sms) {
     // boundaries, every CTA holds one segment and stores one partial, and ranges may be as short as 2 k-tiles
     // (measured: 256^3 25.2 -> 19.6 us, 384^3 27.3 -> 21.3 us; ragged ranges at 512^3: 31.8 us vs 25.4 aligned)
     const int r_cap = num_sms / tiles;
-    if (r_cap >= 3 && !getenv("DGEMM_B200_SK_RAGGED")) {
+    static const int kAlignedMinRanges = getenv("DGEMM_B200_SK_ALIGNED_MIN_RANGES") ? atoi(getenv("DGEMM_B200_SK_ALIGNED_MIN_RANGES")) : 3;
+    if (r_cap >= kAlignedMinRanges && !getenv("DGEMM_B200_SK_RAGGED")) {
       // at most 64 ranges per tile (the parallel fix-up hands out the tile's 64 fragments; 128x128x4096: 64 ranges 4.25,
       // 128 ranges 3.8 TFLOP/s), and no more ranges than it takes to reach the shortest longest range (512^3: 9 ranges
       // of 3-4 k-tiles are slower than 8 ranges of 4: 10.2 vs 10.7 TFLOP/s)
