@@ -129,14 +129,15 @@ def dgemm_device_op(layout, transa, transb, M, N, K, alpha, dA, lda, dB, ldb, be
 
 
 def host_plan(M, N, K, alpha=1.0, beta=1.0, cap=4096):
-    """Schedule mydgemm_gpu_v20 uses for this shape: (panel bounds, slab bounds, [(slab, panel), ...], predicted ms).
+    """Schedule mydgemm_gpu_v20 uses for this shape: (panel bounds, slab bounds, [(slab, panel, end_slab), ...], predicted
+    ms); a call covers K-slabs [slab, end_slab) of one column panel.
     Pure host logic — works without a GPU."""
     nb, kb, od = (C.c_int * cap)(), (C.c_int * cap)(), (C.c_int * cap)()
     n_p, n_s, n_i, ms = C.c_int(), C.c_int(), C.c_int(), C.c_double()
     _check(lib.dgemm_b200_host_plan(M, N, K, alpha, beta, nb, C.byref(n_p), kb, C.byref(n_s), od, C.byref(n_i), cap,
                                     C.byref(ms)))
     return (list(nb[: n_p.value + 1]), list(kb[: n_s.value + 1]),
-            [(od[2 * i], od[2 * i + 1]) for i in range(n_i.value)], ms.value)
+            [(od[3 * i], od[3 * i + 1], od[3 * i + 2]) for i in range(n_i.value)], ms.value)
 
 
 def device_count():

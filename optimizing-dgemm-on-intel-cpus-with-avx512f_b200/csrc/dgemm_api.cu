@@ -466,12 +466,13 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   int result = DGEMM_B200_OK;
   auto body = [&]() -> int {
     for (size_t i = 0; i < order.size(); i++) {
-      const int sI = order[i].s, pI = order[i].p;
+      const int sI = order[i].s, sE = order[i].s_end, pI = order[i].p;
       const int n0 = nb[pI], ncol = nb[pI + 1] - nb[pI];
-      const int k0 = kb[sI], kc = need_ab ? kb[sI + 1] - kb[sI] : K;
-      if (need_ab && !a_sent[sI]) {
-        CU_TRY(h2d(c.a.p + (size_t)k0 * ldaD, ldaD, A + (size_t)k0 * LDA, LDA, M, kc, pa));
-        a_sent[sI] = 1;
+      const int k0 = kb[sI], kc = need_ab ? kb[sE] - kb[sI] : K;
+      for (int sl = sI; need_ab && sl < sE; sl++) {
+        if (a_sent[sl]) continue;
+        CU_TRY(h2d(c.a.p + (size_t)kb[sl] * ldaD, ldaD, A + (size_t)kb[sl] * LDA, LDA, M, kb[sl + 1] - kb[sl], pa));
+        a_sent[sl] = 1;
       }
       if (need_c_in && !first_done[pI])
         CU_TRY(h2d(c.c.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc));
@@ -686,13 +687,15 @@ int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* pa
   std::lock_guard<std::recursive_mutex> lk(g_mu);
   if (M < 0 || N < 0 || K < 0) return fail(DGEMM_B200_ERR_BAD_ARG, "negative dimension M=%d N=%d K=%d", M, N, K);
   const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, !(alpha == 0.0 || K == 0), beta != 0.0, 148);
-  if ((int)plan.nb.size() > cap || (int)plan.kb.size() > cap || 2 * (int)plan.order.size() > cap)
+  if ((int)plan.nb.size() > cap || (int)plan.kb.size() > cap || 3 * (int)plan.order.size() > cap)
     return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_host_plan: cap=%d ints is too small (%zu panels, %zu slabs, %zu calls)",
                 cap, plan.nb.size() - 1, plan.kb.size() - 1, plan.order.size());
   if (panels) std::copy(plan.nb.begin(), plan.nb.end(), panels);
   if (slabs) std::copy(plan.kb.begin(), plan.kb.end(), slabs);
   if (order)
-    for (size_t i = 0; i < plan.order.size(); i++) { order[2 * i] = plan.order[i].s; order[2 * i + 1] = plan.order[i].p; }
+    for (size_t i = 0; i < plan.order.size(); i++) {
+      order[3 * i] = plan.order[i].s; order[3 * i + 1] = plan.order[i].p; order[3 * i + 2] = plan.order[i].s_end;
+    }
   if (n_panels) *n_panels = (int)plan.nb.size() - 1;
   if (n_slabs) *n_slabs = (int)plan.kb.size() - 1;
   if (n_items) *n_items = (int)plan.order.size();

@@ -31,7 +31,7 @@ cudaError_t launch_fill_signed(double* X, int rows, int cols, long long ld, unsi
                                unsigned long long row0, unsigned long long col0, int num_sms, cudaStream_t stream);
 // schedule of the host-pointer entry (dgemm_hostplan.cpp): column-panel / K-slab boundaries and the order of the
 // (slab, panel) device calls; the H2D copies are queued in the order the calls first need them
-struct HostPlanItem { int s, p; };
+struct HostPlanItem { int s, p, s_end; };  // device call: slabs [s, s_end) of K against panel p
 struct HostPlan {
   std::vector<int> nb, kb;
   std::vector<HostPlanItem> order;

@@ -11,9 +11,10 @@
 //            as fast as the rectangle of resident data grows; small lead-in pieces shorten the first, exposed copy;
 //   phase B  once the resident panels are wide enough that one more slab is multiplied for longer than it takes to
 //            copy (N_resident >= 4 * TFLOPs / H2D_BW columns), bring in the rest of A;
-//   phase C  panel by panel: every call of a panel runs back to back, so panels finish one after another and
-//            their D2H hides behind the next panel's math; the last panels are tapered so that the copy left
-//            exposed after the last kernel is small.
+//   phase C  panel by panel, ONE call per panel over the whole K (all of A is resident by now: one epilogue per tile
+//            and one launch instead of one per slab), so panels finish one after another and their D2H hides behind
+//            the next panel's math; the last panels are tapered so that the copy left exposed after the last kernel
+//            is small.
 // The piece widths are chosen per call by simulating the three streams for a few hundred candidates with a
 // calibrated model (below) and taking the fastest — microseconds of host time per candidate, cached per shape.
 #include "dgemm_host.h"
@@ -75,7 +76,7 @@ std::vector<int> make_bounds(int total, const std::vector<int>& lead, int main_w
 
 // the three-phase order described in the header comment
 std::vector<HostPlanItem> make_order(int M, const std::vector<int>& nb, const std::vector<int>& kb, bool need_c_in,
-                                     double need_cols) {
+                                     double need_cols, bool merge_k) {
   const int P = (int)nb.size() - 1, S = (int)kb.size() - 1;
   std::vector<HostPlanItem> order;
   order.reserve((size_t)P * S);
@@ -98,10 +99,14 @@ std::vector<HostPlanItem> make_order(int M, const std::vector<int>& nb, const st
     }
     if (pick_slab) {
       const int s = aS++;
-      for (int p = 0; p < aP; p++) order.push_back({s, p});
+      for (int p = 0; p < aP; p++) order.push_back({s, p, s + 1});
     } else {
       const int p = aP++;
-      for (int s = 0; s < aS; s++) order.push_back({s, p});
+      if (merge_k && aS == S && S > 1) {
+        order.push_back({0, p, S});  // all of A is resident: the whole K in one call (one epilogue per tile, one launch)
+      } else {
+        for (int s = 0; s < aS; s++) order.push_back({s, p, s + 1});
+      }
     }
   }
   return order;
@@ -117,10 +122,11 @@ double simulate(const Model& m, int M, const std::vector<int>& nb, const std::ve
   for (int i = 0; i < (int)order.size(); i++) last[order[i].p] = i;
   double th = 0, tc = 0, td = 0;
   for (int i = 0; i < (int)order.size(); i++) {
-    const int s = order[i].s, p = order[i].p;
-    const double nc = nb[p + 1] - nb[p], kc = kb[s + 1] - kb[s];
+    const int p = order[i].p;
+    const double nc = nb[p + 1] - nb[p], kc = kb[order[i].s_end] - kb[order[i].s];
     th = std::max(th, i * m.t_issue);  // nothing starts before the host has queued it
-    if (!a_sent[s]) { th += 8.0 * M * kc / m.h2d + m.t_copy; a_sent[s] = 1; }
+    for (int s = order[i].s; s < order[i].s_end; s++)
+      if (!a_sent[s]) { th += 8.0 * M * (kb[s + 1] - kb[s]) / m.h2d + m.t_copy; a_sent[s] = 1; }
     if (need_c_in && !c_sent[p]) { th += 8.0 * M * nc / m.h2d + m.t_copy; c_sent[p] = 1; }
     th += 8.0 * kc * nc / m.h2d + m.t_copy;
     tc = std::max(tc, th) + m.kernel(M, (int)nc, (int)kc);
@@ -144,7 +150,7 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
   if (!need_ab || M <= 0 || N <= 0 || K <= 0) {  // C = beta*C only: one piece
     best.nb = {0, std::max(N, 0)};
     best.kb = {0, std::max(K, 0)};
-    best.order = {{0, 0}};
+    best.order = {{0, 0, 1}};
     best.predicted_ms = 0.0;
     return best;
   }
@@ -160,16 +166,21 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
     m.d2h = std::min(m.d2h, m.d2h_pageable);
   }
   const double need_cols = 1.3 * 4.0 * m.flops_per_s() / m.h2d;
+  // whole-K calls in phase C; env switches for A/B measurements
+  const bool merge_k = getenv("DGEMM_B200_PLAN_MERGE_K") ? atoi(getenv("DGEMM_B200_PLAN_MERGE_K")) != 0 : true;
   best.predicted_ms = 1e300;
-  static const int kLeadW[] = {0, 256, 512, 1024};
-  static const int kLeadN[] = {2, 4, 6};
+  // lead-in pieces: none, 2 / 4 / 6 equal ones, or geometric growth towards the main width
+  static const std::vector<int> kLeads[] = {{}, {256, 256}, {256, 256, 256, 256}, {256, 256, 256, 256, 256, 256},
+                                            {512, 512}, {512, 512, 512, 512}, {512, 512, 512, 512, 512, 512},
+                                            {1024, 1024}, {1024, 1024, 1024, 1024}, {1024, 1024, 1024, 1024, 1024, 1024},
+                                            {256, 256, 512, 1024}, {256, 256, 512, 512, 1024, 1024},
+                                            {512, 512, 1024, 1024}, {512, 512, 1024, 1024, 2048},
+                                            {512, 512, 512, 1024, 1024, 1024}, {512, 1024, 1024, 1024, 1024}};
   static const int kMainW[] = {8192, 4096, 2048, 1024, 512, 256};  // coarse first: ties keep fewer pieces
   static const std::vector<int> kTails[] = {{}, {256, 128}, {512, 256, 128}};
   const int max_items = 448;
-  for (int lw : kLeadW)
-    for (int ln : kLeadN) {
-      if (lw == 0 && ln != kLeadN[0]) continue;
-      const std::vector<int> lead(lw ? ln : 0, lw);
+  for (const std::vector<int>& lead : kLeads) {
+      const int lw = lead.empty() ? 0 : lead.back();
       for (int wn : kMainW) {
         if (wn < lw || (wn >= 2 * N && wn > 256)) continue;
         for (const std::vector<int>& tail : kTails) {
@@ -178,7 +189,7 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
             if (wk < lw || (wk >= 2 * K && wk > 256)) continue;
             const std::vector<int> kb = make_bounds(K, lead, wk, {}, Model::BK_);
             if ((nb.size() - 1) * (kb.size() - 1) > (size_t)max_items) continue;
-            std::vector<HostPlanItem> order = make_order(M, nb, kb, need_c_in, need_cols);
+            std::vector<HostPlanItem> order = make_order(M, nb, kb, need_c_in, need_cols, merge_k);
             const double t = simulate(m, M, nb, kb, order, need_c_in);
             if (t < best.predicted_ms * 0.999) {  // ties: keep the earlier (coarser lead-in, fewer pieces) candidate
               best.predicted_ms = t;

@@ -25,7 +25,9 @@ def test_plan_is_a_valid_decomposition(shape, beta):
     assert all(b % 128 == 0 for b in nb[1:-1]), nb      # panel starts on CTA-tile columns
     assert all(b % 16 == 0 for b in kb[1:-1]), kb       # slab starts on k-tile rows (and 16-byte aligned B blocks)
     P, S = len(nb) - 1, len(kb) - 1
-    assert sorted(order) == sorted(itertools.product(range(S), range(P)))   # every block exactly once
+    cells = [(s, p) for (s0, p, s1) in order for s in range(s0, s1)]      # a call covers slabs [s0, s1) of panel p
+    assert all(0 <= s0 < s1 <= S and 0 <= p < P for (s0, p, s1) in order)
+    assert sorted(cells) == sorted(itertools.product(range(S), range(P)))   # every (slab, panel) block exactly once
     assert len(order) <= 448
     assert ms > 0
 
@@ -37,11 +39,15 @@ def test_order_streams_operands_in_index_order(shape):
     M, N, K = shape
     nb, kb, order, _ = dg.host_plan(M, N, K)
     first_slab, first_panel, last_of_panel = {}, {}, {}
-    for i, (s, p) in enumerate(order):
-        first_slab.setdefault(s, i)
+    for i, (s0, p, s1) in enumerate(order):
+        for s in range(s0, s1):
+            first_slab.setdefault(s, i)
         first_panel.setdefault(p, i)
         last_of_panel[p] = i
-    assert [s for s, _ in sorted(first_slab.items(), key=lambda kv: kv[1])] == sorted(first_slab)
+    for p in first_panel:   # within a panel the K-slabs are applied in ascending order (beta only with the first call)
+        seq = [s0 for (s0, pp, s1) in order if pp == p]
+        assert seq == sorted(seq)
+    assert [s for s, _ in sorted(first_slab.items(), key=lambda kv: (kv[1], kv[0]))] == sorted(first_slab)
     assert [p for p, _ in sorted(first_panel.items(), key=lambda kv: kv[1])] == sorted(first_panel)
     assert max(last_of_panel, key=last_of_panel.get) == len(nb) - 2        # the last panel finishes last
     assert order[-1][1] == len(nb) - 2
@@ -50,7 +56,7 @@ def test_order_streams_operands_in_index_order(shape):
 def test_degenerate_calls_are_one_piece():
     for (M, N, K, alpha) in [(512, 512, 0, 1.0), (512, 512, 512, 0.0), (0, 512, 512, 1.0), (512, 0, 512, 1.0)]:
         nb, kb, order, _ = dg.host_plan(M, N, K, alpha, 0.5)
-        assert order == [(0, 0)] and nb == [0, N] and kb == [0, K]
+        assert order == [(0, 0, 1)] and nb == [0, N] and kb == [0, K]
 
 
 def test_large_square_plan_has_lead_in_and_taper():
@@ -58,6 +64,8 @@ def test_large_square_plan_has_lead_in_and_taper():
     last D2H), and a model estimate within 8 % of the kernel-only time at 36.4 TFLOP/s."""
     nb, kb, order, ms = dg.host_plan(16384, 16384, 16384)
     widths = [b - a for a, b in zip(nb, nb[1:])]
+    S = len(kb) - 1
+    assert order[-1] == (0, len(nb) - 2, S)            # the last panels take the whole K in one call (A is resident)
     assert widths[0] <= 1024 and kb[1] <= 1024
     assert widths[-1] <= 256 and max(widths) >= 2048
     ideal_ms = 2.0 * 16384 ** 3 / 36.4e12 * 1e3
