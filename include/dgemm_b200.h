@@ -113,10 +113,12 @@ int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const 
 /* schedule mydgemm_gpu_v20 would use for this shape (no device needed, nothing is launched): the n_panels + 1
  * column-panel boundaries, the n_slabs + 1 K-slab boundaries and the order of the device calls as n_items triples
  * {first slab, panel, end slab}: the call multiplies K-slabs [first, end) of A with the matching rows of panel `panel`.  Every array holds `cap` ints (any may be NULL); predicted_ms is the planner's model
- * estimate of the whole call from pinned host memory.  Plays the role of the reference's N -> K -> M blocking
+ * estimate of the whole call from pinned host memory; deferred_panels (may be NULL) is the number of leading panels
+ * whose beta*C term is added after their last call instead of before their first (so that the start of the pipeline
+ * does not wait for C to arrive).  Plays the role of the reference's N -> K -> M blocking
  * loops (include/kernel18.h:652-669) when the operands start in host memory. */
 int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int *panels, int *n_panels, int *slabs,
-                         int *n_slabs, int *order, int *n_items, int cap, double *predicted_ms);
+                         int *n_slabs, int *order, int *n_items, int cap, double *predicted_ms, int *deferred_panels);
 
 /* ---- helpers so a plain-C harness needs no CUDA headers -------------------------------------------------------- */
 void *dgemm_b200_malloc(size_t bytes);                 /* device memory on the current device (NULL on failure) */

@@ -78,7 +78,7 @@ lib.dgemm_b200_cblas_dgemm.restype = None
 lib.dgemm_b200_device_op.argtypes = [C.c_int, C.c_int, C.c_int] + _DEV_ARGS + [_vp]
 _ip = C.POINTER(C.c_int)
 lib.dgemm_b200_host_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _ip, _ip, _ip, _ip, _ip, _ip,
-                                     C.c_int, C.POINTER(C.c_double)]
+                                     C.c_int, C.POINTER(C.c_double), _ip]
 lib.dgemm_b200_malloc.argtypes = [C.c_size_t]
 lib.dgemm_b200_malloc.restype = _vp
 lib.dgemm_b200_free.argtypes = [_vp]
@@ -133,9 +133,10 @@ def host_plan(M, N, K, alpha=1.0, beta=1.0, cap=4096):
     ms); a call covers K-slabs [slab, end_slab) of one column panel.
     Pure host logic — works without a GPU."""
     nb, kb, od = (C.c_int * cap)(), (C.c_int * cap)(), (C.c_int * cap)()
-    n_p, n_s, n_i, ms = C.c_int(), C.c_int(), C.c_int(), C.c_double()
+    n_p, n_s, n_i, ms, n_d = C.c_int(), C.c_int(), C.c_int(), C.c_double(), C.c_int()
     _check(lib.dgemm_b200_host_plan(M, N, K, alpha, beta, nb, C.byref(n_p), kb, C.byref(n_s), od, C.byref(n_i), cap,
-                                    C.byref(ms)))
+                                    C.byref(ms), C.byref(n_d)))
+    host_plan.deferred_panels = n_d.value
     return (list(nb[: n_p.value + 1]), list(kb[: n_s.value + 1]),
             [(od[3 * i], od[3 * i + 1], od[3 * i + 2]) for i in range(n_i.value)], ms.value)
 

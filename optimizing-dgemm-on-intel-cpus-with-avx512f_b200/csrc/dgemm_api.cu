@@ -61,6 +61,7 @@ struct DeviceCtx {
   cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
   bool ws_used = false;
   Buf a, b, c;                // staging for the host-pointer entries
+  Buf x;                      // C_in of the deferred-C panels of the host pipeline
   Buf ra, rb;                 // realigned copies of TMA-ineligible device operands (see run_device)
   cudaEvent_t r_free = nullptr;  // recorded after the last kernel that read ra / rb
   bool r_used = false;
@@ -459,6 +460,12 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   const std::vector<dg::HostPlanItem>& order = plan.order;
   std::vector<int> last_item(P, -1);                            // index in `order` of the last call of every panel
   for (size_t i = 0; i < order.size(); i++) last_item[order[i].p] = (int)i;
+  // deferred C: panels [0, deferred) start with beta = 0; their C_in goes to a side buffer behind the last B block
+  // and beta*C_in is added by an elementwise pass after their last call
+  const int deferred = need_c_in ? plan.deferred_panels : 0;
+  if (deferred > 0 && (st = grow(c.x, (size_t)ldcD * nb[deferred] * 8))) return st;
+  cudaEvent_t ev_x = nullptr;
+  if (deferred > 0) CU_TRY(cudaEventCreateWithFlags(&ev_x, cudaEventDisableTiming));
   std::vector<cudaEvent_t> ev_in(order.size()), ev_done(P, nullptr);
   for (auto& e : ev_in) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (auto& e : ev_done) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -474,16 +481,25 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
         CU_TRY(h2d(c.a.p + (size_t)kb[sl] * ldaD, ldaD, A + (size_t)kb[sl] * LDA, LDA, M, kb[sl + 1] - kb[sl], pa));
         a_sent[sl] = 1;
       }
-      if (need_c_in && !first_done[pI])
+      const bool defer = pI < deferred;
+      if (need_c_in && !defer && !first_done[pI])
         CU_TRY(h2d(c.c.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc));
       if (need_ab)  // B block (s,p); sending whole B panels at s == 0 front-loads the stream (measured 6 % slower)
         CU_TRY(h2d(c.b.p + (size_t)n0 * ldbD + k0, ldbD, B + (size_t)n0 * LDB + k0, LDB, kc, ncol, pb));
       CU_TRY(cudaEventRecord(ev_in[i], c.s_h2d));
       CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[i], 0));
       int s2 = run_device(c, M, ncol, kc, alpha, c.a.p + (size_t)k0 * ldaD, ldaD, c.b.p + (size_t)n0 * ldbD + k0, ldbD,
-                          first_done[pI] ? 1.0 : beta, c.c.p + (size_t)n0 * ldcD, ldcD, c.s_compute, dg::VARIANT_AUTO, 0);
+                          first_done[pI] ? 1.0 : (defer ? 0.0 : beta), c.c.p + (size_t)n0 * ldcD, ldcD, c.s_compute,
+                          dg::VARIANT_AUTO, 0);
       if (s2) return s2;
       first_done[pI] = 1;
+      if (defer && (int)i == last_item[pI]) {
+        CU_TRY(h2d(c.x.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc));
+        CU_TRY(cudaEventRecord(ev_x, c.s_h2d));
+        CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_x, 0));
+        CU_TRY(dg::launch_add_scaled(c.c.p + (size_t)n0 * ldcD, ldcD, c.x.p + (size_t)n0 * ldcD, ldcD, M, ncol, beta, c.num_sms,
+                                     c.s_compute));
+      }
       if ((int)i == last_item[pI]) {
         CU_TRY(cudaEventRecord(ev_done[pI], c.s_compute));
         if (pc) {
@@ -683,7 +699,7 @@ int dgemm_b200_device_op(int layout, int transa, int transb, int M, int N, int K
 }
 
 int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* panels, int* n_panels, int* slabs,
-                         int* n_slabs, int* order, int* n_items, int cap, double* predicted_ms) {
+                         int* n_slabs, int* order, int* n_items, int cap, double* predicted_ms, int* deferred_panels) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);
   if (M < 0 || N < 0 || K < 0) return fail(DGEMM_B200_ERR_BAD_ARG, "negative dimension M=%d N=%d K=%d", M, N, K);
   const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, !(alpha == 0.0 || K == 0), beta != 0.0, 148);
@@ -700,6 +716,7 @@ int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* pa
   if (n_slabs) *n_slabs = (int)plan.kb.size() - 1;
   if (n_items) *n_items = (int)plan.order.size();
   if (predicted_ms) *predicted_ms = plan.predicted_ms;
+  if (deferred_panels) *deferred_panels = beta != 0.0 ? plan.deferred_panels : 0;
   return ok();
 }
 
@@ -732,7 +749,7 @@ int dgemm_b200_shutdown(void) {
     if (!c.ready) continue;
     cudaSetDevice(d);
     cudaDeviceSynchronize();
-    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.flush, &c.ra, &c.rb, &c.ta, &c.tb}) {
+    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.x, &c.flush, &c.ra, &c.rb, &c.ta, &c.tb}) {
       if (b->p) cudaFree(b->p);
       b->p = nullptr;
       b->cap = 0;

@@ -21,6 +21,9 @@ bool tma_eligible(const Params& P);
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
+// C += beta * X, both M x N column-major
+cudaError_t launch_add_scaled(double* C, long long ldc, const double* X, long long ldx, int M, int N, double beta,
+                              int num_sms, cudaStream_t stream);
 // dst = src (rows x cols, column-major) with a new leading dimension
 cudaError_t launch_realign(const double* src, long long lds, double* dst, long long ldd, int rows, int cols, int num_sms,
                            cudaStream_t stream);
@@ -35,6 +38,7 @@ struct HostPlanItem { int s, p, s_end; };  // device call: slabs [s, s_end) of K
 struct HostPlan {
   std::vector<int> nb, kb;
   std::vector<HostPlanItem> order;
+  int deferred_panels = 0;    // panels [0, deferred_panels): beta*C is added AFTER their last call (see dgemm_hostplan.cpp)
   double predicted_ms = 0.0;  // the planner's own estimate of the whole call (model in dgemm_hostplan.cpp)
 };
 HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, int num_sms, bool pageable = false);

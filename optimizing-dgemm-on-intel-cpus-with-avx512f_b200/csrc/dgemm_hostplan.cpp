@@ -8,7 +8,11 @@
 // a_s slabs and a_p panels resident, one more slab costs M*kw bytes and enables a_p calls, one more panel costs
 // M*nw bytes and enables a_s calls, so the schedule is
 //   phase A  grow slabs and panels in balance (whichever enables more flops per byte) — the math can only run
-//            as fast as the rectangle of resident data grows; small lead-in pieces shorten the first, exposed copy;
+//            as fast as the rectangle of resident data grows; small lead-in pieces shorten the first, exposed copy.
+//            With beta != 0 a panel would cost its M*nw bytes of C before its first call; instead the panels opened
+//            here start with beta = 0 (C is not read) and get beta*C added by an elementwise pass after their LAST
+//            call, when the link has slack ("deferred C"): opening a panel then costs only a B block and the math is
+//            compute-bound after the first small slab of A;
 //   phase B  once the resident panels are wide enough that one more slab is multiplied for longer than it takes to
 //            copy (N_resident >= 4 * TFLOPs / H2D_BW columns), bring in the rest of A;
 //   phase C  panel by panel, ONE call per panel over the whole K (all of A is resident by now: one epilogue per tile
@@ -30,6 +34,7 @@ namespace {
 struct Model {
   double h2d = 55e9, d2h = 55e9;  // bytes/s, pinned host memory, PCIe gen5 x16 (measured; tools/pcie_probe.py)
   double h2d_pageable = 30e9, d2h_pageable = 30e9;  // pageable memory staged by dgemm_staging.cu (measured)
+  double hbm = 5.0e12;            // bytes/s an elementwise kernel sustains (beta*C fix-up of deferred panels)
   double t_ktile = 2.13e-6;       // s per 128x128x16 k-tile per SM: 4096 clk at the DMMA issue limit, 1.965 GHz
   double t_epi = 2.2e-6;          // s per output tile per call: the fused epilogue reads and writes the C tile once per
                                   // K-slab, so thin slabs pay it more often (timeline stamps)
@@ -75,13 +80,17 @@ std::vector<int> make_bounds(int total, const std::vector<int>& lead, int main_w
 }
 
 // the three-phase order described in the header comment
+// defer_c: the panels opened in phase A start with beta = 0 and get beta*C added after their last call, so opening
+// them costs only a B block; *deferred receives how many (they are panels [0, *deferred)).
 std::vector<HostPlanItem> make_order(int M, const std::vector<int>& nb, const std::vector<int>& kb, bool need_c_in,
-                                     double need_cols, bool merge_k) {
+                                     double need_cols, bool merge_k, bool defer_c, int* deferred) {
   const int P = (int)nb.size() - 1, S = (int)kb.size() - 1;
   std::vector<HostPlanItem> order;
   order.reserve((size_t)P * S);
   int aS = 0, aP = 0;
   bool phase_b = false;
+  *deferred = 0;
+  const bool c_costs = need_c_in && !(defer_c && S > 1);
   while (aS < S || aP < P) {
     const double Kw = kb[aS], Nw = nb[aP];
     if (!phase_b && Nw >= need_cols && Kw > 0) phase_b = true;
@@ -94,7 +103,7 @@ std::vector<HostPlanItem> make_order(int M, const std::vector<int>& nb, const st
     else {
       const double kw = kb[aS + 1] - kb[aS], nw = nb[aP + 1] - nb[aP];
       const double rs = (2.0 * M * kw * Nw) / (8.0 * (M * kw + kw * Nw));                       // flops per byte moved
-      const double rp = (2.0 * M * Kw * nw) / (8.0 * ((need_c_in ? (double)M * nw : 0.0) + Kw * nw));
+      const double rp = (2.0 * M * Kw * nw) / (8.0 * ((c_costs ? (double)M * nw : 0.0) + Kw * nw));
       pick_slab = rs > rp;
     }
     if (pick_slab) {
@@ -102,6 +111,7 @@ std::vector<HostPlanItem> make_order(int M, const std::vector<int>& nb, const st
       for (int p = 0; p < aP; p++) order.push_back({s, p, s + 1});
     } else {
       const int p = aP++;
+      if (need_c_in && defer_c && S > 1 && !phase_b && aS < S) *deferred = aP;  // opened during the start-up phase
       if (merge_k && aS == S && S > 1) {
         order.push_back({0, p, S});  // all of A is resident: the whole K in one call (one epilogue per tile, one launch)
       } else {
@@ -115,7 +125,7 @@ std::vector<HostPlanItem> make_order(int M, const std::vector<int>& nb, const st
 // the three streams, exactly as run_host_single queues them: H2D in need-order, kernels in `order`, D2H of a panel
 // after its last call
 double simulate(const Model& m, int M, const std::vector<int>& nb, const std::vector<int>& kb,
-                const std::vector<HostPlanItem>& order, bool need_c_in) {
+                const std::vector<HostPlanItem>& order, bool need_c_in, int deferred) {
   const int P = (int)nb.size() - 1, S = (int)kb.size() - 1;
   std::vector<char> a_sent(S, 0), c_sent(P, 0);
   std::vector<int> last(P, -1);
@@ -127,9 +137,13 @@ double simulate(const Model& m, int M, const std::vector<int>& nb, const std::ve
     th = std::max(th, i * m.t_issue);  // nothing starts before the host has queued it
     for (int s = order[i].s; s < order[i].s_end; s++)
       if (!a_sent[s]) { th += 8.0 * M * (kb[s + 1] - kb[s]) / m.h2d + m.t_copy; a_sent[s] = 1; }
-    if (need_c_in && !c_sent[p]) { th += 8.0 * M * nc / m.h2d + m.t_copy; c_sent[p] = 1; }
+    if (need_c_in && p >= deferred && !c_sent[p]) { th += 8.0 * M * nc / m.h2d + m.t_copy; c_sent[p] = 1; }
     th += 8.0 * kc * nc / m.h2d + m.t_copy;
     tc = std::max(tc, th) + m.kernel(M, (int)nc, (int)kc);
+    if (need_c_in && p < deferred && i == last[p]) {  // C arrives behind the last B block; then C += beta * C_in
+      th += 8.0 * M * nc / m.h2d + m.t_copy;
+      tc = std::max(tc, th) + 24.0 * M * nc / m.hbm + m.t_kernel * 0.5;
+    }
     if (i == last[p]) td = std::max(td, tc) + 8.0 * M * nc / m.d2h + m.t_copy;
   }
   return std::max(td, tc);
@@ -168,6 +182,7 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
   const double need_cols = 1.3 * 4.0 * m.flops_per_s() / m.h2d;
   // whole-K calls in phase C; env switches for A/B measurements
   const bool merge_k = getenv("DGEMM_B200_PLAN_MERGE_K") ? atoi(getenv("DGEMM_B200_PLAN_MERGE_K")) != 0 : true;
+  const bool defer_ok = need_c_in && (getenv("DGEMM_B200_PLAN_DEFER_C") ? atoi(getenv("DGEMM_B200_PLAN_DEFER_C")) != 0 : true);
   best.predicted_ms = 1e300;
   // lead-in pieces: none, 2 / 4 / 6 equal ones, or geometric growth towards the main width
   static const std::vector<int> kLeads[] = {{}, {256, 256}, {256, 256, 256, 256}, {256, 256, 256, 256, 256, 256},
@@ -189,13 +204,18 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
             if (wk < lw || (wk >= 2 * K && wk > 256)) continue;
             const std::vector<int> kb = make_bounds(K, lead, wk, {}, Model::BK_);
             if ((nb.size() - 1) * (kb.size() - 1) > (size_t)max_items) continue;
-            std::vector<HostPlanItem> order = make_order(M, nb, kb, need_c_in, need_cols, merge_k);
-            const double t = simulate(m, M, nb, kb, order, need_c_in);
-            if (t < best.predicted_ms * 0.999) {  // ties: keep the earlier (coarser lead-in, fewer pieces) candidate
-              best.predicted_ms = t;
-              best.nb = nb;
-              best.kb = kb;
-              best.order.swap(order);
+            for (int dc = 0; dc <= (defer_ok ? 1 : 0); dc++) {
+              int deferred = 0;
+              std::vector<HostPlanItem> order = make_order(M, nb, kb, need_c_in, need_cols, merge_k, dc != 0, &deferred);
+              if (dc && deferred == 0) continue;
+              const double t = simulate(m, M, nb, kb, order, need_c_in, deferred);
+              if (t < best.predicted_ms * 0.999) {  // ties: keep the earlier (coarser lead-in, fewer pieces) candidate
+                best.predicted_ms = t;
+                best.nb = nb;
+                best.kb = kb;
+                best.order.swap(order);
+                best.deferred_panels = deferred;
+              }
             }
           }
         }

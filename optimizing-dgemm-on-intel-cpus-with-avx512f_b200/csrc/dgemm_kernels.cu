@@ -446,6 +446,18 @@ __global__ void scale_c_kernel(double* C, int M, int N, long long ldc, double be
   }
 }
 
+// C (M x N, ldc) += beta * X (M x N, ldx): the deferred beta*C term of the host pipeline's start-up panels
+// (dgemm_hostplan.cpp).  HBM-bound, 24 bytes per element.
+__global__ void __launch_bounds__(256)
+add_scaled_kernel(double* __restrict__ C, long long ldc, const double* __restrict__ X, long long ldx, int M, int N,
+                  double beta) {
+  for (int c = blockIdx.x; c < N; c += gridDim.x) {
+    double* cc = C + (long long)c * ldc;
+    const double* xc = X + (long long)c * ldx;
+    for (int r = threadIdx.x; r < M; r += 256) cc[r] = fma(beta, xc[r], cc[r]);
+  }
+}
+
 // dst (rows x cols, ldd) = src (rows x cols, lds), column-major, 8-byte elements: brings an operand with an odd leading
 // dimension or an 8-byte-aligned base into a TMA-describable layout (run_device's realign pre-pass).  HBM-bound.
 __global__ void __launch_bounds__(256)
@@ -606,6 +618,14 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || beta == 1.0) return cudaSuccess;
   scale_c_kernel<<<num_sms * 4, 256, 0, stream>>>(C, M, N, ldc, beta);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_add_scaled(double* C, long long ldc, const double* X, long long ldx, int M, int N, double beta,
+                              int num_sms, cudaStream_t stream) {
+  if (M <= 0 || N <= 0) return cudaSuccess;
+  add_scaled_kernel<<<std::min(N, num_sms * 8), 256, 0, stream>>>(C, ldc, X, ldx, M, N, beta);
   g_launches++;
   return cudaGetLastError();
 }

@@ -77,3 +77,14 @@ def test_plan_rejects_bad_arguments():
         dg.host_plan(-1, 4, 4)
     with pytest.raises(dg.DgemmError):
         dg.host_plan(16384, 16384, 16384, cap=16)
+
+
+def test_deferred_c_only_when_c_is_read():
+    """beta != 0 on a large problem: the start-up panels are opened without their C (it is added after their last
+    call), so the first device call waits for one small slab of A and one B block only.  beta == 0: nothing to defer."""
+    nb, kb, order, ms1 = dg.host_plan(16384, 16384, 16384, 1.0, 1.0)
+    d = dg.host_plan.deferred_panels
+    assert 1 <= d < len(nb) - 1
+    assert all(p < d for (_, p, _) in order[:d])          # the first calls open the deferred panels
+    dg.host_plan(16384, 16384, 16384, 1.0, 0.0)
+    assert dg.host_plan.deferred_panels == 0
