@@ -518,51 +518,86 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
 
     copy_s, d2h_s = torch.cuda.Stream(), torch.cuda.Stream()
     from dgemm_b200.sharding import partition, slab_order
-    SP = 4 if ncols >= 4 * 256 else 1
-    sp = partition(ncols, SP, 128)
+    # column sub-panels of this rank's panel: four main pieces and two narrow last ones (short exposed last D2H)
+    tails = [384, 128] if ncols >= 4096 else []
+    sp = partition(ncols - sum(tails), 4 if ncols - sum(tails) >= 4 * 256 else 1, 128)
+    for t in tails:
+        sp.append(sp[-1] + t)
+    SP = len(sp) - 1
     order = [g for g in slab_order(rank, N) if kb[g + 1] > kb[g]] if N > 1 else []
+    # the own K-slab goes in as sub-slabs so that the first call waits for a quarter of it
+    Q = 4 if (k1 - k0) >= 4 * 512 else 1
+    qb = [k0 + x for x in partition(k1 - k0, Q, 16)]
+    X = torch.empty(M * max(ncols, 1), dtype=torch.float64, device=dev) if (N > 1 and beta != 0.0) else None
 
     def one_pipelined():
-        """Rank-local 2-D pipeline: (K-slab, column sub-panel) calls in slab-major order on the compute stream; H2D of
-        the own A slab, the C sub-panels and the B blocks queued in need-order on a copy stream; every C sub-panel
-        goes back on a third stream as soon as its last slab is done.  The NVLink pull of slab i+1 rides on the first
-        call of slab i."""
+        """Rank-local pipeline on three streams.  Compute: (K-slab, column sub-panel) calls in slab-major order, the
+        own slab first and in Q sub-slabs.  H2D, in need-order: own A sub-slabs with their B blocks, the B blocks of
+        the other slabs, and LAST the C sub-panels — C is deferred: every sub-panel starts with beta = 0 and gets
+        beta*C_in added (dgemm_b200_add_scaled) after its last slab, so the start of the pipeline waits for a quarter
+        slab of A and one B block only.  Every C sub-panel goes back as soon as it is finished.  The NVLink pull of
+        slab i+1 rides on a call of slab i (the LAST call of the own slab for the first pull: by then every owner's
+        slab has reached its HBM, which the stream-ordered all_reduce in front of that call guarantees)."""
         cptr = copy_s.cuda_stream
         copy_s.wait_stream(stream)
-        dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, cptr))
-        ev_a = copy_s.record_event()
-        ev_c, ev_b = [], {}
-        for i, g in enumerate(order):
+        ev_b = {}
+        for q in range(Q):
+            ka, kc = qb[q], qb[q + 1] - qb[q]
+            if kc <= 0:
+                continue
+            dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * ka * M, M, hA.data_ptr() + 8 * (ka - k0) * M, M, M, kc, cptr))
             for j in range(SP):
                 c0, nc = sp[j], sp[j + 1] - sp[j]
-                if i == 0:  # C sub-panel j right before the first call that needs it, not all of C up front
-                    dg._check(dg.lib.dgemm_b200_h2d(Cm.data_ptr() + 8 * c0 * M, M, hC.data_ptr() + 8 * c0 * M, M, M, nc, cptr))
-                    ev_c.append(copy_s.record_event())
+                off = 8 * (c0 * K + ka)
+                dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr() + off, K, hB.data_ptr() + off, K, kc, nc, cptr))
+                ev_b[(0, q, j)] = copy_s.record_event()
+        ev_a = copy_s.record_event()
+        for i, g in enumerate(order):
+            if i == 0:
+                continue
+            for j in range(SP):
+                c0, nc = sp[j], sp[j + 1] - sp[j]
                 off = 8 * (c0 * K + kb[g])
                 dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr() + off, K, hB.data_ptr() + off, K, kb[g + 1] - kb[g], nc, cptr))
-                ev_b[(i, j)] = copy_s.record_event()
-        stream.wait_event(ev_a)
-        dist.all_reduce(token)  # every owner's K-slab is in its HBM before anyone pulls it
-        for i, g in enumerate(order):
-            kc = kb[g + 1] - kb[g]
+                ev_b[(i, 0, j)] = copy_s.record_event()
+        ev_x = []
+        if X is not None:
             for j in range(SP):
                 c0, nc = sp[j], sp[j + 1] - sp[j]
-                if nc <= 0:
-                    continue
-                stream.wait_event(ev_b[(i, j)])
-                if i == 0:
-                    stream.wait_event(ev_c[j])
-                src = dst = nbytes = 0
-                if j == 0 and i + 1 < len(order):
-                    nx = order[i + 1]
-                    src, dst = peers[nx] + 8 * kb[nx] * M, A_ptr + 8 * kb[nx] * M
-                    nbytes = 8 * (kb[nx + 1] - kb[nx]) * M
-                dg.dgemm_device_fetch(M, nc, kc, alpha, A_ptr + 8 * kb[g] * M, M, B.data_ptr() + 8 * (c0 * K + kb[g]), K,
-                                      beta if i == 0 else 1.0, Cm.data_ptr() + 8 * c0 * M, M, sptr, src, dst, nbytes)
-                if i == len(order) - 1:
-                    d2h_s.wait_event(stream.record_event())
-                    dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr() + 8 * c0 * M, M, Cm.data_ptr() + 8 * c0 * M, M, M, nc,
-                                                    d2h_s.cuda_stream))
+                dg._check(dg.lib.dgemm_b200_h2d(X.data_ptr() + 8 * c0 * M, M, hC.data_ptr() + 8 * c0 * M, M, M, nc, cptr))
+                ev_x.append(copy_s.record_event())
+        last_i = len(order) - 1
+        js = [j for j in range(SP) if sp[j + 1] > sp[j]]
+        for i, g in enumerate(order):
+            subs = [(qb[q], qb[q + 1] - qb[q], q) for q in range(Q)] if i == 0 else [(kb[g], kb[g + 1] - kb[g], 0)]
+            subs = [t for t in subs if t[1] > 0]
+            for si, (ka, kc, q) in enumerate(subs):
+                for j in js:
+                    c0, nc = sp[j], sp[j + 1] - sp[j]
+                    stream.wait_event(ev_b[(i, q, j)])
+                    src = dst = nbytes = 0
+                    if i + 1 < len(order):
+                        first_pull = i == 0 and si == len(subs) - 1 and j == js[-1]
+                        if first_pull:
+                            stream.wait_event(ev_a)
+                            dist.all_reduce(token)  # every owner's K-slab is in its HBM before anyone pulls it
+                        if first_pull or (i > 0 and j == js[0]):
+                            nx = order[i + 1]
+                            src, dst = peers[nx] + 8 * kb[nx] * M, A_ptr + 8 * kb[nx] * M
+                            nbytes = 8 * (kb[nx + 1] - kb[nx]) * M
+                    first_call = i == 0 and si == 0
+                    b_eff = (0.0 if X is not None else beta) if first_call else 1.0
+                    dg.dgemm_device_fetch(M, nc, kc, alpha, A_ptr + 8 * ka * M, M, B.data_ptr() + 8 * (c0 * K + ka), K,
+                                          b_eff, Cm.data_ptr() + 8 * c0 * M, M, sptr, src, dst, nbytes)
+                    if i == last_i and si == len(subs) - 1:
+                        if X is not None:
+                            stream.wait_event(ev_x[j])
+                            dg.add_scaled(M, nc, beta, X.data_ptr() + 8 * c0 * M, M, Cm.data_ptr() + 8 * c0 * M, M, sptr)
+                        d2h_s.wait_event(stream.record_event())
+                        dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr() + 8 * c0 * M, M, Cm.data_ptr() + 8 * c0 * M, M, M, nc,
+                                                        d2h_s.cuda_stream))
+        if len(order) == 1:
+            stream.wait_event(ev_a)
         dist.all_reduce(token)  # nobody still reads a slab when its owner overwrites it in the next pass
         d2h_s.synchronize()
         stream.synchronize()
@@ -610,7 +645,8 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
             "api": "mydgemm_gpu_v20(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC) with pinned host pointers" if N == 1 else
                    "per rank: dgemm_b200_h2d (own K-slab of A, B/C panels) + sharded step ("
                    + ("dgemm_b200_device_fetch, fused NVLink pull; (slab, sub-panel) calls pipelined against H2D/D2H "
-                      "on three streams" if fused else "ncclBroadcast + dgemm_b200_device")
+                      "on three streams, own slab in sub-slabs, C deferred (dgemm_b200_add_scaled after the last slab)"
+                      if fused else "ncclBroadcast + dgemm_b200_device")
                    + ") + dgemm_b200_d2h, pinned host buffers"}
 
 

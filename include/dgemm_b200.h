@@ -92,6 +92,12 @@ int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double *dA, lo
 int dgemm_b200_device_op(int layout, int transa, int transb, int M, int N, int K, double alpha, const double *dA,
                          long long lda, const double *dB, long long ldb, double beta, double *dC, long long ldc,
                          void *stream);
+/* C (M x N, ldc) += beta * X (M x N, ldx), device pointers, asynchronous on `stream`.  The "deferred C" step of a
+ * pipelined caller: start the panel's DGEMM calls with beta = 0 while C is still on its way over PCIe, add beta*C_in
+ * after the last one (mydgemm_gpu_v20 does this internally; bench.py's multi-GPU end-to-end pipeline uses this entry).
+ * The reference applies beta first (scale_c_k18, kernel18.h:12-46, 644); the sum is the same up to rounding. */
+int dgemm_b200_add_scaled(int M, int N, double beta, const double *dX, long long ldx, double *dC, long long ldc,
+                          void *stream);
 /* DGEMM fused with an NVLink fetch: while the FP64 tensor-core warps compute this call, spare warps of the same
  * kernel copy fetch_bytes from fetch_src to fetch_dst (16-byte aligned, multiple of 16).  fetch_src is normally a
  * PEER GPU's buffer (dgemm_b200_ipc_open / peer access): the multi-GPU layer uses it to pull the NEXT K-slab of A

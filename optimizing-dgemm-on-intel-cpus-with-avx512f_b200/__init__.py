@@ -35,7 +35,7 @@ EXPORTS = [
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
     "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_host_plan",
-    "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op",
+    "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled",
 ]
 
 
@@ -76,6 +76,7 @@ lib.dgemm_b200_cblas_dgemm.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_i
                                        _vp, C.c_int, C.c_double, _vp, C.c_int]
 lib.dgemm_b200_cblas_dgemm.restype = None
 lib.dgemm_b200_device_op.argtypes = [C.c_int, C.c_int, C.c_int] + _DEV_ARGS + [_vp]
+lib.dgemm_b200_add_scaled.argtypes = [C.c_int, C.c_int, C.c_double, _vp, _ll, _vp, _ll, _vp]
 _ip = C.POINTER(C.c_int)
 lib.dgemm_b200_host_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _ip, _ip, _ip, _ip, _ip, _ip,
                                      C.c_int, C.POINTER(C.c_double), _ip]
@@ -122,6 +123,11 @@ def cblas_dgemm(layout, transa, transb, M, N, K, alpha, A, lda, B, ldb, beta, Cm
     pc = Cm.ctypes.data if isinstance(Cm, np.ndarray) else int(Cm)
     lib.dgemm_b200_cblas_dgemm(layout, transa, transb, M, N, K, alpha, pa, lda, pb, ldb, beta, pc, ldc)
     _check()
+
+
+def add_scaled(M, N, beta, dX, ldx, dC, ldc, stream=0):
+    """C += beta * X on device pointers (the deferred-C step of a pipelined caller)."""
+    _check(lib.dgemm_b200_add_scaled(M, N, float(beta), int(dX), ldx, int(dC), ldc, int(stream) or None))
 
 
 def dgemm_device_op(layout, transa, transb, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0):

@@ -698,6 +698,20 @@ int dgemm_b200_device_op(int layout, int transa, int transb, int M, int N, int K
   return run_device_op(*c, q.ta, q.tb, q.M, q.N, K, alpha, q.A, q.lda, q.B, q.ldb, beta, dC, ldc, (cudaStream_t)stream);
 }
 
+int dgemm_b200_add_scaled(int M, int N, double beta, const double* dX, long long ldx, double* dC, long long ldc,
+                          void* stream) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  if (M < 0 || N < 0 || ldx < std::max(1, M) || ldc < std::max(1, M))
+    return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_add_scaled: M=%d N=%d ldx=%lld ldc=%lld", M, N, ldx, ldc);
+  if (M == 0 || N == 0 || beta == 0.0) return ok();
+  if (!dX || !dC) return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_add_scaled: NULL operand");
+  DeviceCtx* c;
+  int st = current_ctx(&c);
+  if (st) return st;
+  CU_TRY(dg::launch_add_scaled(dC, ldc, dX, ldx, M, N, beta, c->num_sms, (cudaStream_t)stream));
+  return ok();
+}
+
 int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* panels, int* n_panels, int* slabs,
                          int* n_slabs, int* order, int* n_items, int cap, double* predicted_ms, int* deferred_panels) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);
