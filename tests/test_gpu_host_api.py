@@ -88,3 +88,22 @@ def test_pageable_staging_is_byte_exact(dg, shape, pad, alpha, beta, monkeypatch
         gu.check(M, N, K, alpha, A, B, beta, C0, Cg)
         outs.append(Cg)
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[1], outs[2])
+
+
+def test_add_scaled_is_exact(dg):
+    """dgemm_b200_add_scaled: C += beta*X, one fma per entry, padding rows untouched (the deferred-C step)."""
+    M, N, pad = 777, 130, 3
+    Cm = ol.fill_signed(M, N, M + pad, 41, pad_value=-777.0)
+    X = ol.fill_signed(M, N, M + 1, 42, pad_value=5.0)
+    dC, dX = gu.DevMat(dg, Cm), gu.DevMat(dg, X)
+    try:
+        dg.add_scaled(M, N, 0.5, dX.ptr, dX.ld, dC.ptr, dC.ld)
+        assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+        out = dC.to_host()
+    finally:
+        dC.free(); dX.free()
+    want = Cm.copy(order="F")
+    want[:M, :] = np.float64(0.5) * X[:M, :] + Cm[:M, :]       # 0.5*x is exact, so fma == multiply-then-add here
+    assert np.array_equal(out, want)
+    with pytest.raises(dg.DgemmError):
+        dg.add_scaled(8, 8, 1.0, dX.ptr, 4, dC.ptr, 8)          # ldx < M
