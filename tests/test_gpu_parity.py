@@ -181,3 +181,27 @@ def test_k_lockstep_changes_no_bits(dg, monkeypatch):
     dA.free(); dB.free()
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
     gu.check(M, N, K, 1.0, A, B, 1.0, C0, outs[0])
+
+
+def _random_cases(n, seed):
+    rng = np.random.default_rng(seed)
+    cases = []
+    for _ in range(n):
+        M, N, K = (int(rng.integers(1, 700)) for _ in range(3))
+        pad = tuple(int(rng.integers(0, 4)) for _ in range(3))
+        alpha = float(rng.choice([1.0, -1.0, 2.5, 0.5]))
+        beta = float(rng.choice([0.0, 1.0, 0.5, -2.0]))
+        cases.append((M, N, K, pad, alpha, beta))
+    return cases
+
+
+@pytest.mark.parametrize("case", _random_cases(24, 2024), ids=lambda c: "x".join(str(v) for v in c[:3]))
+def test_random_shapes_device_and_host_entries(dg, case):
+    """Seeded random shapes, paddings and scalars through BOTH entries (device pointers: TMA / realigned / cp.async
+    loaders as the alignment dictates; host pointers: planner, staging, deferred C), each against the oracle."""
+    M, N, K, pad, alpha, beta = case
+    gu.run_device(dg, M, N, K, alpha, beta, pad=pad, c_fill=np.nan if beta == 0.0 else None)
+    A, B, C0 = gu.make_inputs(M, N, K, pad)
+    Cg = C0.copy(order="F")
+    dg.mydgemm_gpu_v20(M, N, K, alpha, A, A.shape[0], B, B.shape[0], beta, Cg, Cg.shape[0])
+    gu.check(M, N, K, alpha, A, B, beta, C0, Cg)
