@@ -16,6 +16,7 @@
 
 #include <cuda.h>
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 
 namespace dg {
@@ -550,9 +551,10 @@ bool tma_eligible(const Params& P) {
          P.lda * 8 < (1ll << 40) && P.ldb * 8 < (1ll << 40);
 }
 
-static int g_launches = 0;
-int launch_count() { return g_launches; }
-void reset_launch_count() { g_launches = 0; }
+// counted from every host thread that launches (mydgemm_gpu_v21 drives one thread per GPU)
+static std::atomic<int> g_launches{0};
+int launch_count() { return g_launches.load(std::memory_order_relaxed); }
+void reset_launch_count() { g_launches.store(0, std::memory_order_relaxed); }
 
 constexpr int TMA_STAGES = 6;
 constexpr int CPA_STAGES = 4;
