@@ -170,6 +170,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
       ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// TMA: 1-D bulk copy global -> shared (multiple of 16 bytes, 16-byte aligned), completion on an mbarrier.  SASS: UBLKCP
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// Orders generic-proxy accesses to global memory (st.global / ld.acquire) against async-proxy ones (bulk copies):
+// the stream-K partials are written with st.global by one CTA and read back by another CTA's bulk copy.
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
@@ -445,6 +454,27 @@ __device__ __forceinline__ void add_partial_cg(double (&acc)[FRAG_N][FRAG_M][2],
       double2 v = __ldcg(p + (i * FRAG_M + j) * CONSUMER_THREADS);
       acc[i][j][0] += v.x; acc[i][j][1] += v.y;
     }
+}
+
+// stream-K partial that the producer brought into a pipeline stage with bulk_load_1d: chunk c of the [reg][thread]
+// layout holds fragments q = c*FPC .. c*FPC+FPC-1 for all consumer threads (16-byte LDS, conflict free)
+constexpr int PARTIAL_CHUNKS = (BM * BN * 8) / STAGE_BYTES;              // 4 stages per 128 KB partial
+constexpr int PARTIAL_FPC = (FRAG_N * FRAG_M) / PARTIAL_CHUNKS;          // fragments per chunk
+static_assert(PARTIAL_CHUNKS * STAGE_BYTES == BM * BN * 8 && PARTIAL_FPC * PARTIAL_CHUNKS == FRAG_N * FRAG_M &&
+              PARTIAL_FPC * CONSUMER_THREADS * 16 == STAGE_BYTES, "partial tile must split into whole stages");
+__device__ __forceinline__ void add_partial_smem(double (&acc)[FRAG_N][FRAG_M][2], uint32_t stage, int chunk, int tid) {
+#pragma unroll
+  for (int c = 0; c < PARTIAL_CHUNKS; c++) {
+    if (c != chunk) continue;   // chunk is a compile-time constant at every call site (unrolled loop)
+#pragma unroll
+    for (int jj = 0; jj < PARTIAL_FPC; jj++) {
+      const int q = c * PARTIAL_FPC + jj, i = q / FRAG_M, j = q % FRAG_M;
+      double x, y;
+      asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(x), "=d"(y)
+                   : "r"(stage + (uint32_t)(jj * CONSUMER_THREADS + tid) * 16u) : "memory");
+      acc[i][j][0] += x; acc[i][j][1] += y;
+    }
+  }
 }
 
 // tile index (rasterised order) -> tile coordinates

@@ -142,6 +142,27 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tma_load_2d(dstB, &tmB, full, k0, n0);   // B: one box of 16(k) x 128(n)
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
+        if (sg.kind == SEG_SK_OWNER && !P.sk_parallel) {
+          // serial stream-K fix-up: the partials of the ranges that hold the rest of this tile come in through the
+          // SAME ring, four stages per partial, as soon as their flag is up, so the owner's consumers find them in
+          // shared memory when their main loop ends instead of paying two global round trips per partial.  An owner
+          // segment is the last of its range, and a contributor never waits for anybody: no cycle.
+          const long long total = (long long)P.sk_tiles * P.k_tiles;
+          const long long tile_end = (long long)(sg.tile - P.sk_tile0 + 1) * P.k_tiles;
+          for (int r = sg.slot + 1; r < (int)gridDim.x && total * r / gridDim.x < tile_end; r++) {
+            while (ld_acquire_gpu(P.sk_flags + r) != P.sk_epoch) __nanosleep(64);
+            fence_proxy_async_global();
+            const char* src = reinterpret_cast<const char*>(P.workspace + (size_t)r * (BM * BN));
+#pragma unroll 1
+            for (int c = 0; c < PARTIAL_CHUNKS; c++) {
+              mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
+              const uint32_t full = bars + 8 * s;
+              mbar_arrive_expect_tx(full, STAGE_BYTES);
+              bulk_load_1d(smem_base + s * STAGE_BYTES, src + (size_t)c * STAGE_BYTES, STAGE_BYTES, full);
+              if (++s == STAGES) { s = 0; ph ^= 1; }
+            }
+          }
+        }
       }
     } else if (warp == CONSUMER_WARPS + 1) {
       // ---------------- warp 9: pull the C tile of every segment that ends in an epilogue into L2 -------------------
@@ -252,16 +273,21 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       } else if (sg.kind == SEG_SK_CONTRIB) {
         store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
         __threadfence();
+        fence_proxy_async_global();   // the owner reads this slot with a bulk copy (async proxy)
         consumer_bar_sync();
         if (tid == 0) st_release_gpu(P.sk_flags + sg.slot, P.sk_epoch);
       } else {  // SEG_SK_OWNER: add the partials of the ranges that hold the rest of this tile, in range order
         const long long total = (long long)P.sk_tiles * P.k_tiles;
         const long long tile_end = (long long)(sg.tile - P.sk_tile0 + 1) * P.k_tiles;
         for (int r = sg.slot + 1; r < (int)gridDim.x && total * r / gridDim.x < tile_end; r++) {
-          if (tid == 0)
-            while (ld_acquire_gpu(P.sk_flags + r) != P.sk_epoch) __nanosleep(64);
-          consumer_bar_sync();
-          add_partial_cg(acc, P.workspace + (size_t)r * (BM * BN), tid);
+#pragma unroll
+          for (int c = 0; c < PARTIAL_CHUNKS; c++) {   // the producer fetched partial r into four stages of the ring
+            mbar_wait(bars + 8 * s, ph);
+            add_partial_smem(acc, smem_base + s * STAGE_BYTES, c, tid);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars + 8 * (STAGES + s));
+            if (++s == STAGES) { s = 0; ph ^= 1; }
+          }
         }
         epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       }
