@@ -251,6 +251,13 @@ int check_args(int M, int N, int K, const void* A, long long lda, const void* B,
   return DGEMM_B200_OK;
 }
 
+enum { ODD_SPLIT = 0, ODD_REALIGN = 1, ODD_CPASYNC = 2 };
+int odd_ld_mode() {   // DGEMM_B200_ODD_LD, read per call (tests and probes toggle it); see run_device
+  const char* e = getenv("DGEMM_B200_ODD_LD");
+  if (getenv("DGEMM_B200_NO_REALIGN") != nullptr || (e && !strcmp(e, "cpasync"))) return ODD_CPASYNC;
+  return (e && !strcmp(e, "realign")) ? ODD_REALIGN : ODD_SPLIT;
+}
+
 // the device-side DGEMM on context c (current device must be c.dev)
 struct Fetch {
   const void* src = nullptr;
@@ -271,17 +278,29 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
     return ok();
   }
   dg::Params P;
-  P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
+  P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb; P.M = M; P.N = N; P.K = K;
   bool tma_ok = dg::tma_eligible(P);
   bool realigned = false;
+  // Operands one tensor map cannot describe (odd leading dimension, 8-byte aligned base).  DGEMM_B200_ODD_LD (read per
+  // call) = "split" (default): the TMA kernel reads them in place, by column parity: the parity whose columns start on
+  // a 16-byte boundary through its own tensor map, the other one through cp.async issued by two spare warps
+  // (dgemm_tma_ws_split_kernel); "realign": copy them once into an even-LD scratch and run the plain TMA kernel (the
+  // previous default); "cpasync": the cp.async kernel (also what DGEMM_B200_NO_REALIGN=1 has always meant).
+  // Measured (tools/odd_ld_probe.py, split vs realign vs cp.async kernel, TFLOP/s): 500x501x499 9.1 / 8.2 / 6.0,
+  // 1000x1003x997 22.7 / 21.5 / 19.3, 2001x2003x1999 31.5 / 30.5 / 23.6, 4097x4096x4095 34.2 / 34.1 / 25.6, 8192^3 with
+  // LD 8193: 35.6 / 35.9 / 29.3 -- the copy is O(n^2) and fades, while two cp.async halves keep costing ~2 % of the
+  // main loop.  So "split" hands a call with two or more misaligned halves to the realign pre-pass from 4e11 flops up,
+  // if the scratch can be had; it never needs scratch memory otherwise.
+  const bool odd_cpasync = odd_ld_mode() == ODD_CPASYNC, odd_realign = odd_ld_mode() == ODD_REALIGN;
+  const bool split_ok = !tma_ok && dg::tma_split_ok(P);
+  const bool can_split = split_ok && !odd_cpasync && !odd_realign && fetch.bytes == 0;  // (the fused fetch needs warps 10-11)
+  const double flops = 2.0 * M * (double)N * K;
   static const double kRealignMinFlops = getenv("DGEMM_B200_REALIGN_MIN_FLOPS") ? atof(getenv("DGEMM_B200_REALIGN_MIN_FLOPS")) : 1e8;
-  if (variant == dg::VARIANT_AUTO && !tma_ok && 2.0 * M * (double)N * K >= kRealignMinFlops && !getenv("DGEMM_B200_NO_REALIGN")) {
-    // Operands that a tensor map cannot describe (odd leading dimension or an 8-byte-aligned base): copy the offending
-    // operand(s) once, device to device (realign_kernel), into an even-LD scratch and run the TMA kernel instead of the
-    // cp.async kernel.  The copy moves 16 bytes per element against 2*N (or 2*M) flops per element; it pays from about
-    // 1e8 flops up (500x501x499: 5.9 -> 8.3, 1000x1003x997: 19.3 -> 20.7, 2001x2003x1999: 23.5 -> 30.1,
-    // 4097x4096x4095: 25.5 -> 34.0 TFLOP/s; tools/odd_ld_probe.py).  Below that, or if the scratch cannot be
-    // allocated, the cp.async kernel runs.
+  const double kSplitMaxFlops2 = getenv("DGEMM_B200_SPLIT_MAX_FLOPS2") ? atof(getenv("DGEMM_B200_SPLIT_MAX_FLOPS2")) : 4e11;  // per call
+  const bool prefer_realign = !can_split || (dg::tma_mis_halves(P) >= 2 && flops >= kSplitMaxFlops2);
+  if (variant == dg::VARIANT_AUTO && !tma_ok && !odd_cpasync && prefer_realign && flops >= kRealignMinFlops) {
+    // copy the offending operand(s) once, device to device (realign_kernel, 16 bytes per element against 2*N or 2*M
+    // flops per element), into an even-LD scratch.  If the scratch cannot be allocated: split kernel, else cp.async.
     const bool a_bad = ((uintptr_t)dA % 16 != 0) || (lda % 2 != 0), b_bad = ((uintptr_t)dB % 16 != 0) || (ldb % 2 != 0);
     const long long ldaR = (M + 1) & ~1ll, ldbR = (K + 1) & ~1ll;
     const int saved_status = g_status;
@@ -302,15 +321,18 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
       tma_ok = dg::tma_eligible(P);
       realigned = true;
     } else {
-      g_status = saved_status;  // out of memory for the scratch is not an error: fall through to cp.async
+      g_status = saved_status;  // out of memory for the scratch is not an error: split kernel or cp.async kernel
       g_errmsg[0] = 0;
       cudaGetLastError();
     }
   }
-  if (variant == dg::VARIANT_AUTO) variant = tma_ok ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  const bool use_split = can_split && !realigned;
+  if (variant == dg::VARIANT_AUTO) variant = (tma_ok || use_split) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   if (variant < 0 || variant > dg::VARIANT_DFMA) return fail(DGEMM_B200_ERR_BAD_ARG, "unknown kernel variant %d", variant);
-  if ((variant == dg::VARIANT_TMA || variant == dg::VARIANT_CPASYNC16) && !tma_ok)
+  if (variant == dg::VARIANT_CPASYNC16 && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
+  if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
+    return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d: unaligned operands need K >= 2 and N >= 2 for parity-split tensor maps", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
@@ -835,11 +857,14 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
   int st = current_ctx(&c);
   if (st) return st;
   dg::Params P;
-  P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb;
-  // (run_device realigns TMA-ineligible operands from 1e8 flops up and then runs the TMA kernel as well)
-  const bool realign = 2.0 * M * (double)N * K >= 1e8 && !getenv("DGEMM_B200_NO_REALIGN") &&
+  P.A = dA; P.B = dB; P.lda = lda; P.ldb = ldb; P.M = M; P.N = N; P.K = K;
+  // (run_device: TMA-ineligible operands go through parity-split tensor maps, or are realigned from 1e8 flops up, and
+  // the TMA kernel runs as well)
+  const bool tma_ok = dg::tma_eligible(P);
+  const bool split = !tma_ok && dg::tma_split_ok(P) && odd_ld_mode() == ODD_SPLIT;
+  const bool realign = !tma_ok && !split && odd_ld_mode() != ODD_CPASYNC && 2.0 * M * (double)N * K >= 1e8 &&
                        !getenv("DGEMM_B200_REALIGN_MIN_FLOPS");
-  const int v = (dg::tma_eligible(P) || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
+  const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms);
   if (variant) *variant = v;
   if (splits) *splits = P.splits;

@@ -91,7 +91,16 @@ struct Params {
   unsigned long long fetch_bytes;
   // ---- optional per-CTA timeline (debug / profiling aid; nullptr in normal use): 16 globaltimer stamps per CTA
   unsigned long long* timeline;
+  // ---- parity-split operands (TMA kernel, SPLIT != 0): an operand whose leading dimension is odd or whose base is only
+  // 8-byte aligned cannot be described by ONE tensor map (16-byte base and strides).  Its even and its odd columns can
+  // (stride 2*ld*8 is a multiple of 16) as long as the column start of that parity is 16-byte aligned; TMA rejects a
+  // box that starts 8 bytes off a 16-byte boundary (measured: "illegal instruction" with an odd inner coordinate), so a
+  // parity whose columns start at 8 mod 16 (a_mis / b_mis = 1) is staged with 8-byte cp.async by the two spare warps
+  // of the producer warpgroup instead, into the same swizzled layout and onto the same mbarrier.
+  int a_mis[2], b_mis[2];
 };
+// SPLIT template bits of dgemm_tma_ws_kernel
+enum { SPLIT_NONE = 0, SPLIT_A = 1, SPLIT_B = 2 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -105,6 +114,15 @@ __device__ __forceinline__ void stamp(const Params& P, int slot) {
 // ---- lane -> matrix index maps (see header comment) -------------------------------------------------------
 // row fragment (from B): mma row r = lane/4 feeds n = 8*t + kPermN(r)
 __device__ __forceinline__ int perm_n(int r) { return ((r & 3) << 1) | (r >> 2); }  // 0,2,4,6,1,3,5,7
+// With A split by k parity the k values a lane quad feeds change (see LaneOffsetsKS) and the B fragment loads need a
+// different row permutation to stay conflict free: 0,1,4,5,2,3,6,7 (tools/check_swizzle.py)
+__device__ __forceinline__ int perm_n_ks(int r) { return (r & 1) | ((r & 2) << 1) | ((r & 4) >> 1); }
+template <int SPLIT>
+__device__ __forceinline__ int perm_n_t(int r) { return (SPLIT & SPLIT_A) ? perm_n_ks(r) : perm_n(r); }
+// shared-memory B row of the CTA tile -> column of the tile.  B split by n parity: rows 0..63 hold the even columns,
+// rows 64..127 the odd ones (two TMA boxes of 64 columns each).
+template <int SPLIT>
+__device__ __forceinline__ int tile_col(int row) { return (SPLIT & SPLIT_B) ? (((row & 63) << 1) | (row >> 6)) : row; }
 // column fragment (from A): mma col c feeds m = 16*s + 4*f + kMapM(c)
 __device__ __forceinline__ int map_m(int c) { return (c & 1) | ((c & 2) << 2) | ((c & 4) >> 1); }  // 0,1,8,9,2,3,10,11
 
@@ -190,6 +208,11 @@ __device__ __forceinline__ void cp_async_zfill(uint32_t dst, const void* src, in
   else
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
+// makes the mbarrier track this thread's outstanding cp.async copies: one arrival (already counted in the barrier's
+// init count: .noinc) fires when all of them have landed
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -203,6 +226,60 @@ __device__ __forceinline__ uint32_t a_smem_off(int m_local, int k_local) {
 // B element (k_local, n_local): row n_local, 16-byte chunk (k_local/2) ^ (n_local & 7)
 __device__ __forceinline__ uint32_t b_smem_off(int k_local, int n_local) {
   return (uint32_t)(n_local * 128 + ((((k_local >> 1) ^ (n_local & 7))) << 4) + ((k_local & 1) << 3));
+}
+
+// ---- staging of a misaligned parity half by the helper warps (64 threads, t = 0..63), zero-filled at the edges -------
+constexpr int HELPER_THREADS = 64;
+__device__ __forceinline__ void cp_async_8(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+// A, k parity p: the 8 k-columns k0 + 2j + p of the stage x 128 rows -> smem rows p*8 + j of every 16-row sub-tile.
+// Thread t copies rows t and t + 64 of each column (a warp instruction reads 256 contiguous bytes).  Interior stages take
+// a straight-line path with precomputed offsets: the two helper warps share their SM sub-partitions with DMMA warps and
+// have about 2 us per stage; the generic index arithmetic alone made them the bottleneck when both operands are split.
+__device__ __forceinline__ void helper_copy_a_half(const Params& P, uint32_t dstA, int m0, int k0, int p, int t) {
+  const double* src = P.A + (long long)(k0 + p) * P.lda + m0 + t;
+  const long long step = 2 * P.lda;
+  const uint32_t base = dstA + (uint32_t)(t >> 4) * 2048u + (uint32_t)p * 1024u + (uint32_t)((t & 1) << 3);
+  const uint32_t c0 = (uint32_t)(t & 15) >> 1;
+  if ((m0 + BM <= P.M) && (k0 + BK <= P.K)) {
+#pragma unroll
+    for (int j = 0; j < BK / 2; j++) {
+      const uint32_t off = (uint32_t)j * 128u + ((c0 ^ (uint32_t)j) << 4);
+      cp_async_8(base + off, src + j * step);
+      cp_async_8(base + 4u * 2048u + off, src + j * step + 64);   // row t + 64: four sub-tiles further, same chunk
+    }
+    return;
+  }
+  // edge stage (last tile row / K tail): same addresses, zero fill for rows >= M and columns >= K
+  const bool r0 = m0 + t < P.M, r1 = m0 + t + 64 < P.M;
+#pragma unroll
+  for (int j = 0; j < BK / 2; j++) {
+    const uint32_t off = (uint32_t)j * 128u + ((c0 ^ (uint32_t)j) << 4);
+    const bool kc = k0 + 2 * j + p < P.K;
+    cp_async_zfill<8>(base + off, (r0 && kc) ? src + j * step : P.A, (r0 && kc) ? 8 : 0);
+    cp_async_zfill<8>(base + 4u * 2048u + off, (r1 && kc) ? src + j * step + 64 : P.A, (r1 && kc) ? 8 : 0);
+  }
+}
+// B, column parity p: the 64 columns n0 + 2c + p of the tile x 16 k -> smem rows p*64 + c.  Thread t copies k = t & 15
+// of columns c = (t >> 4) + 4e, e = 0..15.
+__device__ __forceinline__ void helper_copy_b_half(const Params& P, uint32_t dstB, int n0, int k0, int p, int t) {
+  const int c0 = t >> 4, kl = t & 15;
+  const double* src = P.B + (long long)(n0 + 2 * c0 + p) * P.ldb + k0 + kl;
+  const long long step = 8 * P.ldb;   // c += 4 -> n += 8
+  const uint32_t base = dstB + (uint32_t)(p * (BN / 2) + c0) * 128u + (uint32_t)((kl & 1) << 3);
+  const uint32_t x0 = (uint32_t)((kl >> 1) ^ c0) << 4, x1 = (uint32_t)((kl >> 1) ^ (c0 + 4)) << 4;   // row & 7 = c0 (+4)
+  if ((n0 + BN <= P.N) && (k0 + BK <= P.K)) {
+#pragma unroll
+    for (int e = 0; e < 16; e++) cp_async_8(base + (uint32_t)e * 512u + ((e & 1) ? x1 : x0), src + e * step);
+    return;
+  }
+  const bool kv = k0 + kl < P.K;   // edge stage: zero fill for k >= K and columns >= N
+#pragma unroll
+  for (int e = 0; e < 16; e++) {
+    const bool ok = kv && (n0 + 2 * (c0 + 4 * e) + p < P.N);
+    cp_async_zfill<8>(base + (uint32_t)e * 512u + ((e & 1) ? x1 : x0), ok ? src + e * step : P.B, ok ? 8 : 0);
+  }
 }
 
 // Per-lane fragment offsets, computed once per thread.
@@ -222,6 +299,37 @@ __device__ __forceinline__ LaneOffsets make_lane_offsets(int lane, int warp_m, i
   return lo;
 }
 
+// A split by k parity: a 16-row A sub-tile holds the even k in rows 0..7 and the odd k in rows 8..15 (two TMA boxes of
+// 8 k-columns each), i.e. k sits in row (k&1)*8 + (k>>1).  The lanes q = 0..3 of k-step kk then feed
+// k = 8*(kk>>1) + 2q + ((q^kk)&1)  ->  {0,3,4,7} {1,2,5,6} {8,11,12,15} {9,10,13,14}: four distinct rows mod 8 for A
+// (conflict free exactly like the unsplit layout) and both 8-byte halves of two 16-byte chunks for B.
+struct LaneOffsetsKS {
+  uint32_t a[4][2];  // [kk][f]
+  uint32_t b[4];     // [kk]
+};
+__device__ __forceinline__ int ks_k(int kk, int q) { return 8 * (kk >> 1) + 2 * q + ((q ^ kk) & 1); }
+__device__ __forceinline__ LaneOffsetsKS make_lane_offsets_ks(int lane, int warp_m, int warp_n) {
+  const int r = lane >> 2, q = lane & 3;
+  LaneOffsetsKS lo;
+#pragma unroll
+  for (int kk = 0; kk < 4; kk++) {
+    const int k = ks_k(kk, q);
+#pragma unroll
+    for (int f = 0; f < 2; f++) lo.a[kk][f] = a_smem_off(warp_m * WM + 4 * f + map_m(r), (k & 1) * 8 + (k >> 1));
+    lo.b[kk] = b_smem_off(k, warp_n * WN + perm_n_ks(r));
+  }
+  return lo;
+}
+template <int SPLIT> struct LaneOffsetsFor { typedef LaneOffsets type; };
+template <> struct LaneOffsetsFor<SPLIT_A> { typedef LaneOffsetsKS type; };
+template <> struct LaneOffsetsFor<SPLIT_A | SPLIT_B> { typedef LaneOffsetsKS type; };
+__device__ __forceinline__ void make_lane_offsets_t(LaneOffsets& lo, int lane, int warp_m, int warp_n) {
+  lo = make_lane_offsets(lane, warp_m, warp_n);
+}
+__device__ __forceinline__ void make_lane_offsets_t(LaneOffsetsKS& lo, int lane, int warp_m, int warp_n) {
+  lo = make_lane_offsets_ks(lane, warp_m, warp_n);
+}
+
 // Register fragments of one k-step (4 k): 8 column fragments from A, 4 row fragments from B.
 struct Frags {
   double a[FRAG_M];
@@ -231,6 +339,12 @@ __device__ __forceinline__ void load_frags(Frags& f, uint32_t sA, uint32_t sB, c
 #pragma unroll
   for (int j = 0; j < FRAG_M; j++)  // sub-tile j/2, half f = j&1; rows kk*4.. -> (kk>>1)*1024 + (kk&1)*512
     f.a[j] = lds_f64(sA + lo.a[kk & 1][j & 1] + (kk >> 1) * 1024 + (j >> 1) * 2048);
+#pragma unroll
+  for (int i = 0; i < FRAG_N; i++) f.b[i] = lds_f64(sB + lo.b[kk] + i * 1024);
+}
+__device__ __forceinline__ void load_frags(Frags& f, uint32_t sA, uint32_t sB, const LaneOffsetsKS& lo, int kk) {
+#pragma unroll
+  for (int j = 0; j < FRAG_M; j++) f.a[j] = lds_f64(sA + lo.a[kk][j & 1] + (j >> 1) * 2048);
 #pragma unroll
   for (int i = 0; i < FRAG_N; i++) f.b[i] = lds_f64(sB + lo.b[kk] + i * 1024);
 }
@@ -265,6 +379,7 @@ __device__ __forceinline__ void zero_acc(double (&acc)[FRAG_N][FRAG_M][2]) {
 // Fused epilogue: C = alpha*acc + beta*C on the lanes' own entries, straight from registers.
 // beta == 0 never reads C (BLAS convention; NaN/Inf in C are overwritten).  Rows >= M / cols >= N are
 // predicated off, so padding rows M..ldc-1 are never touched.
+template <int SPLIT = SPLIT_NONE>
 __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_M][2], const Params& P, int m0, int n0,
                                                int warp_m, int warp_n, int lane) {
   const int r = lane >> 2, q = lane & 3;
@@ -275,13 +390,14 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
   // Fast path (warp tile fully inside C, 16-byte aligned columns): straight-line code, 16 independent 16-byte loads
   // in flight per lane before the first use.  The predicated edge path below puts every load in its own basic
   // block, which serialises the round trips (measured: ~9 us per tile instead of ~2).
-  const bool inside = (m0 + warp_m * WM + WM <= P.M) && (n0 + warp_n * WN + WN <= P.N);
+  // (with B split by column parity a warp's columns are spread over the whole tile width)
+  const bool inside = (m0 + warp_m * WM + WM <= P.M) && (n0 + ((SPLIT & SPLIT_B) ? BN : warp_n * WN + WN) <= P.N);
   if (inside && !P.c_vec2) {
     // same, for a C whose columns are only 8-byte aligned (odd LDC or base): scalar accesses, still branch-free
 #pragma unroll
     for (int ip = 0; ip < FRAG_N; ip += 2) {
-      double* col0 = P.C + (long long)(n0 + warp_n * WN + ip * 8 + perm_n(r)) * P.ldc + mbase;
-      double* col1 = col0 + 8 * P.ldc;
+      double* col0 = P.C + (long long)(n0 + tile_col<SPLIT>(warp_n * WN + ip * 8 + perm_n_t<SPLIT>(r))) * P.ldc + mbase;
+      double* col1 = col0 + ((SPLIT & SPLIT_B) ? 16 : 8) * P.ldc;   // row + 8 stays in the same parity half
       double c[2][FRAG_M][2];
       if (use_c) {
 #pragma unroll
@@ -309,8 +425,8 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
   if (interior) {
 #pragma unroll
     for (int ip = 0; ip < FRAG_N; ip += 2) {
-      double* col0 = P.C + (long long)(n0 + warp_n * WN + ip * 8 + perm_n(r)) * P.ldc + mbase;
-      double* col1 = col0 + 8 * P.ldc;
+      double* col0 = P.C + (long long)(n0 + tile_col<SPLIT>(warp_n * WN + ip * 8 + perm_n_t<SPLIT>(r))) * P.ldc + mbase;
+      double* col1 = col0 + ((SPLIT & SPLIT_B) ? 16 : 8) * P.ldc;   // row + 8 stays in the same parity half
       double2 c[2][FRAG_M];
       if (use_c) {
 #pragma unroll
@@ -334,7 +450,7 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
   }
 #pragma unroll
   for (int i = 0; i < FRAG_N; i++) {
-    const int n = n0 + warp_n * WN + i * 8 + perm_n(r);
+    const int n = n0 + tile_col<SPLIT>(warp_n * WN + i * 8 + perm_n_t<SPLIT>(r));
     if (n >= P.N) continue;
     double* col = P.C + (long long)n * P.ldc;
     double c0[FRAG_M], c1[FRAG_M];
@@ -369,10 +485,11 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
 
 // Epilogue for ONE fragment (i, j) of the lane: used by the parallel stream-K fix-up, where a CTA finishes only a
 // slice of the tile.  Fully predicated (edges, unaligned C).
+template <int SPLIT = SPLIT_NONE>
 __device__ __forceinline__ void epilogue_frag(double a0, double a1, const Params& P, int m0, int n0, int warp_m,
                                               int warp_n, int lane, int i, int j) {
   const int r = lane >> 2, q = lane & 3;
-  const int n = n0 + warp_n * WN + i * 8 + perm_n(r);
+  const int n = n0 + tile_col<SPLIT>(warp_n * WN + i * 8 + perm_n_t<SPLIT>(r));
   const int m = m0 + warp_m * WM + map_m(2 * q) + (j >> 1) * 16 + (j & 1) * 4;
   if (n >= P.N || m >= P.M) return;
   double* p = P.C + (long long)n * P.ldc + m;

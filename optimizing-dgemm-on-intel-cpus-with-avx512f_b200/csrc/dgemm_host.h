@@ -18,6 +18,9 @@ enum Variant {
 };
 
 bool tma_eligible(const Params& P);
+int tma_split_bits(const Params& P);
+int tma_mis_halves(const Params& P);
+bool tma_split_ok(const Params& P);   // needs P.A, P.B, P.lda, P.ldb, P.K, P.N
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);

@@ -18,6 +18,8 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 
 namespace dg {
 
@@ -81,10 +83,13 @@ struct SegmentWalker {
   }
 };
 
-template <int STAGES>
-__global__ void __launch_bounds__(TMA_THREADS, 1)
-dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params P,
-                    int num_units) {
+// SPLIT (SPLIT_A | SPLIT_B bits): the operand comes in by column parity: a parity whose columns start on a 16-byte
+// boundary through its own tensor map (tmA / tmA1, tmB / tmB1), the other one (Params::a_mis / b_mis) through 8-byte
+// cp.async issued by warps 10-11.  tmA1 / tmB1 are only read when the bit is set.  SPLIT = 0 is the performance path and compiles to what it was before the
+// split variants existed (every difference is an `if constexpr`).
+template <int STAGES, int SPLIT>
+__device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtensorMap& tmA1, const CUtensorMap& tmB,
+                                            const CUtensorMap& tmB1, const Params& P, int num_units) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by SWIZZLE_128B; dynamic smem base is only guaranteed 16 B -> round up
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -97,7 +102,8 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < STAGES; s++) {
-      mbar_init(bars + 8 * s, 1);                          // full: one arrive (the producer's expect_tx)
+      // full: one arrive (the producer's expect_tx); split kernels: + one cp.async arrive-on per helper thread
+      mbar_init(bars + 8 * s, 1 + (SPLIT != SPLIT_NONE ? HELPER_THREADS : 0));
       mbar_init(bars + 8 * (STAGES + s), CONSUMER_WARPS);  // empty: one arrive per consumer warp
     }
     asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(progress), "r"(0u) : "memory");
@@ -109,8 +115,14 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ------------------------------- producer warpgroup: one elected lane issues TMA --------------------------
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PRODUCER_REGS));
     if (warp == CONSUMER_WARPS && lane == 0) {
-      tma_prefetch_desc(&tmA);
-      tma_prefetch_desc(&tmB);
+      if constexpr (SPLIT == SPLIT_NONE) {   // (a split kernel may have been handed a dummy map for a misaligned parity)
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+      }
+      // bytes per stage that arrive by TMA (the misaligned parity halves come from the helper warps)
+      uint32_t tx_bytes = STAGE_BYTES;
+      if constexpr ((SPLIT & SPLIT_A) != 0) tx_bytes -= (uint32_t)(P.a_mis[0] + P.a_mis[1]) * (A_STAGE_BYTES / 2);
+      if constexpr ((SPLIT & SPLIT_B) != 0) tx_bytes -= (uint32_t)(P.b_mis[0] + P.b_mis[1]) * (B_STAGE_BYTES / 2);
       uint32_t s = 0, ph = 0;
       SegmentWalker walk(P, num_units);
       Segment sg;
@@ -134,12 +146,28 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
           const uint32_t full = bars + 8 * s;
           const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
-          mbar_arrive_expect_tx(full, STAGE_BYTES);
+          if constexpr (SPLIT == SPLIT_NONE) mbar_arrive_expect_tx(full, STAGE_BYTES);
+          else mbar_arrive_expect_tx(full, tx_bytes);
           const int k0 = kt * BK;
+          if constexpr ((SPLIT & SPLIT_A) != 0) {
+            // A by k parity: per 16-row sub-tile one box of 16(m) x 8(even k) into rows 0..7, one of the odd k into 8..15
 #pragma unroll
-          for (int sub = 0; sub < BM / 16; sub++)  // A: 8 boxes of 16(m) x 16(k); OOB rows/cols arrive as zeros
-            tma_load_2d(dstA + sub * 2048, &tmA, full, m0 + sub * 16, k0);
-          tma_load_2d(dstB, &tmB, full, k0, n0);   // B: one box of 16(k) x 128(n)
+            for (int sub = 0; sub < BM / 16; sub++) {
+              if (!P.a_mis[0]) tma_load_2d(dstA + sub * 2048, &tmA, full, m0 + sub * 16, k0 >> 1);
+              if (!P.a_mis[1]) tma_load_2d(dstA + sub * 2048 + 1024, &tmA1, full, m0 + sub * 16, k0 >> 1);
+            }
+          } else {
+#pragma unroll
+            for (int sub = 0; sub < BM / 16; sub++)  // A: 8 boxes of 16(m) x 16(k); OOB rows/cols arrive as zeros
+              tma_load_2d(dstA + sub * 2048, &tmA, full, m0 + sub * 16, k0);
+          }
+          if constexpr ((SPLIT & SPLIT_B) != 0) {
+            // B by column parity: 16(k) x 64(even n) into rows 0..63, the odd columns into rows 64..127
+            if (!P.b_mis[0]) tma_load_2d(dstB, &tmB, full, k0, n0 >> 1);
+            if (!P.b_mis[1]) tma_load_2d(dstB + B_STAGE_BYTES / 2, &tmB1, full, k0, n0 >> 1);
+          } else {
+            tma_load_2d(dstB, &tmB, full, k0, n0);   // B: one box of 16(k) x 128(n)
+          }
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
         if (sg.kind == SEG_SK_OWNER && !P.sk_parallel) {
@@ -191,6 +219,52 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
+    } else if (SPLIT != SPLIT_NONE && warp > CONSUMER_WARPS + 1) {
+      // ---------------- helper warps (10, 11) of the split kernels: cp.async staging of the misaligned parity halves --------
+      // They walk the same segments and stages as the producer, wait for the same empty barriers, and every thread
+      // arrives once per stage on the full barrier (arrive-on of its own copies), also for the stages that carry a
+      // stream-K partial, so the barrier's arrival count is the same for every phase.
+      if constexpr (SPLIT != SPLIT_NONE) {
+        const int t = tid - (CONSUMER_THREADS + 64);
+        uint32_t s = 0, ph = 0;
+        SegmentWalker walk(P, num_units);
+        Segment sg;
+        while (walk.next(P, sg)) {
+          int tm, tn;
+          decode_tile(P, sg.tile, tm, tn);
+          const int m0 = tm * BM, n0 = tn * BN;
+#pragma unroll 1
+          for (int kt = sg.kb; kt < sg.ke; kt++) {
+            mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
+            const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
+            const int k0 = kt * BK;
+            if constexpr ((SPLIT & SPLIT_A) != 0) {
+#pragma unroll 1
+              for (int p = 0; p < 2; p++)
+                if (P.a_mis[p]) helper_copy_a_half(P, dstA, m0, k0, p, t);
+            }
+            if constexpr ((SPLIT & SPLIT_B) != 0) {
+#pragma unroll 1
+              for (int p = 0; p < 2; p++)
+                if (P.b_mis[p]) helper_copy_b_half(P, dstB, n0, k0, p, t);
+            }
+            cp_async_mbar_arrive_noinc(bars + 8 * s);
+            if (++s == STAGES) { s = 0; ph ^= 1; }
+          }
+          if (sg.kind == SEG_SK_OWNER && !P.sk_parallel) {
+            const long long total = (long long)P.sk_tiles * P.k_tiles;
+            const long long tile_end = (long long)(sg.tile - P.sk_tile0 + 1) * P.k_tiles;
+            for (int r = sg.slot + 1; r < (int)gridDim.x && total * r / gridDim.x < tile_end; r++) {
+#pragma unroll 1
+              for (int c = 0; c < PARTIAL_CHUNKS; c++) {
+                mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
+                mbar_arrive(bars + 8 * s);
+                if (++s == STAGES) { s = 0; ph ^= 1; }
+              }
+            }
+          }
+        }
+      }
     } else if (warp > CONSUMER_WARPS + 1 && P.fetch_bytes) {
       // ---------------- fetch warps (10, 11): NVLink pull of the NEXT K-slab of A, overlapped with the math ---------
       // every CTA copies one contiguous 1/gridDim.x share; 4 x 16 B per lane in flight
@@ -215,7 +289,8 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ------------------------------- consumer warps: DMMA main loop + epilogue -------------------------------
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
     const int warp_m = warp % WARPS_M, warp_n = warp / WARPS_M;
-    const LaneOffsets lo = make_lane_offsets(lane, warp_m, warp_n);
+    typename LaneOffsetsFor<SPLIT>::type lo;
+    make_lane_offsets_t(lo, lane, warp_m, warp_n);
     double acc[FRAG_N][FRAG_M][2];
     Frags f0, f1;
     uint32_t s = 0, ph = 0;
@@ -259,7 +334,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       decode_tile(P, sg.tile, tm, tn);
       if (tid == 0) stamp(P, tslot++);     // main loop of the segment done
       if (sg.kind == SEG_DIRECT) {
-        epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
+        epilogue_store<SPLIT>(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       } else if (sg.kind == SEG_SPLITK) {
         store_partial(acc, P.workspace + (size_t)sg.slot * (BM * BN), tid);
       } else if (P.sk_parallel) {
@@ -289,7 +364,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (++s == STAGES) { s = 0; ph ^= 1; }
           }
         }
-        epilogue_store(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
+        epilogue_store<SPLIT>(acc, P, tm * BM, tn * BN, warp_m, warp_n, lane);
       }
       if (tid == 0) stamp(P, tslot++);     // epilogue / partial store / fix-up of the segment done
     }
@@ -343,7 +418,8 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int u = 0; u < 4; u++) {
               const int q = min(q0 + u * R, FRAG_N * FRAG_M - 1), i = q / FRAG_M, j = q % FRAG_M;
-              p[u] = P.C + (long long)(tn * BN + warp_n * WN + i * 8 + perm_n(lr)) * P.ldc + tm * BM + warp_m * WM +
+              p[u] = P.C + (long long)(tn * BN + tile_col<SPLIT>(warp_n * WN + i * 8 + perm_n_t<SPLIT>(lr))) * P.ldc +
+                     tm * BM + warp_m * WM +
                      map_m(2 * lq) + (j >> 1) * 16 + (j & 1) * 4;
               c[u] = make_double2(0.0, 0.0);
             }
@@ -362,7 +438,7 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int u = 0; u < 4; u++) {
               const int q = q0 + u * R;
               if (q < FRAG_N * FRAG_M)
-                epilogue_frag(s0[u], s1[u], P, tm * BM, tn * BN, warp_m, warp_n, lane, q / FRAG_M, q % FRAG_M);
+                epilogue_frag<SPLIT>(s0[u], s1[u], P, tm * BM, tn * BN, warp_m, warp_n, lane, q / FRAG_M, q % FRAG_M);
             }
           }
         }
@@ -370,6 +446,21 @@ dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (tid == 0) stamp(P, 15);
     }
   }
+}
+
+template <int STAGES>
+__global__ void __launch_bounds__(TMA_THREADS, 1)
+dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params P,
+                    int num_units) {
+  tma_ws_body<STAGES, SPLIT_NONE>(tmA, tmA, tmB, tmB, P, num_units);
+}
+// operands TMA cannot describe with one map (odd LDA / LDB, 8-byte aligned bases): parity-split maps, no copy
+template <int STAGES, int SPLIT>
+__global__ void __launch_bounds__(TMA_THREADS, 1)
+dgemm_tma_ws_split_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA1,
+                          const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmB1,
+                          const Params P, int num_units) {
+  tma_ws_body<STAGES, SPLIT>(tmA, tmA1, tmB, tmB1, P, num_units);
 }
 
 // =========================================================================================================
@@ -576,6 +667,40 @@ bool tma_eligible(const Params& P) {
   return ((uintptr_t)P.A % 16 == 0) && ((uintptr_t)P.B % 16 == 0) && (P.lda % 2 == 0) && (P.ldb % 2 == 0) &&
          P.lda * 8 < (1ll << 40) && P.ldb * 8 < (1ll << 40);
 }
+// which operands need parity-split tensor maps (SPLIT_A | SPLIT_B), and whether the split kernel can take the call:
+// every parity needs at least one column, and the doubled stride must fit a tensor map
+int tma_split_bits(const Params& P) {
+  if (const char* f = getenv("DGEMM_B200_FORCE_SPLIT")) return atoi(f) & 3;   // debug: parity maps on aligned operands
+  return (((uintptr_t)P.A % 16 != 0 || P.lda % 2 != 0) ? SPLIT_A : 0) |
+         (((uintptr_t)P.B % 16 != 0 || P.ldb % 2 != 0) ? SPLIT_B : 0);
+}
+// how many parity halves of the split operands start at 8 mod 16 and have to be staged with cp.async
+int tma_mis_halves(const Params& P) {
+  const int bits = tma_split_bits(P);
+  int n = 0;
+  for (int p = 0; p < 2; p++) {
+    if ((bits & SPLIT_A) && (uintptr_t)(P.A + (long long)p * P.lda) % 16 != 0) n++;
+    if ((bits & SPLIT_B) && (uintptr_t)(P.B + (long long)p * P.ldb) % 16 != 0) n++;
+  }
+  return n;
+}
+bool tma_split_ok(const Params& P) {
+  const int bits = tma_split_bits(P);
+  if ((uintptr_t)P.A % 8 != 0 || (uintptr_t)P.B % 8 != 0) return false;
+  if (P.lda * 16 >= (1ll << 40) || P.ldb * 16 >= (1ll << 40)) return false;
+  if ((bits & SPLIT_A) && P.K < 2) return false;
+  if ((bits & SPLIT_B) && P.N < 2) return false;
+  return true;
+}
+// Tensor map over the columns of parity p of a column-major operand (rows x cols, ld): stride 2*ld elements.  A parity
+// whose columns start at 8 mod 16 cannot have one (*mis = 1, the kernel stages it with cp.async); *tm is then left alone.
+static bool make_parity_tmap(CUtensorMap* tm, const double* base, long long rows, long long cols, long long ld, int p,
+                             int box_rows, int box_cols, int* mis) {
+  const double* addr = base + (long long)p * ld;
+  *mis = ((uintptr_t)addr % 16 != 0) ? 1 : 0;
+  if (*mis) return true;
+  return make_tmap(tm, addr, rows, (cols - p + 1) / 2, 2 * ld, box_rows, box_cols);
+}
 
 // counted from every host thread that launches (mydgemm_gpu_v21 drives one thread per GPU)
 static std::atomic<int> g_launches{0};
@@ -599,21 +724,56 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     return launch_ladder(P, variant, stream);
   }
   if (variant == VARIANT_TMA) {
-    CUtensorMap tmA, tmB;
-    if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN))
-      return cudaErrorInvalidValue;
+    const int split = tma_split_bits(P);
+    if (split && !tma_split_ok(P)) return cudaErrorInvalidValue;
+    Params Q = P;
+    Q.a_mis[0] = Q.a_mis[1] = Q.b_mis[0] = Q.b_mis[1] = 0;
+    CUtensorMap tmA, tmA1, tmB, tmB1;
+    memset(&tmA, 0, sizeof tmA); memset(&tmA1, 0, sizeof tmA1); memset(&tmB, 0, sizeof tmB); memset(&tmB1, 0, sizeof tmB1);
+    bool ok = true;
+    if (split & SPLIT_A) {
+      if (P.fetch_bytes) return cudaErrorInvalidValue;   // warps 10-11 cannot do both jobs (run_device never asks)
+      ok = ok && make_parity_tmap(&tmA, P.A, P.M, P.K, P.lda, 0, 16, BK / 2, &Q.a_mis[0]) &&
+           make_parity_tmap(&tmA1, P.A, P.M, P.K, P.lda, 1, 16, BK / 2, &Q.a_mis[1]);
+    } else {
+      ok = ok && make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK);
+    }
+    if (split & SPLIT_B) {
+      if (P.fetch_bytes) return cudaErrorInvalidValue;
+      ok = ok && make_parity_tmap(&tmB, P.B, P.K, P.N, P.ldb, 0, BK, BN / 2, &Q.b_mis[0]) &&
+           make_parity_tmap(&tmB1, P.B, P.K, P.N, P.ldb, 1, BK, BN / 2, &Q.b_mis[1]);
+    } else {
+      ok = ok && make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN);
+    }
+    if (!ok) return cudaErrorInvalidValue;
     const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
     static bool attr_done[64] = {};  // function attributes are per device
     int dev = 0;
     if ((err = cudaGetDevice(&dev)) != cudaSuccess) return err;
     if (!attr_done[dev & 63]) {
       if ((err = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem)) != cudaSuccess) return err;
+      if ((err = set_smem(dgemm_tma_ws_split_kernel<TMA_STAGES, SPLIT_A>, smem)) != cudaSuccess) return err;
+      if ((err = set_smem(dgemm_tma_ws_split_kernel<TMA_STAGES, SPLIT_B>, smem)) != cudaSuccess) return err;
+      if ((err = set_smem(dgemm_tma_ws_split_kernel<TMA_STAGES, SPLIT_A | SPLIT_B>, smem)) != cudaSuccess) return err;
       attr_done[dev & 63] = true;
     }
     // data-parallel units first (tiles before sk_tile0, times splits), stream-K ranges after
     const int dp_units = (P.sk_tiles > 0 ? P.sk_tile0 : tiles) * P.splits;
     const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < num_sms ? dp_units : num_sms);
-    dgemm_tma_ws_kernel<TMA_STAGES><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmB, P, dp_units);
+    switch (split) {
+      case SPLIT_NONE:
+        dgemm_tma_ws_kernel<TMA_STAGES><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmB, Q, dp_units);
+        break;
+      case SPLIT_A:
+        dgemm_tma_ws_split_kernel<TMA_STAGES, SPLIT_A><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmA1, tmB, tmB1, Q, dp_units);
+        break;
+      case SPLIT_B:
+        dgemm_tma_ws_split_kernel<TMA_STAGES, SPLIT_B><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmA1, tmB, tmB1, Q, dp_units);
+        break;
+      default:
+        dgemm_tma_ws_split_kernel<TMA_STAGES, SPLIT_A | SPLIT_B><<<grid, TMA_THREADS, smem, stream>>>(tmA, tmA1, tmB, tmB1, Q,
+                                                                                                       dp_units);
+    }
   } else {
     const int smem = CPA_STAGES * STAGE_BYTES + 1024;
     static bool attr_done[64] = {};

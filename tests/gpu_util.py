@@ -72,8 +72,11 @@ def check(M, N, K, alpha, A, B, beta, C0, Cgpu, Cref=None):
 
 
 def run_device(dg, M, N, K, alpha, beta, pad=(0, 0, 0), variant=0, splits=0, seed=1, dist="signed", offset=(0, 0, 0),
-               c_fill=None):
+               c_fill=None, nan_pad=False):
     A, B, C0 = make_inputs(M, N, K, pad, seed, dist, c_fill)
+    if nan_pad:   # padding rows of A and B must never reach the result (TMA out-of-bounds fill, shifted parity maps)
+        A[M:, :] = np.nan
+        B[K:, :] = np.nan
     dA, dB, dC = DevMat(dg, A, offset[0]), DevMat(dg, B, offset[1]), DevMat(dg, C0, offset[2])
     try:
         dg.dgemm_device(M, N, K, alpha, dA.ptr, dA.ld, dB.ptr, dB.ld, beta, dC.ptr, dC.ld, 0, variant, splits)

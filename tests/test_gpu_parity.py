@@ -146,9 +146,13 @@ def test_variants_agree_bitwise(dg):
                                   ((2200, 2304, 2101), (0, 0, 0), (0, 0, 0)),     # odd LDB (= K) only
                                   ((2049, 2051, 2305), (0, 0, 2), (0, 0, 0)),     # odd M -> odd LDA and LDC, odd LDB
                                   ((2304, 2200, 2100), (0, 0, 0), (1, 1, 0))])    # 8-byte-aligned bases
-def test_large_unaligned_operands_are_realigned_on_device(dg, case):
-    """>= 2e10 flops and TMA-ineligible: D2D realign + TMA kernel. Same bound, A/B untouched, pad rows untouched."""
+def test_large_unaligned_operands(dg, case, monkeypatch):
+    """~2e10 flops and TMA-ineligible: read in place by the parity-split TMA kernel (default), or - what calls with two
+    misaligned halves get from 4e11 flops up, forced here through the threshold - D2D realign + plain TMA kernel.
+    Same bound, A/B untouched, pad rows untouched."""
     (M, N, K), pad, offset = case
+    gu.run_device(dg, M, N, K, 1.5, 0.5, pad=pad, offset=offset)
+    monkeypatch.setenv("DGEMM_B200_SPLIT_MAX_FLOPS2", "1e9")
     gu.run_device(dg, M, N, K, 1.5, 0.5, pad=pad, offset=offset)
 
 
@@ -205,3 +209,59 @@ def test_random_shapes_device_and_host_entries(dg, case):
     Cg = C0.copy(order="F")
     dg.mydgemm_gpu_v20(M, N, K, alpha, A, A.shape[0], B, B.shape[0], beta, Cg, Cg.shape[0])
     gu.check(M, N, K, alpha, A, B, beta, C0, Cg)
+
+
+# ---- parity-split tensor maps: odd leading dimensions / 8-byte-aligned bases read in place by the TMA kernel ----------
+_SPLIT_CASES = [
+    ((1000, 1003, 997), (0, 0, 0), (0, 0, 0)),     # BASELINE configs[2]: LDB = 997 odd -> B split by column parity
+    ((1000, 1003, 997), (7, 7, 7), (0, 0, 0)),     # LD = dim + 7: LDA = 1007 odd -> A split by k parity
+    ((1001, 1003, 999), (0, 0, 0), (0, 0, 0)),     # odd M: LDA, LDC odd; odd K: LDB odd -> both split
+    ((640, 512, 8192), (1, 1, 0), (0, 0, 0)),      # all stream-K (parallel fix-up) with both operands split
+    ((2200, 2304, 2100), (1, 0, 0), (0, 0, 0)),    # data-parallel wave + stream-K tail, A split
+    ((2200, 2304, 2101), (0, 0, 0), (0, 0, 0)),    # the same, B split
+    ((2304, 2200, 2100), (0, 0, 0), (1, 1, 0)),    # even LD, bases at 8 mod 16: both parity maps shifted by one row
+    ((777, 555, 333), (0, 0, 0), (1, 0, 1)),       # odd LD AND a shifted base for A; C on an 8-byte base too
+    ((300, 2, 2), (1, 1, 0), (0, 0, 0)),           # smallest K and N the split maps can take
+    ((129, 3, 5), (0, 0, 0), (0, 1, 0)),
+    ((7, 130, 17), (0, 0, 0), (0, 0, 0)),
+    ((128, 128, 16), (1, 1, 1), (1, 1, 1)),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", _SPLIT_CASES, ids=lambda c: "x".join(str(v) for v in c[0]) + "-" + "".join(map(str, c[1] + c[2])))
+@pytest.mark.parametrize("ab", [(1.5, 0.5), (-1.0, 0.0)])
+def test_parity_split_tensor_maps(dg, case, ab):
+    """Operands one tensor map cannot describe run on the TMA kernel through even/odd-column tensor maps (no copy, no
+    cp.async): same bound against the oracle, padding rows untouched, NaN-filled C ignored when beta = 0."""
+    (M, N, K), pad, offset = case
+    gu.run_device(dg, M, N, K, ab[0], ab[1], pad=pad, offset=offset, c_fill=np.nan if ab[1] == 0.0 else None,
+                  nan_pad=True)
+    gu.run_device(dg, M, N, K, ab[0], ab[1], pad=pad, offset=offset, variant=TMA,
+                  c_fill=np.nan if ab[1] == 0.0 else None, nan_pad=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["split", "realign", "cpasync"])
+def test_odd_ld_modes_agree_with_the_oracle(dg, mode, monkeypatch):
+    """DGEMM_B200_ODD_LD selects how TMA-ineligible operands are handled; every mode meets the bound."""
+    monkeypatch.setenv("DGEMM_B200_ODD_LD", mode)
+    gu.run_device(dg, 1000, 1003, 997, 2.5, 0.5)
+    gu.run_device(dg, 1001, 1003, 999, 1.0, 1.0, offset=(1, 0, 0))
+
+
+@pytest.mark.gpu
+def test_column_parity_split_of_b_is_bitwise_identical(dg):
+    """Splitting B by column parity only permutes which shared-memory row holds which column: same DMMA schedule, same
+    bits as the single-map kernel on the same values with an even LDB."""
+    M, N, K = 520, 390, 777
+    A, B, C0 = gu.make_inputs(M, N, K, pad=(0, 1, 0))          # LDB = 778 (even): one tensor map
+    B_odd = np.asfortranarray(B[:K, :])                        # same values, LDB = 777 (odd): parity maps
+    outs = []
+    for Bm in (B, B_odd):
+        dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, Bm), gu.DevMat(dg, C0)
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, TMA, 1)
+        assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+        outs.append(dC.to_host())
+        dA.free(); dB.free(); dC.free()
+    assert np.array_equal(outs[0], outs[1])

@@ -26,6 +26,21 @@ def main():
                 ok &= conflict_free([a_off(16 * s + 4 * f + MAP_M[l // 4], kk * 4 + l % 4) for l in range(32)])
         for t in range(16):
             ok &= conflict_free([b_off(kk * 4 + l % 4, 8 * t + PERM_N[l // 4]) for l in range(32)])
+    # A split by k parity (dgemm_tma_ws_split_kernel, LaneOffsetsKS): k in row (k&1)*8 + (k>>1); lanes q of k-step kk feed
+    # k = 8*(kk>>1) + 2q + ((q^kk)&1); B rows permuted by PERM_N_KS
+    PERM_N_KS = [0, 1, 4, 5, 2, 3, 6, 7]
+    ks_ok = True
+    for kk in range(4):
+        ks = [8 * (kk >> 1) + 2 * q + ((q ^ kk) & 1) for q in range(4)]
+        for f in range(2):
+            for s in range(8):
+                ks_ok &= conflict_free([a_off(16 * s + 4 * f + MAP_M[l // 4], (ks[l % 4] & 1) * 8 + (ks[l % 4] >> 1))
+                                        for l in range(32)])
+        for t in range(16):
+            ks_ok &= conflict_free([b_off(ks[l % 4], 8 * t + PERM_N_KS[l // 4]) for l in range(32)])
+    assert sorted(sum(([8 * (kk >> 1) + 2 * q + ((q ^ kk) & 1) for q in range(4)] for kk in range(4)), [])) == list(range(16))
+    print(f"k-parity-split A layout conflict-free: {ks_ok}")
+    assert ks_ok
     natural_a = conflict_free([a_off(l // 4, l % 4) for l in range(32)])
     natural_b = conflict_free([b_off(l % 4, l // 4) for l in range(32)])
     print(f"permuted lane maps conflict-free: {ok}; natural maps: A {natural_a}, B {natural_b}")

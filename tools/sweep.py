@@ -64,8 +64,8 @@ for n in [256, 512, 1024, 1536, 2048, 3072, 4096, 6144, 8192, 12288, 16384]:
     run(n, n, n, label="square")
 run(2048, 2048, 2048, alpha=2.0, beta=0.0, label="harness pair (test.c:25)")
 run(512, 512, 16384, label="tall-skinny")
-run(1000, 1003, 997, alpha=2.5, beta=0.5, label="edge, LD=dim (LDB odd -> cp.async loader)")
-run(1000, 1003, 997, alpha=2.5, beta=0.5, ld_pad=(7, 7, 7), label="edge, LD=dim+7")
+run(1000, 1003, 997, alpha=2.5, beta=0.5, label="edge, LD=dim (LDB odd -> B by column parity: TMA + cp.async halves)")
+run(1000, 1003, 997, alpha=2.5, beta=0.5, ld_pad=(7, 7, 7), label="edge, LD=dim+7 (LDA odd -> A by k parity)")
 run(1000, 1003, 997, alpha=2.5, beta=0.5, ld_pad=(24, 27, 24), label="edge, LD=1024 (TMA)")
 run(1001, 1003, 997, alpha=2.5, beta=0.5, ld_pad=(23, 27, 23), label="edge odd M, LD=1024 (TMA)")
 run(3000, 3000, 3000, alpha=2.0, beta=0.0, label="reference's largest published size")
