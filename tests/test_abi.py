@@ -39,6 +39,8 @@ def test_library_is_sm100a_cuda_not_cpu(dg):
     assert "UTMALDG" in sass           # cp.async.bulk.tensor (TMA)
     assert "LDGSTS" in sass            # cp.async loader for TMA-ineligible operands
     assert "SYNCS" in sass             # mbarrier
+    assert "UBLKCP" in sass            # cp.async.bulk: stream-K partials come in through the TMA ring
+    assert "dgemm_tma_ws_split_kernel" in sass   # parity-split variants for odd LD / 8-byte-aligned operands
 
 
 def test_product_does_not_link_the_oracle(dg):
