@@ -38,8 +38,10 @@ enum {
 
 /* kernel variants, for tests / ablations (dgemm_b200_device_ex) */
 enum {
-  DGEMM_B200_VARIANT_AUTO = 0,
-  DGEMM_B200_VARIANT_TMA = 1,        /* TMA + mbarrier warp-specialised persistent kernel */
+  DGEMM_B200_VARIANT_AUTO = 0,       /* the TMA kernel for every operand layout (see DGEMM_B200_ODD_LD in INTEGRATION.md) */
+  DGEMM_B200_VARIANT_TMA = 1,        /* TMA + mbarrier warp-specialised persistent kernel; operands with an odd leading
+                                        dimension or an 8-byte-aligned base are read in place by its parity-split
+                                        variant (one parity by TMA, the other by cp.async from spare warps) */
   DGEMM_B200_VARIANT_CPASYNC8 = 2,   /* cp.async 8-byte loader: any alignment / odd leading dimensions */
   DGEMM_B200_VARIANT_CPASYNC16 = 3,  /* cp.async 16-byte loader */
   DGEMM_B200_VARIANT_NAIVE = 4,      /* optimisation-ladder rung 1: one thread per entry (never auto-selected) */

@@ -9,8 +9,8 @@ namespace dg {
 struct Params;
 
 enum Variant {
-  VARIANT_AUTO = 0,       // TMA when the operands allow a tensor map, else cp.async 8-byte
-  VARIANT_TMA = 1,        // dgemm_tma_ws_kernel (needs 16-byte aligned A, B and even lda, ldb)
+  VARIANT_AUTO = 0,       // the TMA kernel; its parity-split variant for odd lda / ldb or 8-byte aligned bases
+  VARIANT_TMA = 1,        // dgemm_tma_ws_kernel / dgemm_tma_ws_split_kernel (unaligned operands need K >= 2, N >= 2)
   VARIANT_CPASYNC8 = 2,   // dgemm_cpasync_kernel<1>: any alignment, any leading dimension
   VARIANT_CPASYNC16 = 3,  // dgemm_cpasync_kernel<2>: same eligibility as TMA
   VARIANT_NAIVE = 4,      // ladder rung 1 (dgemm_ladder.cu): never chosen by VARIANT_AUTO
