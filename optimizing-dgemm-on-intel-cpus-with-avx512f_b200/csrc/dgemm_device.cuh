@@ -43,8 +43,14 @@ constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
 constexpr int CONSUMER_THREADS = CONSUMER_WARPS * 32;
 // register split between the producer warpgroup and the consumer warps (setmaxnreg); the CTA is compiled at
 // 65536 / (CONSUMER_THREADS + 128) registers per thread, rounded down to 8
-constexpr int PRODUCER_REGS = CONSUMER_WARPS == 8 ? 40 : 24;
-constexpr int CONSUMER_REGS = CONSUMER_WARPS == 8 ? 232 : 112;
+#ifndef DG_PRODUCER_REGS
+#define DG_PRODUCER_REGS (DG_WARPS_M * DG_WARPS_N == 8 ? 40 : 24)
+#endif
+#ifndef DG_CONSUMER_REGS
+#define DG_CONSUMER_REGS (DG_WARPS_M * DG_WARPS_N == 8 ? 232 : 112)
+#endif
+constexpr int PRODUCER_REGS = DG_PRODUCER_REGS;
+constexpr int CONSUMER_REGS = DG_CONSUMER_REGS;
 constexpr int WM = BM / WARPS_M;  // 64
 constexpr int WN = BN / WARPS_N;  // 32
 constexpr int FRAG_M = WM / 8;    // 8 column fragments (from A)

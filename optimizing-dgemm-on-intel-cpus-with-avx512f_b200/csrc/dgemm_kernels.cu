@@ -707,7 +707,10 @@ static std::atomic<int> g_launches{0};
 int launch_count() { return g_launches.load(std::memory_order_relaxed); }
 void reset_launch_count() { g_launches.store(0, std::memory_order_relaxed); }
 
-constexpr int TMA_STAGES = 6;
+#ifndef DG_TMA_STAGES
+#define DG_TMA_STAGES 6
+#endif
+constexpr int TMA_STAGES = DG_TMA_STAGES;
 constexpr int CPA_STAGES = 4;
 
 template <typename Kern>
