@@ -175,6 +175,8 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
 static int SK_MIN_ITERS = getenv("DGEMM_B200_SK_MIN_ITERS") ? atoi(getenv("DGEMM_B200_SK_MIN_ITERS")) : 4;
 static int SK_ALIGNED_MIN_ITERS = getenv("DGEMM_B200_SK_ALIGNED_MIN_ITERS") ? std::max(1, atoi(getenv("DGEMM_B200_SK_ALIGNED_MIN_ITERS"))) : 2;
 void plan_stream_k(dg::Params& P, int num_sms) {
+  // the parallel fix-up hands out a tile's fragments (32 per thread on the 128 x 128 tile, 8 on the 64 x 64 one)
+  const int max_ranges = P.tile_small ? 8 : 64;
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0;
   if (P.k_tiles < 8) return;
@@ -195,7 +197,7 @@ void plan_stream_k(dg::Params& P, int num_sms) {
       // at most 64 ranges per tile (the parallel fix-up hands out the tile's 64 fragments; 128x128x4096: 64 ranges 4.25,
       // 128 ranges 3.8 TFLOP/s), and no more ranges than it takes to reach the shortest longest range (512^3: 9 ranges
       // of 3-4 k-tiles are slower than 8 ranges of 4: 10.2 vs 10.7 TFLOP/s)
-      const int r_max = std::max(1, std::min({r_cap, P.k_tiles / SK_ALIGNED_MIN_ITERS, 64}));
+      const int r_max = std::max(1, std::min({r_cap, P.k_tiles / SK_ALIGNED_MIN_ITERS, max_ranges}));
       const int longest = (P.k_tiles + r_max - 1) / r_max;
       g = tiles * ((P.k_tiles + longest - 1) / longest);
     }
@@ -208,13 +210,31 @@ void plan_stream_k(dg::Params& P, int num_sms) {
   P.sk_tile0 = tiles - P.sk_tiles;
 }
 
+// The 64 x 64 build of the TMA kernel (dgemm_kernels_small.cu) for problems too small to fill the GPU with 128 x 128
+// tiles: at most DGEMM_B200_SMALL_TILE_MAX_TILES (64) big tiles and DGEMM_B200_SMALL_TILE_MAX_FLOPS (4e9) flops, plain
+// tensor maps only; DGEMM_B200_NO_SMALL_TILE=1 switches it off.  Read per call.  Measured small / big tile, kernel-only
+// microseconds (tools/small_tile_probe.py, profiles/r01_small_tile_probe.jsonl): 100^3 12.4 / 32.9, 200^3 14.5 / 24.7,
+// 256^3 15.4 / 20.5, 512^3 22.6 / 25.0, 640^3 28.8 / 35.8, 1000^3 76.4 / 86.9, 1024^3 77.3 / 80.8, 1280^3 equal,
+// 1536^3 226.6 / 218.4 (the small tile's main loop loads 6 fragments per 8 DMMAs instead of 12 per 32), 512x512x4096
+// 77.8 / 80.2, 512x512x16384 264.1 / 259.5.
+bool want_small_tile(int M, int N, int K, bool one_map_ok, bool has_fetch) {
+  if (!one_map_ok || has_fetch || getenv("DGEMM_B200_NO_SMALL_TILE")) return false;
+  const long long big_tiles = (long long)((M + dg::BM - 1) / dg::BM) * ((N + dg::BN - 1) / dg::BN);
+  const long long max_tiles = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES") ? atoll(getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) : 64;
+  const double max_flops = getenv("DGEMM_B200_SMALL_TILE_MAX_FLOPS") ? atof(getenv("DGEMM_B200_SMALL_TILE_MAX_FLOPS")) : 4e9;
+  return big_tiles <= max_tiles && 2.0 * M * (double)N * K <= max_flops;
+}
+
 int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
-                long long ldb, double beta, double* dC, long long ldc, int splits, int variant, int num_sms) {
+                long long ldb, double beta, double* dC, long long ldc, int splits, int variant, int num_sms,
+                bool small_tile = false) {
   P.M = M; P.N = N; P.K = K;
   P.alpha = alpha; P.beta = beta;
   P.A = dA; P.lda = lda; P.B = dB; P.ldb = ldb; P.C = dC; P.ldc = ldc;
-  P.tiles_m = (M + dg::BM - 1) / dg::BM;
-  P.tiles_n = (N + dg::BN - 1) / dg::BN;
+  P.tile_small = (small_tile && variant == dg::VARIANT_TMA && splits <= 0) ? 1 : 0;
+  const int bm = P.tile_small ? dg::SMALL_BM : dg::BM, bn = P.tile_small ? dg::SMALL_BN : dg::BN;
+  P.tiles_m = (M + bm - 1) / bm;
+  P.tiles_n = (N + bn - 1) / bn;
   P.k_tiles = (K + dg::BK - 1) / dg::BK;
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0; P.sk_epoch = 0; P.sk_flags = nullptr;
@@ -327,13 +347,15 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
     }
   }
   const bool use_split = can_split && !realigned;
+  const bool auto_variant = variant == dg::VARIANT_AUTO;
   if (variant == dg::VARIANT_AUTO) variant = (tma_ok || use_split) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   if (variant < 0 || variant > dg::VARIANT_DFMA) return fail(DGEMM_B200_ERR_BAD_ARG, "unknown kernel variant %d", variant);
   if (variant == dg::VARIANT_CPASYNC16 && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
   if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d: unaligned operands need K >= 2 and N >= 2 for parity-split tensor maps", variant);
-  fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms);
+  fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms,
+              auto_variant && want_small_tile(M, N, K, tma_ok, fetch.bytes != 0));
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
   // there are at least two full waves; every CTA must be resident, i.e. the grid is one CTA per SM
@@ -357,7 +379,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (uses_ws) {
     const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits
                                       : (size_t)P.sk_grid * (P.sk_parallel ? 2 : 1);
-    const size_t need = slots * dg::BM * dg::BN * sizeof(double);
+    const size_t need = slots * (P.tile_small ? dg::SMALL_BM * dg::SMALL_BN : dg::BM * dg::BN) * sizeof(double);
     if (c.ws.cap < need) {
       int st = grow(c.ws, need);
       if (st) return st;   // (grow synchronises the device before it frees the old buffer)
@@ -865,7 +887,8 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
   const bool realign = !tma_ok && !split && odd_ld_mode() != ODD_CPASYNC && 2.0 * M * (double)N * K >= 1e8 &&
                        !getenv("DGEMM_B200_REALIGN_MIN_FLOPS");
   const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
-  fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms);
+  fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms,
+              want_small_tile(M, N, std::max(K, 1), tma_ok || realign, false));
   if (variant) *variant = v;
   if (splits) *splits = P.splits;
   if (sk_tiles) *sk_tiles = P.sk_tiles;

@@ -20,11 +20,32 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-namespace dg {
+#include "dgemm_params.h"
 
-constexpr int BM = 128;
-constexpr int BN = 128;
-constexpr int BK = 16;
+// Tile configuration of this translation unit.  The library is built from two: the 128 x 128 CTA tile (namespace dg, the
+// performance path and everything else) and a 64 x 64 CTA tile (namespace dg64, dgemm_kernels_small.cu: the same TMA
+// kernel body for problems with too few 128 x 128 tiles to fill the GPU; 32 x 16 warp tiles, 32 KB stream-K partials).
+#ifndef DG_NAMESPACE
+#define DG_NAMESPACE dg
+#endif
+#ifndef DG_BM
+#define DG_BM 128
+#endif
+#ifndef DG_BN
+#define DG_BN 128
+#endif
+
+namespace DG_NAMESPACE {
+#ifdef DG_SMALL_TILE
+using dg::Params;
+using dg::SPLIT_NONE;
+using dg::SPLIT_A;
+using dg::SPLIT_B;
+using dg::BK;
+#endif
+
+constexpr int BM = DG_BM;
+constexpr int BN = DG_BN;
 constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -57,56 +78,7 @@ constexpr int FRAG_M = WM / 8;    // 8 column fragments (from A)
 constexpr int FRAG_N = WN / 8;    // 4 row fragments (from B)
 constexpr int ACC_PER_THREAD = FRAG_M * FRAG_N * 2;  // 64 doubles = 128 registers
 
-struct Params {
-  int M, N, K;
-  double alpha, beta;
-  const double* A; long long lda;
-  const double* B; long long ldb;
-  double* C; long long ldc;
-  int tiles_m, tiles_n;
-  int k_tiles;            // ceil(K / BK)
-  int splits;             // split-K factor, 1 = none
-  int k_tiles_per_split;  // ceil(k_tiles / splits)
-  int group_m;            // rasterisation: tiles are walked in bands of group_m tile-rows
-  int c_vec2;             // C base 16-byte aligned and ldc even -> 16-byte epilogue accesses
-  double* workspace;      // splits > 1: [unit][ACC_PER_THREAD][CONSUMER_THREADS] partial accumulators;
-                          // stream-K: one such slot per CTA range
-  // ---- stream-K tail (TMA kernel only): tiles [sk_tile0, sk_tile0 + sk_tiles) are cut into gridDim.x equal
-  // ranges of (tile, k-tile) iterations instead of whole tiles
-  int sk_tile0, sk_tiles;
-  int sk_grid;                // CTAs launched when sk_tiles > 0 (every one of them must be co-resident)
-  int sk_parallel;            // 1: parallel fix-up (all-stream-K mode, many ranges per tile): every range stores its
-                              // partial (2 slots per range: head / tail) and each participant of a tile reduces a
-                              // 1/R slice of it; 0: the tile's owner adds the other ranges' partials serially
-  unsigned int sk_epoch;      // flag value that means "partial of this launch is in the workspace"
-  unsigned int* sk_flags;     // one flag per CTA range
-  // ---- k-lockstep of the data-parallel waves (TMA kernel only).  Persistent CTAs have no reason to stay together: each
-  // walks its own tiles and nothing pulls a CTA that has fallen behind back.  But the 148 tiles of a wave share 16 row
-  // panels of A and ~9 column panels of B through L2 only while their CTAs read the same k at about the same time; once
-  // they drift further apart than the L2 can bridge, every panel is fetched from HBM several times (measured at
-  // 16384^3: 175 GB of DRAM reads against a 46 GB floor for this tile size).  Every sync_kt k-tiles the producer
-  // thread ticks a per-point counter and will not run more than SYNC_SLACK points ahead of the slowest CTA.
-  unsigned int* sync_ctr;     // one counter per sync point, zeroed before the launch; nullptr = off
-  int sync_waves;             // full waves (every CTA has a tile) covered by the lockstep
-  int sync_kt;                // k-tiles between sync points
-  // ---- fused NVLink fetch (TMA kernel only): while the DMMA warps work on this call's K-slab, the three spare
-  // warps of the producer warpgroup copy fetch_bytes from fetch_src (normally a PEER GPU's copy of the next K-slab
-  // of A, mapped through CUDA IPC / peer access) to fetch_dst in local HBM.  16-byte aligned, multiple of 16.
-  const void* fetch_src;
-  void* fetch_dst;
-  unsigned long long fetch_bytes;
-  // ---- optional per-CTA timeline (debug / profiling aid; nullptr in normal use): 16 globaltimer stamps per CTA
-  unsigned long long* timeline;
-  // ---- parity-split operands (TMA kernel, SPLIT != 0): an operand whose leading dimension is odd or whose base is only
-  // 8-byte aligned cannot be described by ONE tensor map (16-byte base and strides).  Its even and its odd columns can
-  // (stride 2*ld*8 is a multiple of 16) as long as the column start of that parity is 16-byte aligned; TMA rejects a
-  // box that starts 8 bytes off a 16-byte boundary (measured: "illegal instruction" with an odd inner coordinate), so a
-  // parity whose columns start at 8 mod 16 (a_mis / b_mis = 1) is staged with 8-byte cp.async by the two spare warps
-  // of the producer warpgroup instead, into the same swizzled layout and onto the same mbarrier.
-  int a_mis[2], b_mis[2];
-};
-// SPLIT template bits of dgemm_tma_ws_kernel
-enum { SPLIT_NONE = 0, SPLIT_A = 1, SPLIT_B = 2 };
+
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -128,7 +100,9 @@ __device__ __forceinline__ int perm_n_t(int r) { return (SPLIT & SPLIT_A) ? perm
 // shared-memory B row of the CTA tile -> column of the tile.  B split by n parity: rows 0..63 hold the even columns,
 // rows 64..127 the odd ones (two TMA boxes of 64 columns each).
 template <int SPLIT>
-__device__ __forceinline__ int tile_col(int row) { return (SPLIT & SPLIT_B) ? (((row & 63) << 1) | (row >> 6)) : row; }
+__device__ __forceinline__ int tile_col(int row) {
+  return (SPLIT & SPLIT_B) ? (((row % (BN / 2)) << 1) | (row / (BN / 2))) : row;
+}
 // column fragment (from A): mma col c feeds m = 16*s + 4*f + kMapM(c)
 __device__ __forceinline__ int map_m(int c) { return (c & 1) | ((c & 2) << 2) | ((c & 4) >> 1); }  // 0,1,8,9,2,3,10,11
 
@@ -235,6 +209,7 @@ __device__ __forceinline__ uint32_t b_smem_off(int k_local, int n_local) {
 }
 
 // ---- staging of a misaligned parity half by the helper warps (64 threads, t = 0..63), zero-filled at the edges -------
+// (written for the 128 x 128 tile: thread t covers rows t and t + 64; the split kernels exist in that configuration only)
 constexpr int HELPER_THREADS = 64;
 __device__ __forceinline__ void cp_async_8(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
@@ -628,4 +603,4 @@ __device__ __forceinline__ Unit decode_unit(const Params& P, int u) {
   return w;
 }
 
-}  // namespace dg
+}  // namespace DG_NAMESPACE

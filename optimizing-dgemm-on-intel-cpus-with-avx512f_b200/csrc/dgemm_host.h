@@ -22,6 +22,10 @@ int tma_split_bits(const Params& P);
 int tma_mis_halves(const Params& P);
 bool tma_split_ok(const Params& P);   // needs P.A, P.B, P.lda, P.ldb, P.K, P.N
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
+// the TMA kernel on 64 x 64 tiles (dgemm_kernels_small.cu); tmA / tmB point to CUtensorMaps with 16 x 16 / 16 x 64 boxes
+constexpr int SMALL_BM = 64, SMALL_BN = 64;
+cudaError_t launch_tma_small(const void* tmA, const void* tmB, const Params& P, int grid, int dp_units,
+                             cudaStream_t stream);
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
 // C += beta * X, both M x N column-major

@@ -1,0 +1,40 @@
+// dgemm_kernels_small.cu — the persistent TMA kernel of dgemm_tma_kernel.cuh compiled for a 64 x 64 CTA tile
+// (namespace dg64): 8 DMMA consumer warps with 32 x 16 warp tiles, 16 KB pipeline stages, 32 KB stream-K partials.
+//
+// Why: a problem with few 128 x 128 tiles (256^3: 4, 512^3: 16) can only fill 148 SMs by cutting K into many ranges per
+// tile, and then the partial-tile exchange dominates: R ranges of a tile write and read R x 128 KB through L2 (512^3:
+// 16 MB each way, ~6.5 us of an 18 us kernel).  A quarter-size tile needs a quarter of the ranges per tile and moves a
+// quarter of the bytes per partial.  Its main loop is less efficient (6 fragment loads per 8 DMMAs instead of 12 per
+// 32), which does not matter where the launch is a few microseconds long; run_device picks it only for small,
+// TMA-eligible problems (see dgemm_api.cu) and the 128 x 128 kernel stays the performance path.
+// Same role in the reference: the 8x8 / 2x8 ... edge micro-kernels beside the 24x8 one (include/kernel18.h:533-600).
+#define DG_NAMESPACE dg64
+#define DG_SMALL_TILE 1
+#define DG_BM 64
+#define DG_BN 64
+#include "dgemm_tma_kernel.cuh"
+#include "dgemm_host.h"
+
+namespace dg {
+
+static_assert(dg64::BM == SMALL_BM && dg64::BN == SMALL_BN, "dgemm_host.h must state the small tile's size");
+
+cudaError_t launch_tma_small(const void* tmA, const void* tmB, const Params& P, int grid, int dp_units,
+                             cudaStream_t stream) {
+  constexpr int STAGES = 8;   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
+  const int smem = STAGES * dg64::STAGE_BYTES + 2 * STAGES * 8 + 16 + 1024;
+  static bool attr_done[64] = {};  // function attributes are per device
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return err;
+  if (!attr_done[dev & 63]) {
+    err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (err != cudaSuccess) return err;
+    attr_done[dev & 63] = true;
+  }
+  dg64::dgemm_tma_ws_kernel<STAGES><<<grid, dg64::TMA_THREADS, smem, stream>>>(
+      *reinterpret_cast<const CUtensorMap*>(tmA), *reinterpret_cast<const CUtensorMap*>(tmB), P, dp_units);
+  return cudaGetLastError();
+}
+
+}  // namespace dg

@@ -268,3 +268,34 @@ def test_column_parity_split_of_b_is_bitwise_identical(dg):
         outs.append(dC.to_host())
         dA.free(); dB.free(); dC.free()
     assert np.array_equal(outs[0], outs[1])
+
+
+# ---- 64 x 64-tile build of the TMA kernel (small problems) against the 128 x 128 one ---------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(100, 100, 100), (64, 64, 16), (65, 63, 17), (200, 300, 250), (256, 256, 256),
+                                   (500, 501, 498), (512, 512, 512), (640, 384, 2048), (1000, 1002, 996),
+                                   (1024, 1024, 1024), (128, 4096, 512), (4096, 128, 512), (31, 7000, 129)])
+@pytest.mark.parametrize("ab", [(1.0, 1.0), (2.5, 0.0)])
+def test_small_tile_and_big_tile_kernels(dg, shape, ab, monkeypatch):
+    """VARIANT_AUTO runs small TMA-eligible problems on the 64 x 64-tile build (all stream-K modes: data-parallel, serial
+    and parallel fix-up); DGEMM_B200_NO_SMALL_TILE=1 keeps them on the 128 x 128 tile.  Both against the oracle; padded
+    C (odd LDC -> scalar epilogue) included."""
+    M, N, K = shape
+    for pad in ((0, 0, 0), (2, 2, 1)):
+        gu.run_device(dg, M, N, K, ab[0], ab[1], pad=pad, c_fill=np.nan if ab[1] == 0.0 else None, nan_pad=True)
+    monkeypatch.setenv("DGEMM_B200_NO_SMALL_TILE", "1")
+    gu.run_device(dg, M, N, K, ab[0], ab[1], c_fill=np.nan if ab[1] == 0.0 else None)
+
+
+@pytest.mark.gpu
+def test_small_tile_is_deterministic(dg):
+    M, N, K = 384, 320, 1500
+    A, B, C0 = gu.make_inputs(M, N, K)
+    outs = []
+    for _ in range(3):
+        dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld)
+        assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+        outs.append(dC.to_host())
+        dA.free(); dB.free(); dC.free()
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
