@@ -212,13 +212,13 @@ void plan_stream_k(dg::Params& P, int num_sms) {
 
 // The 64 x 64 build of the TMA kernel (dgemm_kernels_small.cu) for problems too small to fill the GPU with 128 x 128
 // tiles: at most DGEMM_B200_SMALL_TILE_MAX_TILES (64) big tiles and DGEMM_B200_SMALL_TILE_MAX_FLOPS (4e9) flops, plain
-// tensor maps only; DGEMM_B200_NO_SMALL_TILE=1 switches it off.  Read per call.  Measured small / big tile, kernel-only
+// or parity-split tensor maps; DGEMM_B200_NO_SMALL_TILE=1 switches it off.  Read per call.  Measured small / big tile, kernel-only
 // microseconds (tools/small_tile_probe.py, profiles/r01_small_tile_probe.jsonl): 100^3 12.4 / 32.9, 200^3 14.5 / 24.7,
 // 256^3 15.4 / 20.5, 512^3 22.6 / 25.0, 640^3 28.8 / 35.8, 1000^3 76.4 / 86.9, 1024^3 77.3 / 80.8, 1280^3 equal,
 // 1536^3 226.6 / 218.4 (the small tile's main loop loads 6 fragments per 8 DMMAs instead of 12 per 32), 512x512x4096
 // 77.8 / 80.2, 512x512x16384 264.1 / 259.5.
-bool want_small_tile(int M, int N, int K, bool one_map_ok, bool has_fetch) {
-  if (!one_map_ok || has_fetch || getenv("DGEMM_B200_NO_SMALL_TILE")) return false;
+bool want_small_tile(int M, int N, int K, bool tma_kernel, bool has_fetch) {
+  if (!tma_kernel || has_fetch || getenv("DGEMM_B200_NO_SMALL_TILE")) return false;
   const long long big_tiles = (long long)((M + dg::BM - 1) / dg::BM) * ((N + dg::BN - 1) / dg::BN);
   const long long max_tiles = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES") ? atoll(getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) : 64;
   const double max_flops = getenv("DGEMM_B200_SMALL_TILE_MAX_FLOPS") ? atof(getenv("DGEMM_B200_SMALL_TILE_MAX_FLOPS")) : 4e9;
@@ -355,7 +355,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d: unaligned operands need K >= 2 and N >= 2 for parity-split tensor maps", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms,
-              auto_variant && want_small_tile(M, N, K, tma_ok, fetch.bytes != 0));
+              auto_variant && want_small_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0));
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
   // there are at least two full waves; every CTA must be resident, i.e. the grid is one CTA per SM
@@ -888,7 +888,7 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
                        !getenv("DGEMM_B200_REALIGN_MIN_FLOPS");
   const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms,
-              want_small_tile(M, N, std::max(K, 1), tma_ok || realign, false));
+              want_small_tile(M, N, std::max(K, 1), tma_ok || split || realign, false));
   if (variant) *variant = v;
   if (splits) *splits = P.splits;
   if (sk_tiles) *sk_tiles = P.sk_tiles;

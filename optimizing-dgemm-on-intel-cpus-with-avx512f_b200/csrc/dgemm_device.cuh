@@ -209,16 +209,17 @@ __device__ __forceinline__ uint32_t b_smem_off(int k_local, int n_local) {
 }
 
 // ---- staging of a misaligned parity half by the helper warps (64 threads, t = 0..63), zero-filled at the edges -------
-// (written for the 128 x 128 tile: thread t covers rows t and t + 64; the split kernels exist in that configuration only)
 constexpr int HELPER_THREADS = 64;
 __device__ __forceinline__ void cp_async_8(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
 }
-// A, k parity p: the 8 k-columns k0 + 2j + p of the stage x 128 rows -> smem rows p*8 + j of every 16-row sub-tile.
-// Thread t copies rows t and t + 64 of each column (a warp instruction reads 256 contiguous bytes).  Interior stages take
-// a straight-line path with precomputed offsets: the two helper warps share their SM sub-partitions with DMMA warps and
-// have about 2 us per stage; the generic index arithmetic alone made them the bottleneck when both operands are split.
+// A, k parity p: the 8 k-columns k0 + 2j + p of the stage x BM rows -> smem rows p*8 + j of every 16-row sub-tile.
+// Thread t copies rows t, t + 64, ... of each column (a warp instruction reads 256 contiguous bytes).  Interior stages
+// take a straight-line path with precomputed offsets: the two helper warps share their SM sub-partitions with DMMA warps
+// and have about 2 us per stage; the generic index arithmetic alone made them the bottleneck when both operands are split.
 __device__ __forceinline__ void helper_copy_a_half(const Params& P, uint32_t dstA, int m0, int k0, int p, int t) {
+  constexpr int ROWS_PER_THREAD = BM / HELPER_THREADS;   // 2 (128 x 128 tile) or 1 (64 x 64 tile)
+  static_assert(ROWS_PER_THREAD * HELPER_THREADS == BM, "helper threads must tile the rows of the CTA tile");
   const double* src = P.A + (long long)(k0 + p) * P.lda + m0 + t;
   const long long step = 2 * P.lda;
   const uint32_t base = dstA + (uint32_t)(t >> 4) * 2048u + (uint32_t)p * 1024u + (uint32_t)((t & 1) << 3);
@@ -227,24 +228,28 @@ __device__ __forceinline__ void helper_copy_a_half(const Params& P, uint32_t dst
 #pragma unroll
     for (int j = 0; j < BK / 2; j++) {
       const uint32_t off = (uint32_t)j * 128u + ((c0 ^ (uint32_t)j) << 4);
-      cp_async_8(base + off, src + j * step);
-      cp_async_8(base + 4u * 2048u + off, src + j * step + 64);   // row t + 64: four sub-tiles further, same chunk
+#pragma unroll
+      for (int h = 0; h < ROWS_PER_THREAD; h++)   // row t + 64h: four sub-tiles further, same chunk
+        cp_async_8(base + (uint32_t)h * 4u * 2048u + off, src + j * step + 64 * h);
     }
     return;
   }
   // edge stage (last tile row / K tail): same addresses, zero fill for rows >= M and columns >= K
-  const bool r0 = m0 + t < P.M, r1 = m0 + t + 64 < P.M;
 #pragma unroll
   for (int j = 0; j < BK / 2; j++) {
     const uint32_t off = (uint32_t)j * 128u + ((c0 ^ (uint32_t)j) << 4);
     const bool kc = k0 + 2 * j + p < P.K;
-    cp_async_zfill<8>(base + off, (r0 && kc) ? src + j * step : P.A, (r0 && kc) ? 8 : 0);
-    cp_async_zfill<8>(base + 4u * 2048u + off, (r1 && kc) ? src + j * step + 64 : P.A, (r1 && kc) ? 8 : 0);
+#pragma unroll
+    for (int h = 0; h < ROWS_PER_THREAD; h++) {
+      const bool ok = kc && (m0 + t + 64 * h < P.M);
+      cp_async_zfill<8>(base + (uint32_t)h * 4u * 2048u + off, ok ? src + j * step + 64 * h : P.A, ok ? 8 : 0);
+    }
   }
 }
-// B, column parity p: the 64 columns n0 + 2c + p of the tile x 16 k -> smem rows p*64 + c.  Thread t copies k = t & 15
-// of columns c = (t >> 4) + 4e, e = 0..15.
+// B, column parity p: the BN/2 columns n0 + 2c + p of the tile x 16 k -> smem rows p*BN/2 + c.  Thread t copies
+// k = t & 15 of columns c = (t >> 4) + 4e, e = 0..BN/8-1.
 __device__ __forceinline__ void helper_copy_b_half(const Params& P, uint32_t dstB, int n0, int k0, int p, int t) {
+  constexpr int COLS_PER_THREAD = (BN / 2) / (HELPER_THREADS / BK);   // 16 or 8
   const int c0 = t >> 4, kl = t & 15;
   const double* src = P.B + (long long)(n0 + 2 * c0 + p) * P.ldb + k0 + kl;
   const long long step = 8 * P.ldb;   // c += 4 -> n += 8
@@ -252,12 +257,12 @@ __device__ __forceinline__ void helper_copy_b_half(const Params& P, uint32_t dst
   const uint32_t x0 = (uint32_t)((kl >> 1) ^ c0) << 4, x1 = (uint32_t)((kl >> 1) ^ (c0 + 4)) << 4;   // row & 7 = c0 (+4)
   if ((n0 + BN <= P.N) && (k0 + BK <= P.K)) {
 #pragma unroll
-    for (int e = 0; e < 16; e++) cp_async_8(base + (uint32_t)e * 512u + ((e & 1) ? x1 : x0), src + e * step);
+    for (int e = 0; e < COLS_PER_THREAD; e++) cp_async_8(base + (uint32_t)e * 512u + ((e & 1) ? x1 : x0), src + e * step);
     return;
   }
   const bool kv = k0 + kl < P.K;   // edge stage: zero fill for k >= K and columns >= N
 #pragma unroll
-  for (int e = 0; e < 16; e++) {
+  for (int e = 0; e < COLS_PER_THREAD; e++) {
     const bool ok = kv && (n0 + 2 * (c0 + 4 * e) + p < P.N);
     cp_async_zfill<8>(base + (uint32_t)e * 512u + ((e & 1) ? x1 : x0), ok ? src + e * step : P.B, ok ? 8 : 0);
   }

@@ -22,9 +22,10 @@ int tma_split_bits(const Params& P);
 int tma_mis_halves(const Params& P);
 bool tma_split_ok(const Params& P);   // needs P.A, P.B, P.lda, P.ldb, P.K, P.N
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream);
-// the TMA kernel on 64 x 64 tiles (dgemm_kernels_small.cu); tmA / tmB point to CUtensorMaps with 16 x 16 / 16 x 64 boxes
+// the TMA kernel on 64 x 64 tiles (dgemm_kernels_small.cu); maps = {tmA, tmA1, tmB, tmB1} (CUtensorMap*, the second of a
+// pair only read when the operand's SPLIT bit is set), boxes 16 x 16 (or 16 x 8 per k parity) / 16 x 64 (16 x 32)
 constexpr int SMALL_BM = 64, SMALL_BN = 64;
-cudaError_t launch_tma_small(const void* tmA, const void* tmB, const Params& P, int grid, int dp_units,
+cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                              cudaStream_t stream);
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);

@@ -287,19 +287,11 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     g_launches++;
     return launch_ladder(P, variant, stream);
   }
-  if (variant == VARIANT_TMA && P.tile_small) {   // 64 x 64 tiles (dgemm_kernels_small.cu): plain tensor maps, stream-K
-    if (!tma_eligible(P) || P.splits != 1 || P.fetch_bytes) return cudaErrorInvalidValue;
-    CUtensorMap tmA, tmB;
-    if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, SMALL_BN))
-      return cudaErrorInvalidValue;
-    const int dp_units = P.sk_tiles > 0 ? P.sk_tile0 : tiles;
-    const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < num_sms ? dp_units : num_sms);
-    g_launches++;
-    return launch_tma_small(&tmA, &tmB, P, grid, dp_units, stream);
-  }
   if (variant == VARIANT_TMA) {
     const int split = tma_split_bits(P);
     if (split && !tma_split_ok(P)) return cudaErrorInvalidValue;
+    if (P.tile_small && (P.splits != 1 || P.fetch_bytes)) return cudaErrorInvalidValue;
+    const int bn = P.tile_small ? SMALL_BN : BN;   // (the A boxes are 16 rows high in both tile configurations)
     Params Q = P;
     Q.a_mis[0] = Q.a_mis[1] = Q.b_mis[0] = Q.b_mis[1] = 0;
     CUtensorMap tmA, tmA1, tmB, tmB1;
@@ -314,12 +306,19 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     }
     if (split & SPLIT_B) {
       if (P.fetch_bytes) return cudaErrorInvalidValue;
-      ok = ok && make_parity_tmap(&tmB, P.B, P.K, P.N, P.ldb, 0, BK, BN / 2, &Q.b_mis[0]) &&
-           make_parity_tmap(&tmB1, P.B, P.K, P.N, P.ldb, 1, BK, BN / 2, &Q.b_mis[1]);
+      ok = ok && make_parity_tmap(&tmB, P.B, P.K, P.N, P.ldb, 0, BK, bn / 2, &Q.b_mis[0]) &&
+           make_parity_tmap(&tmB1, P.B, P.K, P.N, P.ldb, 1, BK, bn / 2, &Q.b_mis[1]);
     } else {
-      ok = ok && make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN);
+      ok = ok && make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, bn);
     }
     if (!ok) return cudaErrorInvalidValue;
+    if (P.tile_small) {   // 64 x 64 tiles: dgemm_kernels_small.cu
+      const int dp_units = P.sk_tiles > 0 ? P.sk_tile0 : tiles;
+      const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < num_sms ? dp_units : num_sms);
+      const void* maps[4] = {&tmA, &tmA1, &tmB, &tmB1};
+      g_launches++;
+      return launch_tma_small(maps, split, Q, grid, dp_units, stream);
+    }
     const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
     static bool attr_done[64] = {};  // function attributes are per device
     int dev = 0;

@@ -19,7 +19,7 @@ namespace dg {
 
 static_assert(dg64::BM == SMALL_BM && dg64::BN == SMALL_BN, "dgemm_host.h must state the small tile's size");
 
-cudaError_t launch_tma_small(const void* tmA, const void* tmB, const Params& P, int grid, int dp_units,
+cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                              cudaStream_t stream) {
   constexpr int STAGES = 8;   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
   const int smem = STAGES * dg64::STAGE_BYTES + 2 * STAGES * 8 + 16 + 1024;
@@ -28,12 +28,31 @@ cudaError_t launch_tma_small(const void* tmA, const void* tmB, const Params& P, 
   cudaError_t err = cudaGetDevice(&dev);
   if (err != cudaSuccess) return err;
   if (!attr_done[dev & 63]) {
-    err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (err != cudaSuccess) return err;
+    const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_kernel<STAGES>, a, smem)) != cudaSuccess) return err;
+    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A>, a, smem)) != cudaSuccess) return err;
+    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_B>, a, smem)) != cudaSuccess) return err;
+    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A | SPLIT_B>, a, smem)) != cudaSuccess)
+      return err;
     attr_done[dev & 63] = true;
   }
-  dg64::dgemm_tma_ws_kernel<STAGES><<<grid, dg64::TMA_THREADS, smem, stream>>>(
-      *reinterpret_cast<const CUtensorMap*>(tmA), *reinterpret_cast<const CUtensorMap*>(tmB), P, dp_units);
+  const CUtensorMap &tmA = *reinterpret_cast<const CUtensorMap*>(maps[0]), &tmA1 = *reinterpret_cast<const CUtensorMap*>(maps[1]),
+                    &tmB = *reinterpret_cast<const CUtensorMap*>(maps[2]), &tmB1 = *reinterpret_cast<const CUtensorMap*>(maps[3]);
+  const int threads = dg64::TMA_THREADS;
+  switch (split) {
+    case SPLIT_NONE:
+      dg64::dgemm_tma_ws_kernel<STAGES><<<grid, threads, smem, stream>>>(tmA, tmB, P, dp_units);
+      break;
+    case SPLIT_A:
+      dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A><<<grid, threads, smem, stream>>>(tmA, tmA1, tmB, tmB1, P, dp_units);
+      break;
+    case SPLIT_B:
+      dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_B><<<grid, threads, smem, stream>>>(tmA, tmA1, tmB, tmB1, P, dp_units);
+      break;
+    default:
+      dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A | SPLIT_B><<<grid, threads, smem, stream>>>(tmA, tmA1, tmB, tmB1, P,
+                                                                                                  dp_units);
+  }
   return cudaGetLastError();
 }
 
