@@ -488,7 +488,33 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   // pageable caller memory (the reference harness mallocs its matrices, test.c:27-30) is staged through pinned slots
   // by a team of host threads instead of the driver's single bounce buffer; small calls are not worth the threads
   const double moved = 8.0 * ((need_ab ? (double)M * K + (double)K * N : 0.0) + (double)M * N);
-  const bool stage = moved >= (double)(8 << 20) && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
+  // Tiny calls (the low end of the reference harness, test.c:12-14: 100^3 moves 240 KB and computes for a few
+  // microseconds): one stream, four copies, one kernel, one synchronisation -- no planner, no events, no second stream.
+  // (harness, malloc'ed operands: 100^3 78 us -> see profiles/r01_harness_k20_v3.txt; the reference's kernel18: 60 us)
+  static const double kTinyBytes = getenv("DGEMM_B200_TINY_BYTES") ? atof(getenv("DGEMM_B200_TINY_BYTES")) : 1.5e6;
+  if (moved <= kTinyBytes) {
+    cudaStream_t s = c.s_compute;
+    // contiguous matrices (the harness passes LD = rows, utils.c:159-165) go as ONE 1-D copy: the driver's 2-D path
+    // costs more per call, and at this size the call is nothing but API latency
+    auto copy = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
+                    cudaMemcpyKind kind) -> cudaError_t {
+      if (ldd == rows && lds == rows) return cudaMemcpyAsync(dst, src, (size_t)rows * cols * 8, kind, s);
+      return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols, kind, s);
+    };
+    if (need_ab) {
+      CU_TRY(copy(c.a.p, ldaD, A, LDA, M, K, cudaMemcpyHostToDevice));
+      CU_TRY(copy(c.b.p, ldbD, B, LDB, K, N, cudaMemcpyHostToDevice));
+    }
+    if (need_c_in) CU_TRY(copy(c.c.p, ldcD, C, LDC, M, N, cudaMemcpyHostToDevice));
+    if ((st = run_device(c, M, N, K, alpha, c.a.p, ldaD, c.b.p, ldbD, beta, c.c.p, ldcD, s, dg::VARIANT_AUTO, 0))) return st;
+    CU_TRY(copy(C, LDC, c.c.p, ldcD, M, N, cudaMemcpyDeviceToHost));
+    CU_TRY(cudaStreamSynchronize(s));
+    return ok();
+  }
+  // (staging pays from about 16 MB: 600^3 = 8.6 MB took 1270 us staged against 490 us for 500^3 through the driver's
+  // own pageable path, 800^3 = 15 MB breaks even; profiles/r01_harness_k20_v2.txt)
+  static const double kStageMinBytes = getenv("DGEMM_B200_STAGE_MIN_BYTES") ? atof(getenv("DGEMM_B200_STAGE_MIN_BYTES")) : (double)(16 << 20);
+  const bool stage = moved >= kStageMinBytes && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
   const bool pa = stage && need_ab && dg::host_pointer_is_pageable(A), pb = stage && need_ab && dg::host_pointer_is_pageable(B),
              pc = stage && dg::host_pointer_is_pageable(C);
   auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
@@ -594,7 +620,10 @@ int run_host_op(int dev, bool ta, bool tb, int M, int N, int K, double alpha, co
   }
   if ((st = grow(c.c, (size_t)ldcD * N * 8))) return st;
   const double moved = 8.0 * ((need_ab ? (double)M * K + (double)K * N : 0.0) + (double)M * N);
-  const bool stage = moved >= (double)(8 << 20) && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
+  // (staging pays from about 16 MB: 600^3 = 8.6 MB took 1270 us staged against 490 us for 500^3 through the driver's
+  // own pageable path, 800^3 = 15 MB breaks even; profiles/r01_harness_k20_v2.txt)
+  static const double kStageMinBytes = getenv("DGEMM_B200_STAGE_MIN_BYTES") ? atof(getenv("DGEMM_B200_STAGE_MIN_BYTES")) : (double)(16 << 20);
+  const bool stage = moved >= kStageMinBytes && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
   auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols) {
     if (stage && dg::host_pointer_is_pageable(src)) return dg::staged_h2d(dst, ldd, src, lds, rows, cols, c.s_h2d, dev);
     return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
