@@ -29,6 +29,28 @@ def test_v20_host_pointers(dg, shape, pad, alpha, beta):
     assert np.array_equal(A, A_before) and np.array_equal(B, B_before)  # A and B are read-only
 
 
+@pytest.mark.parametrize("shape,pad,alpha,beta", [
+    ((100, 100, 100), (0, 0, 0), 2.0, 0.0),          # the harness' first size (test.c:12-14): contiguous 1-D copies
+    ((100, 100, 100), (0, 0, 0), 1.0, 1.0),
+    ((200, 150, 180), (3, 1, 2), 2.5, 0.5),          # padded leading dimensions: 2-D copies, padding rows survive
+    ((101, 99, 97), (0, 0, 0), -1.0, 1.0),           # odd everything (the reference drops odd M/N)
+    ((1, 1, 1), (0, 0, 0), 1.0, 1.0),
+    ((7, 9, 8), (1, 0, 5), 1.0, 0.5),
+])
+def test_v20_tiny_calls_take_the_latency_path(dg, shape, pad, alpha, beta):
+    """Calls that move <= DGEMM_B200_TINY_BYTES (1.5e6) run on one stream without the planner (csrc/dgemm_api.cu,
+    run_host_single): same results, same padding guarantees, beta == 0 does not read C."""
+    M, N, K = shape
+    assert 8.0 * (M * K + K * N + M * N) <= 1.5e6
+    A, B, C0 = gu.make_inputs(M, N, K, pad, c_fill=np.nan if beta == 0.0 else None)
+    Cg = C0.copy(order="F")
+    dg.mydgemm_gpu_v20(M, N, K, alpha, A, A.shape[0], B, B.shape[0], beta, Cg, Cg.shape[0])
+    if beta == 0.0:
+        C0[:M, :] = 0.0
+    gu.check(M, N, K, alpha, A, B, beta, C0, Cg)
+    assert np.isfinite(Cg[:M, :]).all()
+
+
 def test_test_kernel_dispatch(dg):
     m = n = k = 400
     A, B, C0 = gu.make_inputs(m, n, k, dist="reference")
