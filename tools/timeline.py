@@ -14,7 +14,7 @@ for rep in range(3):
     dg.lib.dgemm_b200_h2d(tl, 148 * 16, host.ctypes.data, 148 * 16, 148 * 16, 1, None)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(tl)
-    dg.dgemm_device(M, N, K, 1.0, dA, M, dB, K, 1.0, dC, M, 0, 1, splits)
+    dg.dgemm_device(M, N, K, 1.0, dA, M, dB, K, 1.0, dC, M, 0, int(os.environ.get("TL_VARIANT", "1")), splits)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(None)
 out = np.zeros((148, 16), dtype=np.uint64)
