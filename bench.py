@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cublas", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the whole-panel oracle check before the timed region")
+    ap.add_argument("--no-v21", action="store_true", help="N > 1: skip the single-process mydgemm_gpu_v21 leg")
+    ap.add_argument("--no-scale-base", action="store_true", help="N = 1: skip the one 65536^3 pass (strong-scaling base)")
     return ap.parse_args()
 
 
@@ -133,6 +136,34 @@ def cpu_reference_step(n, nthr, state):
     return time.perf_counter() - t0
 
 
+REF_PANEL = 8192  # kernel19 is wrong / crashes for N > 9216 per call: the named workload goes in column panels
+
+
+def cpu_reference_full_step(size, nthr, state, panels=None):
+    """One step of the NAMED workload on the host: C = A*B + C at M=N=K=size as kernel19 calls on column panels of
+    REF_PANEL columns (M = K = size per call; mathematically the same DGEMM, and the same partition the multi-GPU layer
+    uses).  `panels` limits the step to the first few panels (the bounded fallback).  Returns (seconds, columns done)."""
+    import oracle_lib as ol
+    if "A" not in state:
+        state["kind"] = "reference" if ol.have_ref() else "port"
+        state["A"] = ol.fill_signed(size, size, size, 11)
+        state["B"] = ol.fill_signed(size, size, size, 12)
+        state["C"] = ol.fill_signed(size, size, size, 13)
+        if state["kind"] == "reference":
+            ol.ref().ref_set_num_threads(nthr)
+    bounds = list(range(0, size, REF_PANEL)) + [size]
+    if panels:
+        bounds = bounds[: panels + 1]
+    t0 = time.perf_counter()
+    for n0, n1 in zip(bounds[:-1], bounds[1:]):
+        Bp, Cp = state["B"][:, n0:n1], state["C"][:, n0:n1]   # column slices of Fortran-ordered arrays keep their ld
+        if state["kind"] == "reference":
+            ol.call_gemm(ol.ref().mydgemm_cpu_v19, size, n1 - n0, size, 1.0, state["A"], Bp, 1.0, Cp)
+        else:
+            ol.oracle_k19(size, n1 - n0, size, 1.0, state["A"], Bp, 1.0, Cp, nthr)
+    return time.perf_counter() - t0, bounds[-1]
+
+
 def cpu_model():
     try:
         with open("/proc/cpuinfo") as f:
@@ -174,31 +205,71 @@ def run_cpu_baseline(sample_n, reps):
 
 
 def reference_arm(args):
-    """--impl reference: the reference's CPU implementation of the path, timed on this box's host cores."""
+    """--impl reference: the reference's own CPU implementation of the path (unmodified mydgemm_cpu_v19 from
+    oracle/_ref/libref.so; the oracle port where the reference could not be compiled), all host cores.
+
+    N = 1: every step is the NAMED workload, M=N=K=16384, as kernel19 calls on 8192-column panels (SURVEY.md F2 forbids
+    N > 9216 per call; F3: thread count with even row bands); --steps / --warmup are honoured.  If one step turns out so
+    slow that the run would exceed BENCH_REF_BUDGET_S (default 420 s), the steps are cut to the first panel(s) and the
+    line says so (same_config false).
+    N > 1: the workload is 65536^3, which the reference cannot index (32-bit offsets): each step is an
+    8192^3 kernel19 sample and the line says so."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     N = args.gpus
     size = args.size or (16384 if N == 1 else 65536)
-    sample_n = int(os.environ.get("BENCH_REF_SAMPLE", 8192 if (os.cpu_count() or 1) >= 8 else 4096))
     steps = args.steps or 3
+    warmup = max(args.warmup, 0)
     cores = os.cpu_count() or 1
-    nthr = pick_threads(sample_n, cores)
     os.environ.setdefault("OMP_PROC_BIND", "close")
     os.environ.setdefault("OMP_PLACES", "cores")
+    forced_sample = os.environ.get("BENCH_REF_SAMPLE")
+    budget = float(os.environ.get("BENCH_REF_BUDGET_S", "420"))
     state = {}
-    for _ in range(max(1, min(args.warmup, 1))):  # each sample is seconds of CPU work; one warm-up is enough
-        cpu_reference_step(sample_n, nthr, state)
-    t = [cpu_reference_step(sample_n, nthr, state) for _ in range(steps)]
-    total = sum(t)
-    value = 2.0 * sample_n ** 3 * steps / total / 1e12
-    sample = (f"each step = reference kernel19 on M=N=K={sample_n} (a {sample_n}^3 sub-problem of the {size}^3 "
-              f"workload; kernel19 cannot take N > 9216, SURVEY.md F2), {nthr} threads on {cores} host cores "
-              f"({cpu_model()})")
+    full = forced_sample is None and size <= 32768 and size % 2 == 0
+    if full:
+        nthr = pick_threads(size, cores)
+        n_panels = -(-size // REF_PANEL)
+        t_first, _ = cpu_reference_full_step(size, nthr, state)           # also the first warm-up step
+        panels = None
+        if t_first * (steps + max(warmup - 1, 0)) > budget:               # bounded fallback: fewer panels per step
+            panels = max(1, int(budget / (steps + max(warmup - 1, 0)) / (t_first / n_panels)))
+            panels = min(panels, n_panels)
+        for _ in range(max(warmup - 1, 0)):
+            cpu_reference_full_step(size, nthr, state, panels)
+        t, cols = [], size
+        for _ in range(steps):
+            dt, cols = cpu_reference_full_step(size, nthr, state, panels)
+            t.append(dt)
+        total = sum(t)
+        value = 2.0 * size * cols * size * steps / total / 1e12
+        same = cols == size
+        sample = (f"each step = the whole M=N=K={size} DGEMM as {-(-cols // REF_PANEL)} reference kernel19 call(s) on "
+                  f"{REF_PANEL}-column panels (M=K={size} per call; kernel19 cannot take N > 9216, SURVEY.md F2)"
+                  + ("" if same else f" -- ONLY the first {cols} of {size} columns per step: one full step took {t_first:.1f} s "
+                                     f"and {steps} of them would exceed the {budget:.0f} s budget")
+                  + f", {nthr} threads on {cores} host cores ({cpu_model()})")
+        sample_shape = [size, cols, size]
+    else:
+        sample_n = int(forced_sample or (8192 if cores >= 8 else 4096))
+        nthr = pick_threads(sample_n, cores)
+        for _ in range(max(1, warmup)):
+            cpu_reference_step(sample_n, nthr, state)
+        t = [cpu_reference_step(sample_n, nthr, state) for _ in range(steps)]
+        total = sum(t)
+        value = 2.0 * sample_n ** 3 * steps / total / 1e12
+        same = False
+        sample = (f"each step = reference kernel19 on M=N=K={sample_n}, a sample of the {size}^3 workload "
+                  + ("(the reference cannot index 65536^2 matrices: 32-bit offsets, SURVEY.md F5; and kernel19 cannot take "
+                     "N > 9216, F2)" if forced_sample is None else "(BENCH_REF_SAMPLE)")
+                  + f", {nthr} threads on {cores} host cores ({cpu_model()})")
+        sample_shape = [sample_n] * 3
     line = {"impl": "reference", "metric": "fp64_dgemm_tflops", "value": value, "unit": UNIT, "n_gpus": N,
-            "steps": steps, "warmup": 1, "ms_per_step": 1e3 * total / steps, "higher_is_better": True,
+            "steps": steps, "warmup": max(warmup, 1), "ms_per_step": 1e3 * total / steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"M=N=K={size} column-major DGEMM alpha=1 beta=1", "sample": sample},
+            "config": {"workload": f"M=N=K={size} column-major DGEMM C=alpha*A*B+beta*C, alpha=1 beta=1, LD=dim",
+                       "sample": sample, "sample_shape_mnk": sample_shape, "same_config": same},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthr, "kind": state["kind"], "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -252,8 +323,16 @@ def main():
         raise SystemExit("bench.py: no B200 visible — the DGEMM path is CUDA-only (no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    host_group = None
     if N > 1:
         dist.init_process_group("nccl", device_id=dev)
+        # host-side barriers (between end-to-end passes, around the single-process v21 leg) go through gloo: an NCCL
+        # barrier is a GPU kernel that would sit on the SMs of the waiting ranks
+        host_group = dist.new_group(backend="gloo")
+
+    def host_barrier():
+        if N > 1:
+            dist.barrier(group=host_group)
 
     size = args.size or (16384 if N == 1 else 65536)
     M = Nn = K = size
@@ -262,19 +341,27 @@ def main():
     warmup = max(args.warmup, 0)
     stream = torch.cuda.current_stream()
     sptr = stream.cuda_stream
+    fused = N > 1 and args.exchange == "fused"
+
+    # ---- parity of the multi-GPU paths, BEFORE anything is timed: whole panels against the oracle --------------------
+    parity = None
+    if N > 1 and fused and not args.no_parity:
+        parity = parity_panels(torch, dist, dg, N, rank, dev, host_group)
+        if not parity["max_ratio"] <= 2.0:
+            raise SystemExit(f"bench.py: multi-GPU parity FAILED: {json.dumps(parity)}")
 
     # ---- operands resident in HBM: every rank owns a column panel of B and C and a K-slab of A ----------------
     nb = partition(Nn, N, 128)
     kb = partition(K, N, 16)
     n0, n1 = nb[rank], nb[rank + 1]
     ncols = n1 - n0
-    fused = N > 1 and args.exchange == "fused"
     ctx = {"peers": {}}
     if fused:
-        # A lives in a plain cudaMalloc buffer (IPC-exportable); peers map it and the GEMM kernel pulls from it
-        A_ptr = dg.malloc(8 * M * K)
+        # A lives in an exchange buffer (cudaMalloc, IPC-exportable, sequence words behind A); peers map it and the GEMM
+        # kernel pulls from it
+        A_ptr = dg.exchange_alloc(M, K)
         handles = [None] * N
-        dist.all_gather_object(handles, dg.ipc_export(A_ptr))
+        dist.all_gather_object(handles, dg.ipc_export(A_ptr), group=host_group)
         ctx["peers"] = {g: dg.ipc_open(handles[g]) for g in range(N) if g != rank}
         A = None
     else:
@@ -288,8 +375,7 @@ def main():
     dg.fill_signed(B.data_ptr(), K, ncols, K, 2, 0, n0, sptr)
     dg.fill_signed(Cm.data_ptr(), M, ncols, M, 3, 0, n0, sptr)
     torch.cuda.synchronize()
-    if N > 1:
-        dist.barrier()
+    host_barrier()
 
     def gemm_fetch(kbeg, kc, b_eff, fetch):
         src = dst = nbytes = 0
@@ -363,15 +449,44 @@ def main():
     flops = 2.0 * M * Nn * K
     value = flops * steps / (total_ms * 1e-3) / 1e12
 
-    # ---- end to end through the reference-facing host-pointer entry (pinned host buffers) -----------------------
+    # ---- end to end through the reference-facing host-pointer entries (pinned host buffers) ---------------------
     e2e = None
-    if not args.no_e2e:
-        e2e = run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm,
-                      max(2, min(steps, 5)), fused, step, ctx["peers"])
+    if not args.no_e2e and (N == 1 or fused):
+        xbufs = [A_ptr if g == rank else ctx["peers"][g] for g in range(N)] if N > 1 else None
+        e2e = run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, B, Cm, max(2, min(steps, 5)),
+                      xbufs, host_barrier, host_group)
+
+    cublas = None
+    if rank == 0 and not args.no_cublas and N == 1:
+        cublas = cublas_ceiling(torch, A, B, Cm, M, Nn, K)
+
+    # ---- release the per-rank operands; then the legs that need the GPUs to themselves ---------------------------
+    n_sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    for g, p in ctx["peers"].items():
+        dg.ipc_close(p)
+    host_barrier()
+    if fused:
+        dg.free(A_ptr)
+    del A, B, Cm
+    torch.cuda.empty_cache()
+
+    # the strong-scaling base: the 65536^3 problem the N > 1 lines are quoted on, ONE pass on one GPU (BASELINE configs[3])
+    scale_base = None
+    if N == 1 and args.size is None and not args.no_scale_base:
+        scale_base = strong_scaling_base(torch, dg, dev, 65536)
+
+    # the single-process multi-GPU entry with the reference's own 11-argument signature: rank 0 drives all N GPUs alone
+    e2e_v21 = None
+    if N > 1 and fused and not args.no_v21:
+        dg.shutdown()   # every rank returns its cached device buffers before rank 0 takes the box
+        torch.cuda.synchronize()
+        host_barrier()
+        if rank == 0:
+            e2e_v21 = run_v21(torch, dg, N, int(os.environ.get("BENCH_V21_SIZE", "32768")), 2)
+        host_barrier()
 
     if rank != 0:
         if N > 1:
-            dist.barrier()
             dist.destroy_process_group()
         return
 
@@ -380,7 +495,6 @@ def main():
     kern_ms = statistics.mean(step_ms) / 1.0  # one rank's step; at N = 1 a step is exactly one kernel launch
     achieved = (flops / N) / (kern_ms * 1e-3) / 1e12 if N == 1 else value / N
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-    n_sms = torch.cuda.get_device_properties(dev).multi_processor_count
     peak = n_sms * FLOP_PER_CLK_PER_SM * sm_mhz * 1e6 / 1e12
     probe = load_profile_json("profiles/fp64_peak_probe.json")
     traffic = load_profile_json("profiles/ncu_traffic.json")
@@ -391,20 +505,24 @@ def main():
                                "127.5 flop/clk/SM with DMMA alone)",
                 "dmma_probe_tflops": (probe or {}).get("dmma_tflops"),
                 "frac_of_dmma_probe": (achieved / probe["dmma_tflops"]) if probe and probe.get("dmma_tflops") else None,
-                "traffic": (traffic or {}).get(str(size)),
+                "traffic": (traffic or {}).get(str(size)) if N == 1 else None,
+                "traffic_source": "STORED: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of "
+                                  "this kernel at this size (profiles/ncu_traffic.json) -- not measured in this run"
+                                  if N == 1 else "no single-kernel capture of the sharded step (see profiles/ for the "
+                                                 "fused-fetch kernel's ncu counters)",
                 "algorithmic_bytes": 8.0 * (M * K + K * Nn + 2 * M * Nn),
                 "kernel": "dg::dgemm_tma_ws_kernel<6>", "kernels_per_step": kernels_per_step}
 
     cpu_baseline = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and N == 1:
         try:
             cpu_baseline = run_cpu_baseline(8192 if (os.cpu_count() or 1) >= 8 else 4096, 2)
         except Exception as e:  # noqa: BLE001 - the baseline is a report, never a reason to lose the GPU number
             cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(e)}
-
-    cublas = None
-    if not args.no_cublas and N == 1:
-        cublas = cublas_ceiling(torch, A, B, Cm, M, Nn, K)
+    elif N > 1:
+        cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
+                        "sample": "not timed at N > 1 (the contract times it on rank 0 at N = 1 only: beside N-1 live ranks "
+                                  "the host cores are contended); see the N = 1 line and the --impl reference arm"}
 
     line = {
         "metric": "fp64_dgemm_tflops", "value": value, "unit": UNIT, "n_gpus": N, "steps": steps, "warmup": warmup,
@@ -423,10 +541,184 @@ def main():
         "spot_check_max_err_over_bound": value_check,
         "pct_of_fp64_peak": 100.0 * value / (N * peak),
     }
+    if parity is not None:
+        line["parity_panel_max_ratio"] = parity["max_ratio"]
+        line["parity_panels"] = parity
+    if e2e_v21 is not None:
+        line["e2e_v21"] = e2e_v21
+    if scale_base is not None:
+        line["strong_scaling_base"] = scale_base
     emit(line)
     if N > 1:
-        dist.barrier()
         dist.destroy_process_group()
+
+
+def parity_panels(torch, dist, dg, N, rank, dev, host_group):
+    """Whole-panel parity of BOTH multi-GPU paths at sizes the oracle finishes in seconds, every entry, bound c = 2:
+      (i)  dgemm_b200_rank_pipeline  host operands -> pipelined uploads, NVLink pulls behind sequence words, deferred C, D2H
+      (ii) the fused device step     sharded_dgemm_step_fused over dgemm_b200_device_fetch (what `value` times)
+    The oracle (oracle/liboracle.so, kernel18's arithmetic restated) is the CHECKER here, exactly as in tests/: it is never
+    timed and nothing it computes reaches a reported number."""
+    import numpy as np
+    import oracle_lib as ol
+    from dgemm_b200.sharding import partition, sharded_dgemm_step_fused
+    out = {"bound": "|C-C_ref| <= 2*K*eps*(|alpha||A||B| + |beta*C0|), every entry of every rank's panel", "cases": []}
+    worst = 0.0
+    sptr = torch.cuda.current_stream().cuda_stream
+    for (M, Nn, K, alpha, beta) in [(4096, 1024 * N, 4096, 1.0, 1.0), (1000, 1003, 997, 2.5, 0.5)]:
+        nb, kb = partition(Nn, N, 128), partition(K, N, 16)
+        n0, ncols = nb[rank], nb[rank + 1] - nb[rank]
+        k0, kc = kb[rank], kb[rank + 1] - kb[rank]
+        Ah = ol.fill_signed(M, K, M, 1)
+        Bh = ol.fill_signed(K, max(ncols, 1), K, 2, col0=n0)
+        C0 = ol.fill_signed(M, max(ncols, 1), M, 3, col0=n0)
+        want = C0.copy(order="F")
+        if ncols > 0:
+            ol.oracle_k18(M, ncols, K, alpha, Ah, Bh, beta, want)
+        x = dg.exchange_alloc(M, K)
+        handles = [None] * N
+        dist.all_gather_object(handles, dg.ipc_export(x), group=host_group)
+        peers = {g: dg.ipc_open(handles[g]) for g in range(N) if g != rank}
+        xbufs = [x if g == rank else peers[g] for g in range(N)]
+        ldaD = (M + 1) & ~1
+        # (i) the rank pipeline, from host memory
+        Cg = C0.copy(order="F")
+        A_slab = np.asfortranarray(Ah[:, k0:k0 + kc])
+        dg.rank_pipeline(M, ncols, K, alpha, A_slab, M, Bh, K, beta, Cg, M, rank, N, kb, xbufs, 0)
+        r1 = ol.bound_ratio(M, ncols, K, alpha, Ah, Bh, beta, C0, Cg, want)[0] if ncols > 0 else 0.0
+        dist.barrier(group=host_group)
+        # (ii) the fused device step: own slab resident, everything else NaN until it is pulled
+        nanfill = torch.full((ldaD * K,), float("nan"), dtype=torch.float64, device=dev)
+        dg.dgemm_device_fetch(0, 0, 0, 0.0, 0, 1, 0, 1, 0.0, 0, 1, sptr, nanfill.data_ptr(), x, 8 * ldaD * K)
+        dg._check(dg.lib.dgemm_b200_h2d(x + 8 * k0 * ldaD, ldaD, A_slab.ctypes.data, M, M, kc, sptr))
+        dB = torch.from_numpy(np.ascontiguousarray(Bh.T)).to(dev)    # column-major K x ncols == row-major ncols x K
+        dC = torch.from_numpy(np.ascontiguousarray(C0.T)).to(dev)
+        torch.cuda.synchronize()
+        dist.barrier(group=host_group)
+
+        def gemm_fetch(kbeg, kk, b_eff, fetch):
+            src = dst = nbytes = 0
+            if fetch is not None:
+                owner, fk, fc = fetch
+                src, dst, nbytes = peers[owner] + 8 * fk * ldaD, x + 8 * fk * ldaD, 8 * fc * ldaD
+            dg.dgemm_device_fetch(M, ncols, kk, alpha, x + 8 * kbeg * ldaD, ldaD, dB.data_ptr() + 8 * kbeg, K, b_eff,
+                                  dC.data_ptr(), M, sptr, src, dst, nbytes)
+        if ncols > 0:
+            sharded_dgemm_step_fused(rank, N, kb, beta, gemm_fetch)
+        torch.cuda.synchronize()
+        r2 = 0.0
+        if ncols > 0:
+            got = np.asfortranarray(dC.cpu().numpy().T)
+            r2 = ol.bound_ratio(M, ncols, K, alpha, Ah, Bh, beta, C0, got, want)[0]
+        dist.barrier(group=host_group)   # nobody still pulls from a buffer that is about to be freed
+        for p in peers.values():
+            dg.ipc_close(p)
+        dist.barrier(group=host_group)
+        dg.free(x)
+        del nanfill, dB, dC
+        both = torch.tensor([r1, r2], dtype=torch.float64, device=dev)
+        dist.all_reduce(both, op=dist.ReduceOp.MAX)
+        r1, r2 = float(both[0].item()), float(both[1].item())
+        if not (r1 == r1 and r2 == r2):   # NaN: a pull or a multiply ran ahead of its data
+            r1 = r2 = float("inf")
+        out["cases"].append({"M": M, "N": Nn, "K": K, "alpha": alpha, "beta": beta,
+                             "rank_pipeline_max_ratio": r1, "fused_step_max_ratio": r2})
+        worst = max(worst, r1, r2)
+    out["max_ratio"] = worst
+    return out
+
+
+def strong_scaling_base(torch, dg, dev, size):
+    """One kernel-only pass of the size^3 problem on ONE GPU (3 x 34 GB at 65536): the denominator of the strong-scaling
+    curve, so that the N > 1 lines and the N = 1 line are the same problem.  Sampled entries are checked."""
+    import numpy as np
+    M = size
+    try:
+        free, _total = torch.cuda.mem_get_info(dev)
+        if free < 3 * 8 * M * M + (8 << 30):
+            return {"size": size, "value": None, "note": f"skipped: {free / 1e9:.0f} GB free, needs {3 * 8 * M * M / 1e9:.0f} GB"}
+        sptr = torch.cuda.current_stream().cuda_stream
+        bufs = [dg.malloc(8 * M * M) for _ in range(3)]
+        for i, p in enumerate(bufs):
+            dg.fill_signed(p, M, M, M, i + 1, 0, 0, sptr)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        dg.dgemm_device(M, M, M, 1.0, bufs[0], M, bufs[1], M, 1.0, bufs[2], M, sptr)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        rng = np.random.default_rng(7)
+        idx = [(int(rng.integers(M)), int(rng.integers(M))) for _ in range(3)] + [(M - 1, M - 1)]
+        host = np.zeros(1)
+        got = []
+        for i, j in idx:
+            dg._check(dg.lib.dgemm_b200_d2h(host.ctypes.data, 1, bufs[2] + 8 * (j * M + i), 1, 1, 1, None))
+            dg._check(dg.lib.dgemm_b200_sync(None))
+            got.append(float(host[0]))
+        c0 = [float(gen_signed(3, np.array([i]), np.array([j]))[0]) for i, j in idx]
+        check = spot_check(c0, got, idx, M, M, 0, 1.0, 1.0)
+        for p in bufs:
+            dg.free(p)
+        if not check <= 1.0:
+            raise SystemExit(f"bench.py: {size}^3 single-GPU pass is WRONG: max |err|/bound = {check}")
+        return {"size": size, "value": 2.0 * M ** 3 / ms / 1e9, "unit": UNIT, "ms": ms, "passes": 1,
+                "spot_check_max_err_over_bound": check,
+                "note": f"kernel-only, one pass of M=N=K={size} on one GPU after the {16384}^3 runs warmed the device: the same "
+                        "problem the N > 1 lines shard (strong-scaling denominator)"}
+    except dg.DgemmError as e:
+        return {"size": size, "value": None, "note": f"skipped: {e}"}
+
+
+def run_v21(torch, dg, G, size, reps):
+    """mydgemm_gpu_v21 -- the reference's 11-argument signature, ONE process driving all G GPUs -- on pinned host operands,
+    copies inside the timed region.  Rank 0 only; the other ranks have released their GPUs and wait on a host barrier."""
+    import numpy as np
+    M = Nn = K = size
+    dg.lib.dgemm_b200_set_max_gpus(G)
+    nbytes = 8 * M * M
+    hA, hB, hC = (dg.lib.dgemm_b200_host_alloc(nbytes) for _ in range(3))
+    if not (hA and hB and hC):
+        return {"value": None, "note": "pinned host allocation failed"}
+    # inputs: generated on the device, copied out (no 26 GB numpy fill on the host)
+    d = dg.malloc(nbytes)
+    for seed, h in ((1, hA), (2, hB), (3, hC)):
+        dg.fill_signed(d, M, M, M, seed, 0, 0, 0)
+        dg._check(dg.lib.dgemm_b200_d2h(h, M, d, M, M, M, None))
+        dg._check(dg.lib.dgemm_b200_sync(None))
+    dg.free(d)
+    rng = np.random.default_rng(4321)
+    idx = [(int(rng.integers(M)), int(rng.integers(Nn))) for _ in range(12)] + [(M - 1, Nn - 1), (0, 0)]
+    # sampled entries straddle every GPU's panel boundary as well
+    per = -(-(-(-Nn // G)) // 128) * 128
+    idx += [(int(rng.integers(M)), min(Nn - 1, g * per + d)) for g in range(1, G) for d in (-1, 0)]
+    import ctypes
+    view = (ctypes.c_double * (M * Nn)).from_address(hC)
+
+    def call():
+        dg.mydgemm_gpu_v21(M, Nn, K, 1.0, hA, M, hB, K, 1.0, hC, M)
+    call()   # warm-up: allocates the exchange buffers, enables peer access
+    before = [view[j * M + i] for i, j in idx]
+    call()
+    after = [view[j * M + i] for i, j in idx]
+    check = spot_check(before, after, idx, M, K, 0, 1.0, 1.0)
+    dg.reset_launch_count()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        call()
+    dt = time.perf_counter() - t0
+    launches = dg.launch_count()
+    for h in (hA, hB, hC):
+        dg.lib.dgemm_b200_host_free(h)
+    dg.shutdown()
+    if not check <= 1.0:
+        raise SystemExit(f"bench.py: mydgemm_gpu_v21 result is WRONG: max |err|/bound = {check}")
+    return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "unit": UNIT, "ms_per_step": 1e3 * dt / reps, "reps": reps,
+            "size": size, "gpus": G, "h2d_bytes_per_step": 3 * nbytes, "d2h_bytes_per_step": nbytes, "gpu_launches": launches,
+            "spot_check_max_err_over_bound": check,
+            "spot_check": f"{len(idx)} entries (incl. both sides of every panel boundary) recomputed on the host in long double",
+            "api": f"mydgemm_gpu_v21(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC), M=N=K={size}, pinned host pointers, one process "
+                   f"driving {G} GPUs (one host thread per GPU, the same rank pipeline as dgemm_b200_rank_pipeline)"}
 
 
 def gen_signed(seed, rows, cols):
@@ -485,10 +777,11 @@ def cublas_ceiling(torch, A, B, Cm, M, Nn, K):
     return {"tflops": 2.0 * M * Nn * K / ms / 1e9, "ms": ms, "note": "torch.matmul(float64) -> cublasDgemm; ceiling only"}
 
 
-def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, A, B, Cm, reps, fused, step, peers):
+def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr, B, Cm, reps, xbufs, host_barrier, host_group):
     """Same metric through the public host-pointer API with HOST (pinned) buffers, copies inside the timed region.
-    N = 1: mydgemm_gpu_v20 (the reference's 11-argument signature).  N > 1: each rank stages its own K-slab of A and
-    its B/C panels from pinned memory, runs the sharded step (A exchanged over NVLink), copies its C panel back."""
+    N = 1: mydgemm_gpu_v20 (the reference's 11-argument signature).
+    N > 1: dgemm_b200_rank_pipeline, ONE library call per rank and pass: the rank's K-slab of A, its B and C panels go in
+    from pinned memory, A is completed over NVLink, the C panel comes back.  One host barrier between passes."""
     n0, n1 = nb[rank], nb[rank + 1]
     ncols = n1 - n0
     k0, k1 = kb[rank], kb[rank + 1]
@@ -502,113 +795,17 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
     torch.cuda.synchronize()
     h2d = 8 * (hA.numel() + hB.numel() + hC.numel())
     d2h = 8 * hC.numel()
-    stream = torch.cuda.current_stream()
-    sptr = stream.cuda_stream
-    token = torch.zeros(1, device=dev)
+    state = {"pass": 0}
 
-    def one_simple():
-        dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * k0 * M, M, hA.data_ptr(), M, M, k1 - k0, sptr))
-        dist.all_reduce(token)  # stream-ordered barrier: every owner's K-slab is in its HBM before anyone pulls it
-        dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr(), K, hB.data_ptr(), K, K, ncols, sptr))
-        dg._check(dg.lib.dgemm_b200_h2d(Cm.data_ptr(), M, hC.data_ptr(), M, M, ncols, sptr))
-        step()
-        dist.all_reduce(token)  # ... and nobody still reads a slab when its owner overwrites it in the next pass
-        dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr(), M, Cm.data_ptr(), M, M, ncols, sptr))
-        stream.synchronize()
-
-    copy_s, d2h_s = torch.cuda.Stream(), torch.cuda.Stream()
-    from dgemm_b200.sharding import partition, slab_order
-    # column sub-panels of this rank's panel: four main pieces and two narrow last ones (short exposed last D2H)
-    tails = [384, 128] if ncols >= 4096 else []
-    sp = partition(ncols - sum(tails), 4 if ncols - sum(tails) >= 4 * 256 else 1, 128)
-    for t in tails:
-        sp.append(sp[-1] + t)
-    SP = len(sp) - 1
-    order = [g for g in slab_order(rank, N) if kb[g + 1] > kb[g]] if N > 1 else []
-    # the own K-slab goes in as sub-slabs so that the first call waits for a quarter of it
-    Q = 4 if (k1 - k0) >= 4 * 512 else 1
-    qb = [k0 + x for x in partition(k1 - k0, Q, 16)]
-    X = torch.empty(M * max(ncols, 1), dtype=torch.float64, device=dev) if (N > 1 and beta != 0.0) else None
-
-    def one_pipelined():
-        """Rank-local pipeline on three streams.  Compute: (K-slab, column sub-panel) calls in slab-major order, the
-        own slab first and in Q sub-slabs.  H2D, in need-order: own A sub-slabs with their B blocks, the B blocks of
-        the other slabs, and LAST the C sub-panels — C is deferred: every sub-panel starts with beta = 0 and gets
-        beta*C_in added (dgemm_b200_add_scaled) after its last slab, so the start of the pipeline waits for a quarter
-        slab of A and one B block only.  Every C sub-panel goes back as soon as it is finished.  The NVLink pull of
-        slab i+1 rides on a call of slab i (the LAST call of the own slab for the first pull: by then every owner's
-        slab has reached its HBM, which the stream-ordered all_reduce in front of that call guarantees)."""
-        cptr = copy_s.cuda_stream
-        copy_s.wait_stream(stream)
-        ev_b = {}
-        for q in range(Q):
-            ka, kc = qb[q], qb[q + 1] - qb[q]
-            if kc <= 0:
-                continue
-            dg._check(dg.lib.dgemm_b200_h2d(A_ptr + 8 * ka * M, M, hA.data_ptr() + 8 * (ka - k0) * M, M, M, kc, cptr))
-            for j in range(SP):
-                c0, nc = sp[j], sp[j + 1] - sp[j]
-                off = 8 * (c0 * K + ka)
-                dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr() + off, K, hB.data_ptr() + off, K, kc, nc, cptr))
-                ev_b[(0, q, j)] = copy_s.record_event()
-        ev_a = copy_s.record_event()
-        for i, g in enumerate(order):
-            if i == 0:
-                continue
-            for j in range(SP):
-                c0, nc = sp[j], sp[j + 1] - sp[j]
-                off = 8 * (c0 * K + kb[g])
-                dg._check(dg.lib.dgemm_b200_h2d(B.data_ptr() + off, K, hB.data_ptr() + off, K, kb[g + 1] - kb[g], nc, cptr))
-                ev_b[(i, 0, j)] = copy_s.record_event()
-        ev_x = []
-        if X is not None:
-            for j in range(SP):
-                c0, nc = sp[j], sp[j + 1] - sp[j]
-                dg._check(dg.lib.dgemm_b200_h2d(X.data_ptr() + 8 * c0 * M, M, hC.data_ptr() + 8 * c0 * M, M, M, nc, cptr))
-                ev_x.append(copy_s.record_event())
-        last_i = len(order) - 1
-        js = [j for j in range(SP) if sp[j + 1] > sp[j]]
-        for i, g in enumerate(order):
-            subs = [(qb[q], qb[q + 1] - qb[q], q) for q in range(Q)] if i == 0 else [(kb[g], kb[g + 1] - kb[g], 0)]
-            subs = [t for t in subs if t[1] > 0]
-            for si, (ka, kc, q) in enumerate(subs):
-                for j in js:
-                    c0, nc = sp[j], sp[j + 1] - sp[j]
-                    stream.wait_event(ev_b[(i, q, j)])
-                    src = dst = nbytes = 0
-                    if i + 1 < len(order):
-                        first_pull = i == 0 and si == len(subs) - 1 and j == js[-1]
-                        if first_pull:
-                            stream.wait_event(ev_a)
-                            dist.all_reduce(token)  # every owner's K-slab is in its HBM before anyone pulls it
-                        if first_pull or (i > 0 and j == js[0]):
-                            nx = order[i + 1]
-                            src, dst = peers[nx] + 8 * kb[nx] * M, A_ptr + 8 * kb[nx] * M
-                            nbytes = 8 * (kb[nx + 1] - kb[nx]) * M
-                    first_call = i == 0 and si == 0
-                    b_eff = (0.0 if X is not None else beta) if first_call else 1.0
-                    dg.dgemm_device_fetch(M, nc, kc, alpha, A_ptr + 8 * ka * M, M, B.data_ptr() + 8 * (c0 * K + ka), K,
-                                          b_eff, Cm.data_ptr() + 8 * c0 * M, M, sptr, src, dst, nbytes)
-                    if i == last_i and si == len(subs) - 1:
-                        if X is not None:
-                            stream.wait_event(ev_x[j])
-                            dg.add_scaled(M, nc, beta, X.data_ptr() + 8 * c0 * M, M, Cm.data_ptr() + 8 * c0 * M, M, sptr)
-                        d2h_s.wait_event(stream.record_event())
-                        dg._check(dg.lib.dgemm_b200_d2h(hC.data_ptr() + 8 * c0 * M, M, Cm.data_ptr() + 8 * c0 * M, M, M, nc,
-                                                        d2h_s.cuda_stream))
-        if len(order) == 1:
-            stream.wait_event(ev_a)
-        dist.all_reduce(token)  # nobody still reads a slab when its owner overwrites it in the next pass
-        d2h_s.synchronize()
-        stream.synchronize()
-
-    def one():
+    def one(timeline_cap=0):
         if N == 1:
             dg.mydgemm_gpu_v20(M, Nn, K, alpha, hA.data_ptr(), M, hB.data_ptr(), K, beta, hC.data_ptr(), M)
-        elif fused and os.environ.get("BENCH_E2E_SIMPLE") != "1":
-            one_pipelined()
-        else:
-            one_simple()
+            return []
+        tl = dg.rank_pipeline(M, ncols, K, alpha, hA.data_ptr(), M, hB.data_ptr(), K, beta, hC.data_ptr(), M, rank, N, kb,
+                              xbufs, state["pass"], timeline_cap)
+        state["pass"] += 1
+        host_barrier()   # pass p+1 may not overwrite a slab a slower peer is still pulling in pass p
+        return tl
 
     one()  # warm-up (allocates the library's staging buffers)
     # spot check of the end-to-end path itself: one more pass, a few entries recomputed on the host
@@ -616,38 +813,70 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
     rng = np.random.default_rng(1234 + rank)
     idx = [(int(rng.integers(M)), int(rng.integers(ncols))) for _ in range(6)] + [(M - 1, ncols - 1), (0, 0)]
     before = [float(hC[j * M + i]) for i, j in idx]
-    one()
+    tl = one(30000 if N > 1 else 0)
     after = [float(hC[j * M + i]) for i, j in idx]
     check = spot_check(before, after, idx, M, K, n0, alpha, beta)
-    if N > 1:
-        dist.barrier()
+    host_barrier()
     torch.cuda.synchronize()
+    dg.reset_launch_count()
     t0 = time.perf_counter()
     for _ in range(reps):
         one()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    launches = dg.launch_count()
+    timeline = None
     if N > 1:
         t = torch.tensor([dt], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
-        b = torch.tensor([h2d, d2h], dtype=torch.int64, device=dev)
+        b = torch.tensor([h2d, d2h, launches], dtype=torch.int64, device=dev)
         dist.all_reduce(b, op=dist.ReduceOp.SUM)
-        h2d, d2h = int(b[0].item()), int(b[1].item())
+        h2d, d2h, launches = int(b[0].item()), int(b[1].item()), int(b[2].item())
         ck = torch.tensor([check], dtype=torch.float64, device=dev)
         dist.all_reduce(ck, op=dist.ReduceOp.MAX)
         check = float(ck.item())
+        # where one pass spends its time, per rank (CUDA events inside the library, ms since the pass began)
+        mine = summarise_timeline(tl)
+        allr = [None] * N
+        dist.all_gather_object(allr, mine, group=host_group)
+        timeline = {"per_rank": allr,
+                    "legend": "ms since the rank's pass began: first_call_start = start-up exposure (first A piece + B block "
+                              "over PCIe); last_call_end - first_call_start = compute incl. any starvation; "
+                              "last_d2h_end - last_call_end = exposed tail; h2d_all_done = when the last upload landed"}
+        full = os.environ.get("BENCH_TIMELINE_FILE")
+        if full:
+            allt = [None] * N
+            dist.all_gather_object(allt, tl, group=host_group)
+            if rank == 0:
+                with open(full, "w") as f:
+                    json.dump({"n_gpus": N, "size": M, "kinds": {"0": "h2d done for call", "1": "call start", "2": "call end",
+                                                                  "3": "d2h of sub-panel done"},
+                               "ranks": allt}, f)
     if not check <= 1.0:
         raise SystemExit(f"bench.py: end-to-end result is WRONG: max |err|/bound = {check}")
     return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "spot_check_max_err_over_bound": check,
             "spot_check": f"{len(idx)} entries per rank recomputed on the host in long double", "unit": UNIT, "h2d_bytes_per_step": h2d,
-            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps,
+            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps, "gpu_launches": launches,
+            "timeline": timeline,
             "api": "mydgemm_gpu_v20(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC) with pinned host pointers" if N == 1 else
-                   "per rank: dgemm_b200_h2d (own K-slab of A, B/C panels) + sharded step ("
-                   + ("dgemm_b200_device_fetch, fused NVLink pull; (slab, sub-panel) calls pipelined against H2D/D2H "
-                      "on three streams, own slab in sub-slabs, C deferred (dgemm_b200_add_scaled after the last slab)"
-                      if fused else "ncclBroadcast + dgemm_b200_device")
-                   + ") + dgemm_b200_d2h, pinned host buffers"}
+                   "dgemm_b200_rank_pipeline(M,ncols,K,alpha,A_slab,LDA,B_panel,LDB,beta,C_panel,LDC,rank,world,kb,xbuf,pass,...): "
+                   "one library call per rank and pass, pinned host pointers (csrc/dgemm_rank.cu; the schedule "
+                   "mydgemm_gpu_v21 runs per GPU)"}
+
+
+def summarise_timeline(tl):
+    if not tl:
+        return None
+    starts = [ms for k, _i, ms in tl if k == 1]
+    ends = [ms for k, _i, ms in tl if k == 2]
+    h2d = [ms for k, _i, ms in tl if k == 0]
+    d2h = [ms for k, _i, ms in tl if k == 3]
+    busy = sum(e - s for s, e in zip(starts, ends))
+    return {"first_call_start": round(min(starts), 3), "last_call_end": round(max(ends), 3),
+            "h2d_all_done": round(max(h2d), 3) if h2d else None, "last_d2h_end": round(max(d2h), 3) if d2h else None,
+            "calls": len(starts), "sum_call_ms": round(busy, 3),
+            "gaps_between_calls_ms": round(max(ends) - min(starts) - busy, 3)}
 
 
 if __name__ == "__main__":

@@ -113,6 +113,38 @@ int dgemm_b200_device_fetch(int M, int N, int K, double alpha, const double *dA,
 int dgemm_b200_ipc_export(const void *dptr, void *handle64);
 int dgemm_b200_ipc_open(const void *handle64, void **dptr);
 int dgemm_b200_ipc_close(void *dptr);
+/* ---- one rank's share of a column-panel sharded DGEMM, host operands in and out (one process per GPU) ------------------
+ * The multi-GPU counterpart of the reference's parallel kernel (include/kernel19.h:678-755: one OpenMP thread per row
+ * band, partition_m_dim :636-656).  Rank r of `world` owns the column panel J_r of B and C and the K-slab
+ * [kb[r], kb[r+1]) of A, all in HOST memory (pinned for full speed), and computes
+ *     C[:, J_r] = beta * C[:, J_r] + alpha * A * B[:, J_r]
+ * on the CURRENT device.  A is completed over NVLink: every rank uploads only its own slab into its exchange buffer
+ * (dgemm_b200_exchange_alloc; peers' buffers opened with dgemm_b200_ipc_open) and the DGEMM kernels of the other ranks pull
+ * it from there with their spare warps while they compute.  Ranks never wait for each other on the host and there is no
+ * collective: the only dependency is "piece q of rank g's slab has landed", a sequence word behind g's H2D copies.
+ *   A_slab    M x (kb[r+1]-kb[r]), leading dimension LDA          B_panel  K x ncols, LDB          C_panel  M x ncols, LDC
+ *   kb        world + 1 ascending K boundaries, kb[0] = 0, kb[world] = K, the same on every rank; every rank needs a
+ *             non-empty slab (multiples of 16 keep the pulls 16-byte aligned)
+ *   xbuf      world exchange buffers for this (M, K): xbuf[rank] the rank's own, xbuf[g] rank g's as mapped here
+ *   pass      the same number on every rank, increased by one for every pass on these exchange buffers; the caller keeps
+ *             pass p+1 from starting on any rank before every rank has returned from pass p (one host barrier)
+ *   timeline  optional: receives (kind, index, milliseconds since the pass began) triples, kind 0 = H2D for call `index`
+ *             complete, 1 / 2 = call `index` started / finished, 3 = D2H of column sub-panel `index` complete
+ * Same semantics as mydgemm_gpu_v20 on the panel (alpha == 0 or K == 0 -> C = beta*C; beta == 0 -> C not read). */
+int dgemm_b200_rank_pipeline(int M, int ncols, int K, double alpha, const double *A_slab, int LDA,
+                             const double *B_panel, int LDB, double beta, double *C_panel, int LDC, int rank,
+                             int world, const int *kb, void *const *xbuf, unsigned int pass, double *timeline,
+                             int timeline_cap, int *timeline_n);
+size_t dgemm_b200_exchange_bytes(int M, int K);   /* size of an exchange buffer: A (ld = M rounded up to even) + sequence words */
+void *dgemm_b200_exchange_alloc(int M, int K);    /* on the current device, sequence words zeroed; free with dgemm_b200_free */
+/* the schedule dgemm_b200_rank_pipeline uses (no device needed): n_calls x 12 ints {k0, kc, c0, nc, first, last, pull owner
+ * (-1: none), pull k0, pull kc, owner pieces needed, H2D copy awaited, C_in copy awaited (-1: none)} and n_copies x 6 ints
+ * {kind 0 = own A piece / 1 = B block / 2 = C_in, k0, kc, c0, nc, piece}; p1 > 0 forces the number of slab-major slabs */
+int dgemm_b200_rank_plan(int M, int ncols, int K, int world, int rank, const int *kb, int need_c_in, int p1, int *calls,
+                         int cap_calls, int *n_calls, int *copies, int cap_copies, int *n_copies, int *p1_out);
+/* re-read the DGEMM_B200_* environment switches (they are read once, at the first call) */
+int dgemm_b200_reload_env(void);
+
 /* plan the heuristic would use: writes variant, split-K factor, CTA count and the number of output tiles handled
  * by the stream-K tail (any out pointer may be NULL); returns status */
 int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const double *dB, long long ldb,

@@ -35,7 +35,8 @@ EXPORTS = [
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
     "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_host_plan",
-    "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled",
+    "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled", "dgemm_b200_rank_pipeline",
+    "dgemm_b200_exchange_bytes", "dgemm_b200_exchange_alloc", "dgemm_b200_rank_plan", "dgemm_b200_reload_env",
 ]
 
 
@@ -80,6 +81,15 @@ lib.dgemm_b200_add_scaled.argtypes = [C.c_int, C.c_int, C.c_double, _vp, _ll, _v
 _ip = C.POINTER(C.c_int)
 lib.dgemm_b200_host_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _ip, _ip, _ip, _ip, _ip, _ip,
                                      C.c_int, C.POINTER(C.c_double), _ip]
+lib.dgemm_b200_rank_pipeline.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, _vp, C.c_int, _vp, C.c_int, C.c_double, _vp,
+                                         C.c_int, C.c_int, C.c_int, _ip, C.POINTER(_vp), C.c_uint, C.POINTER(C.c_double),
+                                         C.c_int, _ip]
+lib.dgemm_b200_exchange_bytes.argtypes = [C.c_int, C.c_int]
+lib.dgemm_b200_exchange_bytes.restype = C.c_size_t
+lib.dgemm_b200_exchange_alloc.argtypes = [C.c_int, C.c_int]
+lib.dgemm_b200_exchange_alloc.restype = _vp
+lib.dgemm_b200_rank_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _ip, C.c_int, C.c_int, _ip, C.c_int, _ip,
+                                     _ip, C.c_int, _ip, _ip]
 lib.dgemm_b200_malloc.argtypes = [C.c_size_t]
 lib.dgemm_b200_malloc.restype = _vp
 lib.dgemm_b200_free.argtypes = [_vp]
@@ -149,6 +159,52 @@ def host_plan(M, N, K, alpha=1.0, beta=1.0, cap=4096):
 
 def device_count():
     return lib.dgemm_b200_device_count()
+
+
+def reload_env():
+    """The DGEMM_B200_* switches are read once; call this after changing one in os.environ."""
+    lib.dgemm_b200_reload_env()
+
+
+# ---- multi-GPU: one rank's pass (one process per GPU) ------------------------------------------------------------
+RANK_CALL_FIELDS = ("k0", "kc", "c0", "nc", "first", "last", "f_owner", "f_k0", "f_kc", "f_need_piece", "wait_copy",
+                    "wait_x_copy")
+RANK_COPY_FIELDS = ("kind", "k0", "kc", "c0", "nc", "piece")
+
+
+def rank_plan(M, ncols, K, world, rank, kb, need_c_in=True, p1=0, cap=1 << 16):
+    """Schedule of dgemm_b200_rank_pipeline as ({p1, calls: [dict], copies: [dict]}); pure host logic, no GPU needed."""
+    kbv = (C.c_int * (world + 1))(*kb)
+    calls, copies = (C.c_int * cap)(), (C.c_int * cap)()
+    nc, ncp, p1o = C.c_int(), C.c_int(), C.c_int()
+    _check(lib.dgemm_b200_rank_plan(M, ncols, K, world, rank, kbv, int(need_c_in), p1, calls, cap, C.byref(nc), copies, cap,
+                                    C.byref(ncp), C.byref(p1o)))
+    return {"p1": p1o.value,
+            "calls": [dict(zip(RANK_CALL_FIELDS, calls[12 * i: 12 * i + 12])) for i in range(nc.value)],
+            "copies": [dict(zip(RANK_COPY_FIELDS, copies[6 * i: 6 * i + 6])) for i in range(ncp.value)]}
+
+
+def exchange_alloc(M, K):
+    p = lib.dgemm_b200_exchange_alloc(M, K)
+    if not p:
+        _check()
+        raise DgemmError(ERR_OOM, "dgemm_b200_exchange_alloc failed")
+    return p
+
+
+def rank_pipeline(M, ncols, K, alpha, A_slab, LDA, B_panel, LDB, beta, C_panel, LDC, rank, world, kb, xbuf, pass_no,
+                  timeline_cap=0):
+    """One rank's pass of the column-panel sharded DGEMM from host operands (numpy arrays or raw host addresses).
+    Returns the timeline as a list of (kind, index, ms) when timeline_cap > 0."""
+    kbv = (C.c_int * (world + 1))(*kb)
+    xb = (_vp * world)(*[int(x) for x in xbuf])
+    tl = (C.c_double * max(timeline_cap, 1))()
+    n = C.c_int()
+    st = lib.dgemm_b200_rank_pipeline(M, ncols, K, float(alpha), _host_ptr(A_slab), LDA, _host_ptr(B_panel), LDB, float(beta),
+                                      _host_ptr(C_panel), LDC, rank, world, kbv, xb, pass_no,
+                                      tl if timeline_cap else None, timeline_cap, C.byref(n))
+    _check(st)
+    return [(int(tl[i]), int(tl[i + 1]), tl[i + 2]) for i in range(0, n.value, 3)]
 
 
 def _host_ptr(a):

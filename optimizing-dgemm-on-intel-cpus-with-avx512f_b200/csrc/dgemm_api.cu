@@ -18,8 +18,11 @@
 namespace {
 
 std::recursive_mutex g_mu;
-int g_status = DGEMM_B200_OK;
-char g_errmsg[512] = "";
+// Status and message are per host thread: mydgemm_gpu_v21 drives one worker thread per GPU through run_device, and a
+// worker's ok() must not erase another worker's failure before the parent has folded them (the parent re-raises the
+// first failure on its own thread, which is the one the caller reads with dgemm_b200_last_status()).
+thread_local int g_status = DGEMM_B200_OK;
+thread_local char g_errmsg[512] = "";
 
 int fail(int status, const char* fmt, ...) {
   g_status = status;
@@ -44,6 +47,72 @@ int ok() {
                   #expr, cudaGetErrorString(e_));                                                      \
   } while (0)
 
+// ---- environment switches ------------------------------------------------------------------------------------
+// Read ONCE (first call) and again only on dgemm_b200_reload_env(): the dispatch path of a 50 us call must not walk
+// the environment a dozen times.  Tests and probes that flip a switch in-process call dgemm_b200_reload_env().
+struct Env {
+  int device = 0;                       // DGEMM_B200_DEVICE
+  int max_gpus = 0;                     // DGEMM_B200_MAX_GPUS (0 = all)
+  int odd_ld = 0;                       // DGEMM_B200_ODD_LD / DGEMM_B200_NO_REALIGN: ODD_SPLIT / ODD_REALIGN / ODD_CPASYNC
+  bool no_small_tile = false;           // DGEMM_B200_NO_SMALL_TILE
+  long long small_max_tiles = 64;       // DGEMM_B200_SMALL_TILE_MAX_TILES
+  double small_max_flops = 4e9;         // DGEMM_B200_SMALL_TILE_MAX_FLOPS
+  bool no_lockstep = false;             // DGEMM_B200_NO_LOCKSTEP
+  int sync_kt = 64;                     // DGEMM_B200_SYNC_KT
+  int group_m = 16;                     // DGEMM_B200_GROUP_M
+  double realign_min_flops = 1e8;       // DGEMM_B200_REALIGN_MIN_FLOPS
+  bool realign_min_set = false;
+  double split_max_flops2 = 4e11;       // DGEMM_B200_SPLIT_MAX_FLOPS2
+  double tiny_bytes = 1.5e6;            // DGEMM_B200_TINY_BYTES
+  double stage_min_bytes = (double)(16 << 20);  // DGEMM_B200_STAGE_MIN_BYTES
+  bool no_staging = false;              // DGEMM_B200_NO_STAGING
+  int sk_min_iters = 4, sk_aligned_min_iters = 2, sk_aligned_min_ranges = 3;  // DGEMM_B200_SK_*
+  bool sk_ragged = false;
+  bool no_wait_kernels = false;         // DGEMM_B200_NO_WAIT: never launch a configuration whose CTAs wait on each other
+  bool no_tmap_cache = false;           // DGEMM_B200_NO_TMAP_CACHE
+  bool no_pdl = false;                  // DGEMM_B200_NO_PDL
+  double flag_timeout_ms = 20000.0;     // DGEMM_B200_FLAG_TIMEOUT_MS: bound of the multi-GPU layer's wait for a peer's upload
+  double hbm_budget = 0.0;              // DGEMM_B200_HBM_BUDGET (bytes; 0 = 90 % of the free HBM): out-of-core threshold
+  void load() {
+    *this = Env();
+    auto geti = [](const char* n, int d) { const char* e = getenv(n); return e ? atoi(e) : d; };
+    auto getd = [](const char* n, double d) { const char* e = getenv(n); return e ? atof(e) : d; };
+    auto has = [](const char* n) { return getenv(n) != nullptr; };
+    device = geti("DGEMM_B200_DEVICE", 0);
+    max_gpus = std::max(0, geti("DGEMM_B200_MAX_GPUS", 0));
+    const char* o = getenv("DGEMM_B200_ODD_LD");
+    if (has("DGEMM_B200_NO_REALIGN") || (o && !strcmp(o, "cpasync"))) odd_ld = 2;
+    else odd_ld = (o && !strcmp(o, "realign")) ? 1 : 0;
+    no_small_tile = has("DGEMM_B200_NO_SMALL_TILE");
+    if (const char* e = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) small_max_tiles = atoll(e);
+    small_max_flops = getd("DGEMM_B200_SMALL_TILE_MAX_FLOPS", small_max_flops);
+    no_lockstep = has("DGEMM_B200_NO_LOCKSTEP");
+    sync_kt = std::max(1, geti("DGEMM_B200_SYNC_KT", 64));
+    group_m = std::max(1, geti("DGEMM_B200_GROUP_M", 16));
+    realign_min_set = has("DGEMM_B200_REALIGN_MIN_FLOPS");
+    realign_min_flops = getd("DGEMM_B200_REALIGN_MIN_FLOPS", realign_min_flops);
+    split_max_flops2 = getd("DGEMM_B200_SPLIT_MAX_FLOPS2", split_max_flops2);
+    tiny_bytes = getd("DGEMM_B200_TINY_BYTES", tiny_bytes);
+    stage_min_bytes = getd("DGEMM_B200_STAGE_MIN_BYTES", stage_min_bytes);
+    no_staging = has("DGEMM_B200_NO_STAGING");
+    sk_min_iters = geti("DGEMM_B200_SK_MIN_ITERS", 4);
+    sk_aligned_min_iters = std::max(1, geti("DGEMM_B200_SK_ALIGNED_MIN_ITERS", 2));
+    sk_aligned_min_ranges = geti("DGEMM_B200_SK_ALIGNED_MIN_RANGES", 3);
+    sk_ragged = has("DGEMM_B200_SK_RAGGED");
+    no_wait_kernels = has("DGEMM_B200_NO_WAIT");
+    no_tmap_cache = has("DGEMM_B200_NO_TMAP_CACHE");
+    no_pdl = has("DGEMM_B200_NO_PDL");
+    hbm_budget = getd("DGEMM_B200_HBM_BUDGET", 0.0);
+    flag_timeout_ms = std::max(1.0, getd("DGEMM_B200_FLAG_TIMEOUT_MS", flag_timeout_ms));
+  }
+};
+Env g_env;
+std::once_flag g_env_once;
+const Env& env() {
+  std::call_once(g_env_once, [] { g_env.load(); });
+  return g_env;
+}
+
 // ---- per-device context ----------------------------------------------------------------------------------
 struct Buf {
   double* p = nullptr;
@@ -60,6 +129,8 @@ struct DeviceCtx {
   unsigned int sk_epoch = 0;
   cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
   bool ws_used = false;
+  cudaStream_t ws_stream = nullptr;  // ... and the stream it ran on (the same stream needs no event wait)
+  unsigned int* fetch_fail = nullptr;  // set by a fused fetch whose source never arrived (Params::fetch_fail)
   Buf a, b, c;                // staging for the host-pointer entries
   Buf x;                      // C_in of the deferred-C panels of the host pipeline
   Buf ra, rb;                 // realigned copies of TMA-ineligible device operands (see run_device)
@@ -115,6 +186,8 @@ int ensure_ctx(int dev, DeviceCtx** out) {
     CU_TRY(cudaMalloc(&c.sk_flags, 1024 * sizeof(unsigned int)));
     CU_TRY(cudaMemset(c.sk_flags, 0, 1024 * sizeof(unsigned int)));
     CU_TRY(cudaMalloc(&c.sync_ctr, SYNC_POINTS * sizeof(unsigned int)));
+    CU_TRY(cudaMalloc(&c.fetch_fail, 256));
+    CU_TRY(cudaMemset(c.fetch_fail, 0, 256));
     c.ready = true;
     cudaSetDevice(prev);
   }
@@ -172,9 +245,8 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
 // plus one full wave ("two-tile" stream-K) is cut into equal (tile, k-tile) ranges, one per CTA, so every SM gets
 // the same number of k-tiles.  When there are fewer tiles than SMs the whole problem is stream-K (this is what
 // split-K was for: M=N=512, K=16384 has 16 tiles for 148 SMs).
-static int SK_MIN_ITERS = getenv("DGEMM_B200_SK_MIN_ITERS") ? atoi(getenv("DGEMM_B200_SK_MIN_ITERS")) : 4;
-static int SK_ALIGNED_MIN_ITERS = getenv("DGEMM_B200_SK_ALIGNED_MIN_ITERS") ? std::max(1, atoi(getenv("DGEMM_B200_SK_ALIGNED_MIN_ITERS"))) : 2;
 void plan_stream_k(dg::Params& P, int num_sms) {
+  const int SK_MIN_ITERS = env().sk_min_iters, SK_ALIGNED_MIN_ITERS = env().sk_aligned_min_iters;
   // the parallel fix-up hands out a tile's fragments (32 per thread on the 128 x 128 tile, 8 on the 64 x 64 one)
   const int max_ranges = P.tile_small ? 8 : 64;
   const int tiles = P.tiles_m * P.tiles_n;
@@ -192,8 +264,7 @@ void plan_stream_k(dg::Params& P, int num_sms) {
     // boundaries, every CTA holds one segment and stores one partial, and ranges may be as short as 2 k-tiles
     // (measured: 256^3 25.2 -> 19.6 us, 384^3 27.3 -> 21.3 us; ragged ranges at 512^3: 31.8 us vs 25.4 aligned)
     const int r_cap = num_sms / tiles;
-    static const int kAlignedMinRanges = getenv("DGEMM_B200_SK_ALIGNED_MIN_RANGES") ? atoi(getenv("DGEMM_B200_SK_ALIGNED_MIN_RANGES")) : 3;
-    if (r_cap >= kAlignedMinRanges && !getenv("DGEMM_B200_SK_RAGGED")) {
+    if (r_cap >= env().sk_aligned_min_ranges && !env().sk_ragged) {
       // at most 64 ranges per tile (the parallel fix-up hands out the tile's 64 fragments; 128x128x4096: 64 ranges 4.25,
       // 128 ranges 3.8 TFLOP/s), and no more ranges than it takes to reach the shortest longest range (512^3: 9 ranges
       // of 3-4 k-tiles are slower than 8 ranges of 4: 10.2 vs 10.7 TFLOP/s)
@@ -218,11 +289,9 @@ void plan_stream_k(dg::Params& P, int num_sms) {
 // 1536^3 226.6 / 218.4 (the small tile's main loop loads 6 fragments per 8 DMMAs instead of 12 per 32), 512x512x4096
 // 77.8 / 80.2, 512x512x16384 264.1 / 259.5.
 bool want_small_tile(int M, int N, int K, bool tma_kernel, bool has_fetch) {
-  if (!tma_kernel || has_fetch || getenv("DGEMM_B200_NO_SMALL_TILE")) return false;
+  if (!tma_kernel || has_fetch || env().no_small_tile) return false;
   const long long big_tiles = (long long)((M + dg::BM - 1) / dg::BM) * ((N + dg::BN - 1) / dg::BN);
-  const long long max_tiles = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES") ? atoll(getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) : 64;
-  const double max_flops = getenv("DGEMM_B200_SMALL_TILE_MAX_FLOPS") ? atof(getenv("DGEMM_B200_SMALL_TILE_MAX_FLOPS")) : 4e9;
-  return big_tiles <= max_tiles && 2.0 * M * (double)N * K <= max_flops;
+  return big_tiles <= env().small_max_tiles && 2.0 * M * (double)N * K <= env().small_max_flops;
 }
 
 int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
@@ -242,8 +311,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   P.sync_ctr = nullptr; P.sync_waves = 0; P.sync_kt = 0;
   P.timeline = g_timeline;
   // rasterisation band: about sqrt(#SMs) tile-rows so a wave of CTAs covers a near-square block of C
-  static const int kGroupM = getenv("DGEMM_B200_GROUP_M") ? std::max(1, atoi(getenv("DGEMM_B200_GROUP_M"))) : 16;
-  P.group_m = std::min(P.tiles_m, kGroupM);
+  P.group_m = std::min(P.tiles_m, env().group_m);
   P.c_vec2 = ((uintptr_t)dC % 16 == 0) && (ldc % 2 == 0);
   P.workspace = nullptr;
   if (splits <= 0 && variant == dg::VARIANT_TMA) {  // auto on the persistent kernel: stream-K, never split-K
@@ -272,17 +340,15 @@ int check_args(int M, int N, int K, const void* A, long long lda, const void* B,
 }
 
 enum { ODD_SPLIT = 0, ODD_REALIGN = 1, ODD_CPASYNC = 2 };
-int odd_ld_mode() {   // DGEMM_B200_ODD_LD, read per call (tests and probes toggle it); see run_device
-  const char* e = getenv("DGEMM_B200_ODD_LD");
-  if (getenv("DGEMM_B200_NO_REALIGN") != nullptr || (e && !strcmp(e, "cpasync"))) return ODD_CPASYNC;
-  return (e && !strcmp(e, "realign")) ? ODD_REALIGN : ODD_SPLIT;
-}
+int odd_ld_mode() { return env().odd_ld; }   // DGEMM_B200_ODD_LD (tests and probes toggle it + reload_env); see run_device
 
 // the device-side DGEMM on context c (current device must be c.dev)
 struct Fetch {
   const void* src = nullptr;
   void* dst = nullptr;
   size_t bytes = 0;
+  const unsigned int* flag = nullptr;  // owner's "landed" sequence word (peer memory); nullptr: the source is complete
+  unsigned int need = 0;               // value it must have reached (signed distance)
 };
 
 int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
@@ -291,7 +357,9 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (fetch.bytes && (((uintptr_t)fetch.src | (uintptr_t)fetch.dst | fetch.bytes) & 15))
     return fail(DGEMM_B200_ERR_BAD_ARG, "fused fetch needs 16-byte aligned src/dst and a multiple of 16 bytes");
   if (M == 0 || N == 0 || alpha == 0.0 || K == 0) {
-    // no GEMM kernel to fuse with: the copy engine does the fetch
+    // no GEMM kernel to fuse with: the copy engine does the fetch (a flagged source needs the fetch warps' wait, and the
+    // multi-GPU layer never attaches one to a degenerate call)
+    if (fetch.bytes && fetch.flag) return fail(DGEMM_B200_ERR_BAD_ARG, "a flagged fused fetch needs M, N, K > 0 and alpha != 0");
     if (fetch.bytes) CU_TRY(cudaMemcpyAsync(fetch.dst, fetch.src, fetch.bytes, cudaMemcpyDefault, stream));
     if (M == 0 || N == 0) return ok();
     CU_TRY(dg::launch_scale_c(dC, M, N, ldc, beta, c.num_sms, stream));  // C = beta*C only (kernel18.h:644-645)
@@ -315,8 +383,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   const bool split_ok = !tma_ok && dg::tma_split_ok(P);
   const bool can_split = split_ok && !odd_cpasync && !odd_realign && fetch.bytes == 0;  // (the fused fetch needs warps 10-11)
   const double flops = 2.0 * M * (double)N * K;
-  static const double kRealignMinFlops = getenv("DGEMM_B200_REALIGN_MIN_FLOPS") ? atof(getenv("DGEMM_B200_REALIGN_MIN_FLOPS")) : 1e8;
-  const double kSplitMaxFlops2 = getenv("DGEMM_B200_SPLIT_MAX_FLOPS2") ? atof(getenv("DGEMM_B200_SPLIT_MAX_FLOPS2")) : 4e11;  // per call
+  const double kRealignMinFlops = env().realign_min_flops, kSplitMaxFlops2 = env().split_max_flops2;
   const bool prefer_realign = !can_split || (dg::tma_mis_halves(P) >= 2 && flops >= kSplitMaxFlops2);
   if (variant == dg::VARIANT_AUTO && !tma_ok && !odd_cpasync && prefer_realign && flops >= kRealignMinFlops) {
     // copy the offending operand(s) once, device to device (realign_kernel, 16 bytes per element against 2*N or 2*M
@@ -359,8 +426,8 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
   // there are at least two full waves; every CTA must be resident, i.e. the grid is one CTA per SM
-  const bool kNoSync = getenv("DGEMM_B200_NO_LOCKSTEP") != nullptr;   // read per call: tests toggle it
-  const int kSyncKt = getenv("DGEMM_B200_SYNC_KT") ? std::max(1, atoi(getenv("DGEMM_B200_SYNC_KT"))) : 64;
+  const bool kNoSync = env().no_lockstep;
+  const int kSyncKt = env().sync_kt;
   bool lockstep = false;
   if (variant == dg::VARIANT_TMA && P.splits == 1 && !kNoSync) {
     const int tiles = P.tiles_m * P.tiles_n;
@@ -374,8 +441,25 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
       lockstep = true;
     }
   }
+  // Co-residency: the k-lockstep and the parallel stream-K fix-up make CTAs wait for OTHER CTAs of the grid, which is only
+  // correct when the whole grid is resident at once.  They are launched cooperatively (the runtime guarantees it or fails
+  // the launch), and never planned for a grid larger than the device can hold; otherwise, and with DGEMM_B200_NO_WAIT=1,
+  // the schedule without such waits runs: no lockstep, serial fix-up (an owner only waits for lower-numbered CTAs, which
+  // were dispatched before it and wait for nobody).
+  auto drop_waits = [&]() {
+    lockstep = false;
+    P.sync_ctr = nullptr; P.sync_waves = 0; P.sync_kt = 0;
+    P.sk_parallel = 0;
+  };
+  if (variant == dg::VARIANT_TMA && (lockstep || P.sk_parallel)) {
+    const int tiles = P.tiles_m * P.tiles_n;
+    const int grid = P.sk_tiles > 0 ? P.sk_grid : std::min(tiles, c.num_sms);
+    if (env().no_wait_kernels || grid > dg::tma_coresident_capacity(P.tile_small != 0, c.num_sms)) drop_waits();
+  }
   const bool shares_ctx = uses_ws || lockstep;  // workspace / flags / counters: one launch at a time
-  if (shares_ctx && c.ws_used) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));  // previous user (maybe another stream)
+  // previous user on another stream (the same stream is ordered anyway, and an event wait between two kernels would
+  // keep the second one from launching programmatically behind the first)
+  if (shares_ctx && c.ws_used && c.ws_stream != stream) CU_TRY(cudaStreamWaitEvent(stream, c.ws_free, 0));
   if (uses_ws) {
     const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits
                                       : (size_t)P.sk_grid * (P.sk_parallel ? 2 : 1);
@@ -395,10 +479,19 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
     CU_TRY(cudaMemsetAsync(c.sync_ctr, 0, points * sizeof(unsigned int), stream));
   }
   P.fetch_src = fetch.src; P.fetch_dst = fetch.dst; P.fetch_bytes = fetch.bytes;
-  CU_TRY(dg::launch_gemm(P, variant, c.num_sms, stream));
+  const bool pdl = !env().no_pdl;
+  cudaError_t le = dg::launch_gemm(P, variant, c.num_sms, stream, lockstep || P.sk_parallel, pdl);
+  if (le == cudaErrorCooperativeLaunchTooLarge || (le == cudaErrorNotSupported && (lockstep || P.sk_parallel))) {
+    // fewer SMs are usable than the device reports (MPS share, green context, ...): run the schedule without waits
+    drop_waits();
+    le = dg::launch_gemm(P, variant, c.num_sms, stream, false, pdl);
+  }
+  CU_TRY(le);
   if (shares_ctx) {
+    // (an event record between two kernels of one stream does not break their programmatic pairing; the WAIT does)
     CU_TRY(cudaEventRecord(c.ws_free, stream));
     c.ws_used = true;
+    c.ws_stream = stream;
   }
   if (realigned) {
     CU_TRY(cudaEventRecord(c.r_free, stream));
@@ -491,8 +584,7 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   // Tiny calls (the low end of the reference harness, test.c:12-14: 100^3 moves 240 KB and computes for a few
   // microseconds): one stream, four copies, one kernel, one synchronisation -- no planner, no events, no second stream.
   // (harness, malloc'ed operands: 100^3 78 us -> see profiles/r01_harness_k20_v3.txt; the reference's kernel18: 60 us)
-  static const double kTinyBytes = getenv("DGEMM_B200_TINY_BYTES") ? atof(getenv("DGEMM_B200_TINY_BYTES")) : 1.5e6;
-  if (moved <= kTinyBytes) {
+  if (moved <= env().tiny_bytes) {
     cudaStream_t s = c.s_compute;
     // contiguous matrices (the harness passes LD = rows, utils.c:159-165) go as ONE 1-D copy: the driver's 2-D path
     // costs more per call, and at this size the call is nothing but API latency
@@ -513,8 +605,7 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   }
   // (staging pays from about 16 MB: 600^3 = 8.6 MB took 1270 us staged against 490 us for 500^3 through the driver's
   // own pageable path, 800^3 = 15 MB breaks even; profiles/r01_harness_k20_v2.txt)
-  static const double kStageMinBytes = getenv("DGEMM_B200_STAGE_MIN_BYTES") ? atof(getenv("DGEMM_B200_STAGE_MIN_BYTES")) : (double)(16 << 20);
-  const bool stage = moved >= kStageMinBytes && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
+  const bool stage = moved >= env().stage_min_bytes && !env().no_staging && dg::staging_usable(dev);
   const bool pa = stage && need_ab && dg::host_pointer_is_pageable(A), pb = stage && need_ab && dg::host_pointer_is_pageable(B),
              pc = stage && dg::host_pointer_is_pageable(C);
   auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
@@ -528,17 +619,27 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   const std::vector<int>& kb = plan.kb;
   const int P = (int)nb.size() - 1, S = (int)kb.size() - 1;
   const std::vector<dg::HostPlanItem>& order = plan.order;
+  if (P < 1 || S < 1 || order.empty()) return fail(DGEMM_B200_ERR_BAD_ARG, "no host schedule for M=%d N=%d K=%d", M, N, K);
   std::vector<int> last_item(P, -1);                            // index in `order` of the last call of every panel
   for (size_t i = 0; i < order.size(); i++) last_item[order[i].p] = (int)i;
   // deferred C: panels [0, deferred) start with beta = 0; their C_in goes to a side buffer behind the last B block
   // and beta*C_in is added by an elementwise pass after their last call
   const int deferred = need_c_in ? plan.deferred_panels : 0;
   if (deferred > 0 && (st = grow(c.x, (size_t)ldcD * nb[deferred] * 8))) return st;
+  struct Events {   // every per-call event, destroyed on every way out
+    std::vector<cudaEvent_t> all;
+    cudaError_t make(cudaEvent_t* e) {
+      cudaError_t r = cudaEventCreateWithFlags(e, cudaEventDisableTiming);
+      if (r == cudaSuccess) all.push_back(*e);
+      return r;
+    }
+    ~Events() { for (cudaEvent_t e : all) cudaEventDestroy(e); }
+  } events;
   cudaEvent_t ev_x = nullptr;
-  if (deferred > 0) CU_TRY(cudaEventCreateWithFlags(&ev_x, cudaEventDisableTiming));
+  if (deferred > 0) CU_TRY(events.make(&ev_x));
   std::vector<cudaEvent_t> ev_in(order.size()), ev_done(P, nullptr);
-  for (auto& e : ev_in) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  for (auto& e : ev_done) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (auto& e : ev_in) CU_TRY(events.make(&e));
+  for (auto& e : ev_done) CU_TRY(events.make(&e));
   std::vector<char> a_sent(S, 0), first_done(P, 0);
   int result = DGEMM_B200_OK;
   auto body = [&]() -> int {
@@ -589,9 +690,17 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
     return DGEMM_B200_OK;
   };
   result = body();
-  if (result && pc) dg::staged_d2h_wait();  // the D2H team may still hold ev_done events
-  for (auto e : ev_in) cudaEventDestroy(e);
-  for (auto e : ev_done) cudaEventDestroy(e);
+  if (result) {
+    // nothing of this call may still be reading or writing the caller's A / B / C when the error is returned
+    const int saved = g_status;
+    char msg[sizeof(g_errmsg)];
+    memcpy(msg, g_errmsg, sizeof(msg));
+    if (pc) dg::staged_d2h_wait();  // the D2H team may still hold ev_done events
+    for (cudaStream_t q : {c.s_d2h, c.s_compute, c.s_h2d}) cudaStreamSynchronize(q);
+    cudaGetLastError();
+    g_status = saved;
+    memcpy(g_errmsg, msg, sizeof(msg));
+  }
   return result ? result : ok();
 }
 
@@ -622,8 +731,7 @@ int run_host_op(int dev, bool ta, bool tb, int M, int N, int K, double alpha, co
   const double moved = 8.0 * ((need_ab ? (double)M * K + (double)K * N : 0.0) + (double)M * N);
   // (staging pays from about 16 MB: 600^3 = 8.6 MB took 1270 us staged against 490 us for 500^3 through the driver's
   // own pageable path, 800^3 = 15 MB breaks even; profiles/r01_harness_k20_v2.txt)
-  static const double kStageMinBytes = getenv("DGEMM_B200_STAGE_MIN_BYTES") ? atof(getenv("DGEMM_B200_STAGE_MIN_BYTES")) : (double)(16 << 20);
-  const bool stage = moved >= kStageMinBytes && !getenv("DGEMM_B200_NO_STAGING") && dg::staging_usable(dev);
+  const bool stage = moved >= env().stage_min_bytes && !env().no_staging && dg::staging_usable(dev);
   auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols) {
     if (stage && dg::host_pointer_is_pageable(src)) return dg::staged_h2d(dst, ldd, src, lds, rows, cols, c.s_h2d, dev);
     return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
@@ -719,13 +827,95 @@ int dgemm_b200_internal_run_on(int dev, int M, int N, int K, double alpha, const
   return run_device(*c, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream, dg::VARIANT_AUTO, 0, f);
 }
 
+// device-side resources of a rank's pass (dgemm_rank.cu): the context's B / C / C_in staging buffers and its three streams
+int dgemm_b200_internal_rank_ctx(int dev, size_t b_bytes, size_t c_bytes, size_t x_bytes, double** b, double** c, double** x,
+                                 cudaStream_t* s_compute, cudaStream_t* s_h2d, cudaStream_t* s_d2h, int* num_sms,
+                                 unsigned int** fetch_fail) {
+  DeviceCtx* cp = nullptr;
+  int st = ensure_ctx(dev, &cp);
+  if (st) return st;
+  if (b_bytes && (st = grow(cp->b, b_bytes))) return st;
+  if (c_bytes && (st = grow(cp->c, c_bytes))) return st;
+  if (x_bytes && (st = grow(cp->x, x_bytes))) return st;
+  *b = cp->b.p; *c = cp->c.p; *x = cp->x.p;
+  *s_compute = cp->s_compute; *s_h2d = cp->s_h2d; *s_d2h = cp->s_d2h;
+  *num_sms = cp->num_sms;
+  *fetch_fail = cp->fetch_fail;
+  return DGEMM_B200_OK;
+}
+const char* dgemm_b200_internal_errmsg() { return g_errmsg; }
+double dgemm_b200_internal_flag_timeout_ms() { return env().flag_timeout_ms; }
+
 extern "C" {
+
+size_t dgemm_b200_exchange_bytes(int M, int K) { return dg::exchange_bytes(M, K); }
+
+void* dgemm_b200_exchange_alloc(int M, int K) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  if (M < 0 || K < 0) {
+    fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_exchange_alloc: M=%d K=%d", M, K);
+    return nullptr;
+  }
+  void* p = dgemm_b200_malloc(dg::exchange_bytes(M, K));
+  if (!p) return nullptr;
+  if (cudaMemset(static_cast<char*>(p) + dg::exchange_flag_offset(M, K), 0, 256) != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(p);
+    fail(DGEMM_B200_ERR_CUDA, "dgemm_b200_exchange_alloc: cudaMemset of the sequence words failed");
+    return nullptr;
+  }
+  ok();
+  return p;
+}
+
+int dgemm_b200_rank_pipeline(int M, int ncols, int K, double alpha, const double* A_slab, int LDA, const double* B_panel,
+                             int LDB, double beta, double* C_panel, int LDC, int rank, int world, const int* kb,
+                             void* const* xbuf, unsigned int pass, double* timeline, int timeline_cap, int* timeline_n) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  if (timeline_n) *timeline_n = 0;
+  if (probe_devices() <= 0)
+    return fail(DGEMM_B200_ERR_NO_DEVICE, "no usable sm_100 CUDA device (this library has no CPU fallback)");
+  if (ncols > 0 && M > 0 && !C_panel) return fail(DGEMM_B200_ERR_BAD_ARG, "C_panel is NULL");
+  if (ncols > 0 && M > 0 && K > 0 && alpha != 0.0 && !B_panel) return fail(DGEMM_B200_ERR_BAD_ARG, "B_panel is NULL");
+  int dev = 0;
+  CU_TRY(cudaGetDevice(&dev));
+  dg::RankArgs a;
+  a.M = M; a.ncols = ncols; a.K = K; a.alpha = alpha; a.beta = beta;
+  a.A_slab = A_slab; a.LDA = LDA; a.B = B_panel; a.LDB = LDB; a.C = C_panel; a.LDC = LDC;
+  a.rank = rank; a.world = world; a.kb = kb; a.xbuf = xbuf; a.pass = pass;
+  a.timeline = timeline; a.timeline_cap = timeline_cap; a.timeline_n = timeline_n;
+  return dg::rank_pipeline_exec(dev, a);
+}
+
+int dgemm_b200_rank_plan(int M, int ncols, int K, int world, int rank, const int* kb, int need_c_in, int p1, int* calls,
+                         int cap_calls, int* n_calls, int* copies, int cap_copies, int* n_copies, int* p1_out) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  if (!kb || world < 1) return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_rank_plan: kb / world");
+  const dg::RankPlan plan = dg::plan_rank_pipeline(M, ncols, K, world, rank, kb, need_c_in != 0, p1);
+  if (!plan.ok) return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_rank_plan: no schedule (empty own K-slab, or kb not ascending 0..K)");
+  if ((int)plan.calls.size() * 12 > cap_calls || (int)plan.copies.size() * 6 > cap_copies)
+    return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_rank_plan: %zu calls / %zu copies do not fit", plan.calls.size(),
+                plan.copies.size());
+  for (size_t i = 0; calls && i < plan.calls.size(); i++) {
+    const dg::RankCall& c = plan.calls[i];
+    const int v[12] = {c.k0, c.kc, c.c0, c.nc, c.first, c.last, c.f_owner, c.f_k0, c.f_kc, c.f_need_piece, c.wait_copy, c.wait_x_copy};
+    std::copy(v, v + 12, calls + 12 * i);
+  }
+  for (size_t i = 0; copies && i < plan.copies.size(); i++) {
+    const dg::RankCopy& c = plan.copies[i];
+    const int v[6] = {c.kind, c.k0, c.kc, c.c0, c.nc, c.piece};
+    std::copy(v, v + 6, copies + 6 * i);
+  }
+  if (n_calls) *n_calls = (int)plan.calls.size();
+  if (n_copies) *n_copies = (int)plan.copies.size();
+  if (p1_out) *p1_out = plan.p1;
+  return ok();
+}
 
 void mydgemm_gpu_v20(int M, int N, int K, double alpha, double* A, int LDA, double* B, int LDB, double beta, double* C,
                      int LDC) {
   std::lock_guard<std::recursive_mutex> lk(g_mu);
-  int dev = 0;
-  if (const char* e = getenv("DGEMM_B200_DEVICE")) dev = atoi(e);
+  const int dev = env().device;
   run_host_single(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
 }
 
@@ -740,9 +930,9 @@ void mydgemm_gpu_v21(int M, int N, int K, double alpha, double* A, int LDA, doub
   }
   int g = g_ndev;
   if (g_max_gpus > 0) g = std::min(g, g_max_gpus);
-  if (const char* e = getenv("DGEMM_B200_MAX_GPUS")) g = std::max(1, std::min(g, atoi(e)));
+  if (env().max_gpus > 0) g = std::max(1, std::min(g, env().max_gpus));
   if (g <= 1 || N < 2 * dg::BN) {
-    run_host_single(0, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
+    run_host_single(env().device, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
     return;
   }
   dgemm_b200_run_host_multi(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC, g);
@@ -753,8 +943,7 @@ void dgemm_b200_cblas_dgemm(int layout, int transa, int transb, int M, int N, in
   std::lock_guard<std::recursive_mutex> lk(g_mu);
   ColMajorCall q = {};
   if (to_col_major(layout, transa, transb, M, N, A, lda, B, ldb, &q)) return;
-  int dev = 0;
-  if (const char* e = getenv("DGEMM_B200_DEVICE")) dev = atoi(e);
+  const int dev = env().device;
   run_host_op(dev, q.ta, q.tb, q.M, q.N, K, alpha, q.A, (int)q.lda, q.B, (int)q.ldb, beta, C, ldc);
 }
 
@@ -807,6 +996,13 @@ int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int* pa
   return ok();
 }
 
+int dgemm_b200_reload_env(void) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  env();
+  g_env.load();
+  return DGEMM_B200_OK;
+}
+
 int dgemm_b200_last_status(void) { return g_status; }
 const char* dgemm_b200_last_error(void) { return g_errmsg; }
 
@@ -849,6 +1045,7 @@ int dgemm_b200_shutdown(void) {
     cudaEventDestroy(c.t_free);
     cudaFree(c.sk_flags);
     cudaFree(c.sync_ctr);
+    cudaFree(c.fetch_fail);
     c = DeviceCtx();
   }
   if (g_ndev > 0) cudaSetDevice(prev);
@@ -914,7 +1111,7 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
   const bool tma_ok = dg::tma_eligible(P);
   const bool split = !tma_ok && dg::tma_split_ok(P) && odd_ld_mode() == ODD_SPLIT;
   const bool realign = !tma_ok && !split && odd_ld_mode() != ODD_CPASYNC && 2.0 * M * (double)N * K >= 1e8 &&
-                       !getenv("DGEMM_B200_REALIGN_MIN_FLOPS");
+                       !env().realign_min_set;
   const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms,
               want_small_tile(M, N, std::max(K, 1), tma_ok || split || realign, false));

@@ -221,6 +221,23 @@ HostPlan plan_host_pipeline(int M, int N, int K, bool need_ab, bool need_c_in, i
         }
       }
     }
+  if (best.order.empty()) {
+    // No candidate fits the item budget (N or K in the millions with the other dimensions thin: even 8192-wide pieces
+    // give more than max_items panels x slabs).  A schedule that always fits: pieces widened until it does, uniform, no
+    // lead-in, panels x slabs in the same three-phase order.
+    int wn = 8192, wk = 8192;
+    auto pieces = [](int total, int w) { return (total + w - 1) / w; };
+    while ((long long)pieces(N, wn) * pieces(K, wk) > max_items) {
+      if (pieces(N, wn) >= pieces(K, wk)) wn *= 2; else wk *= 2;
+    }
+    const std::vector<int> nb = make_bounds(N, {}, wn, {}, Model::BN_), kb = make_bounds(K, {}, wk, {}, Model::BK_);
+    int deferred = 0;
+    best.order = make_order(M, nb, kb, need_c_in, need_cols, merge_k, defer_ok, &deferred);
+    best.predicted_ms = simulate(m, M, nb, kb, best.order, need_c_in, deferred);
+    best.nb = nb;
+    best.kb = kb;
+    best.deferred_panels = deferred;
+  }
   best.predicted_ms *= 1e3;
   {
     std::lock_guard<std::mutex> lk(g_cache_mu);

@@ -14,16 +14,21 @@
 #define DG_BN 64
 #include "dgemm_tma_kernel.cuh"
 #include "dgemm_host.h"
+#include "dgemm_launch.h"
+
+#include <atomic>
 
 namespace dg {
 
 static_assert(dg64::BM == SMALL_BM && dg64::BN == SMALL_BN, "dgemm_host.h must state the small tile's size");
 
-cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
-                             cudaStream_t stream) {
-  constexpr int STAGES = 8;   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
-  const int smem = STAGES * dg64::STAGE_BYTES + 2 * STAGES * 8 + 16 + 1024;
-  static bool attr_done[64] = {};  // function attributes are per device
+constexpr int SMALL_STAGES = 8;   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
+constexpr int SMALL_SMEM = SMALL_STAGES * dg64::STAGE_BYTES + 2 * SMALL_STAGES * 8 + 16 + 1024;
+
+static cudaError_t small_attrs() {
+  constexpr int STAGES = SMALL_STAGES;
+  const int smem = SMALL_SMEM;
+  static std::atomic<bool> attr_done[64];  // function attributes are per device
   int dev = 0;
   cudaError_t err = cudaGetDevice(&dev);
   if (err != cudaSuccess) return err;
@@ -36,24 +41,41 @@ cudaError_t launch_tma_small(const void* const maps[4], int split, const Params&
       return err;
     attr_done[dev & 63] = true;
   }
+  return cudaSuccess;
+}
+
+cudaError_t small_tile_occupancy(int* ctas_per_sm) {
+  cudaError_t err = small_attrs();
+  if (err != cudaSuccess) return err;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, dg64::dgemm_tma_ws_kernel<SMALL_STAGES>, dg64::TMA_THREADS,
+                                                       SMALL_SMEM);
+}
+
+cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
+                             cudaStream_t stream, bool cooperative, bool pdl) {
+  constexpr int STAGES = SMALL_STAGES;
+  cudaError_t err = small_attrs();
+  if (err != cudaSuccess) return err;
   const CUtensorMap &tmA = *reinterpret_cast<const CUtensorMap*>(maps[0]), &tmA1 = *reinterpret_cast<const CUtensorMap*>(maps[1]),
                     &tmB = *reinterpret_cast<const CUtensorMap*>(maps[2]), &tmB1 = *reinterpret_cast<const CUtensorMap*>(maps[3]);
-  const int threads = dg64::TMA_THREADS;
+  LaunchCfg cfg;
+  cfg.grid = grid; cfg.threads = dg64::TMA_THREADS; cfg.smem = SMALL_SMEM; cfg.stream = stream;
+  cfg.cooperative = cooperative; cfg.pdl = pdl;
   switch (split) {
     case SPLIT_NONE:
-      dg64::dgemm_tma_ws_kernel<STAGES><<<grid, threads, smem, stream>>>(tmA, tmB, P, dp_units);
+      err = launch_ex(dg64::dgemm_tma_ws_kernel<STAGES>, cfg, tmA, tmB, P, dp_units);
       break;
     case SPLIT_A:
-      dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A><<<grid, threads, smem, stream>>>(tmA, tmA1, tmB, tmB1, P, dp_units);
+      err = launch_ex(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A>, cfg, tmA, tmA1, tmB, tmB1, P, dp_units);
       break;
     case SPLIT_B:
-      dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_B><<<grid, threads, smem, stream>>>(tmA, tmA1, tmB, tmB1, P, dp_units);
+      err = launch_ex(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_B>, cfg, tmA, tmA1, tmB, tmB1, P, dp_units);
       break;
     default:
-      dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A | SPLIT_B><<<grid, threads, smem, stream>>>(tmA, tmA1, tmB, tmB1, P,
-                                                                                                  dp_units);
+      err = launch_ex(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A | SPLIT_B>, cfg, tmA, tmA1, tmB, tmB1, P, dp_units);
   }
-  return cudaGetLastError();
+  if (err != cudaSuccess) cudaGetLastError();
+  return err;
 }
 
 }  // namespace dg

@@ -29,11 +29,13 @@
 #include <cstring>
 #include <future>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
 int dgemm_b200_internal_fail(int status, const char* msg);
 int dgemm_b200_internal_ok();
+const char* dgemm_b200_internal_errmsg();
 int dgemm_b200_internal_run_on(int dev, int M, int N, int K, double alpha, const double* dA, long long lda,
                                const double* dB, long long ldb, double beta, double* dC, long long ldc,
                                cudaStream_t stream, const void* fetch_src, void* fetch_dst, size_t fetch_bytes);
@@ -69,8 +71,11 @@ struct NcclApi {
 
 struct DevState {
   cudaStream_t s_h2d = nullptr, s_comm = nullptr, s_compute = nullptr, s_d2h = nullptr;
-  double *a = nullptr, *b = nullptr, *c = nullptr, *x = nullptr;  // x: C_in of the deferred-C pipeline
-  size_t a_cap = 0, b_cap = 0, c_cap = 0, x_cap = 0;
+  double *a = nullptr, *b = nullptr, *c = nullptr;   // simple path: whole A, the B and C panels
+  size_t a_cap = 0, b_cap = 0, c_cap = 0;
+  void* xbuf = nullptr;                              // rank pipeline: exchange buffer (A + sequence words)
+  size_t x_cap_bytes = 0;
+  int x_M = 0, x_K = 0;
   cudaEvent_t ev_slab = nullptr, ev_bc = nullptr, ev_done = nullptr;
   std::vector<cudaEvent_t> ev_bcast;  // per slab
 };
@@ -78,6 +83,7 @@ struct DevState {
 struct MultiCtx {
   int g = 0;
   bool fused = false;  // peer access everywhere -> in-kernel NVLink fetch instead of NCCL broadcasts
+  bool want_fused = true;  // what DGEMM_B200_EXCHANGE asked for when the context was built
   NcclApi nccl;
   std::vector<ncclComm_t> comms;
   std::vector<DevState> dev;
@@ -104,13 +110,14 @@ struct MultiCtx {
 
 int ensure_multi(int g) {
   MultiCtx& m = g_multi;
-  if (m.g == g) return DGEMM_B200_OK;
-  if (m.g != 0) {
-    dgemm_b200_multi_shutdown();
-  }
   // peer access for every ordered pair -> fused exchange
   const char* mode = getenv("DGEMM_B200_EXCHANGE");
   bool want_fused = !(mode && strcmp(mode, "nccl") == 0);
+  if (m.g == g && m.want_fused == want_fused) return DGEMM_B200_OK;   // (a later change of DGEMM_B200_EXCHANGE rebuilds it)
+  if (m.g != 0) {
+    dgemm_b200_multi_shutdown();
+  }
+  m.want_fused = want_fused;
   if (want_fused) {
     for (int a = 0; a < g && want_fused; a++)
       for (int b = 0; b < g && want_fused; b++) {
@@ -179,7 +186,7 @@ void dgemm_b200_multi_shutdown() {
     if (s.a) cudaFree(s.a);
     if (s.b) cudaFree(s.b);
     if (s.c) cudaFree(s.c);
-    if (s.x) cudaFree(s.x);
+    if (s.xbuf) cudaFree(s.xbuf);
     cudaStreamDestroy(s.s_h2d); cudaStreamDestroy(s.s_comm); cudaStreamDestroy(s.s_compute); cudaStreamDestroy(s.s_d2h);
     cudaEventDestroy(s.ev_slab); cudaEventDestroy(s.ev_bc); cudaEventDestroy(s.ev_done);
     for (auto e : s.ev_bcast) cudaEventDestroy(e);
@@ -198,173 +205,53 @@ static void partition(int total, int parts, int align, std::vector<int>& begin) 
   for (int i = 0; i <= parts; i++) begin[i] = std::min(total, i * per);
 }
 
-// ---- fused mode, large problems: every GPU runs its own three-stream pipeline from its own host thread ----------
-// Same schedule as the one-process-per-GPU path (bench.py: one_pipelined): the own K-slab of A goes in as sub-slabs,
-// each followed by its B blocks; then the B blocks of the other slabs; C is DEFERRED — every column sub-panel starts
-// with beta = 0 and gets beta*C_in added after its last slab (launch_add_scaled), so the first call waits for a
-// quarter slab of A and one B block.  The call that multiplies slab i pulls slab i+1 from its owner's HBM with the
-// kernel's spare warps (the first pull rides on the LAST call of the own slab: the owner's upload must be complete).
-// Sub-panels go back to the host as soon as their last slab is done; the last ones are narrow.
-static int run_host_multi_pipelined(int M, int N, int K, double alpha, const double* A, int LDA, const double* B, int LDB,
-                                    double beta, double* C, int LDC, int G, const std::vector<int>& nb,
-                                    const std::vector<int>& kb) {
+// ---- fused mode: every GPU runs the rank pipeline (dgemm_rank.cu) from its own host thread ---------------------------------
+// The same executor and schedule as the one-process-per-GPU entry dgemm_b200_rank_pipeline: own K-slab uploaded in growing
+// pieces and published piece by piece, foreign slabs pulled over NVLink by the DGEMM kernel's spare warps, slab-major start,
+// panel-major finish with deferred C and tapered last sub-panels.  The threads never synchronise with each other on the
+// host; joining them is the barrier between two passes that the exchange buffers need.
+static int run_host_multi_ranked(int M, int N, int K, double alpha, const double* A, int LDA, const double* B, int LDB,
+                                 double beta, double* C, int LDC, int G, const std::vector<int>& nb,
+                                 const std::vector<int>& kb) {
   MultiCtx& m = g_multi;
-  const bool need_c_in = beta != 0.0;
-  const long long ldaD = (M + 1) & ~1ll, ldbD = (K + 1) & ~1ll, ldcD = (M + 1) & ~1ll;
-  int st;
+  const size_t xbytes = dg::exchange_bytes(M, K);
   for (int d = 0; d < G; d++) {
     MCU(cudaSetDevice(d));
     DevState& s = m.dev[d];
-    const int ncols = std::max(nb[d + 1] - nb[d], 1);
-    if ((st = grow_dev(&s.a, &s.a_cap, (size_t)ldaD * K * 8))) return st;
-    if ((st = grow_dev(&s.b, &s.b_cap, (size_t)ldbD * ncols * 8))) return st;
-    if ((st = grow_dev(&s.c, &s.c_cap, (size_t)ldcD * ncols * 8))) return st;
-    if (need_c_in && (st = grow_dev(&s.x, &s.x_cap, (size_t)ldcD * ncols * 8))) return st;
+    if (s.x_cap_bytes < xbytes || s.x_M != M || s.x_K != K) {   // (the flag block sits behind A: its offset depends on M, K)
+      if (s.xbuf) {
+        MCU(cudaDeviceSynchronize());
+        cudaFree(s.xbuf);
+        s.xbuf = nullptr;
+        s.x_cap_bytes = 0;
+      }
+      MCU(cudaMalloc(&s.xbuf, xbytes));
+      s.x_cap_bytes = xbytes; s.x_M = M; s.x_K = K;
+    }
+    MCU(cudaMemset(static_cast<char*>(s.xbuf) + dg::exchange_flag_offset(M, K), 0, 256));
   }
-  std::vector<std::promise<int>> slab_recorded(G);
-  std::vector<std::shared_future<int>> slab_fut;
-  for (auto& p : slab_recorded) slab_fut.push_back(p.get_future().share());
-  std::vector<int> status(G, 0);      // 0 ok, > 0 cudaError_t, < 0 library status (already reported by fail())
+  std::vector<void*> xbuf(G);
+  for (int d = 0; d < G; d++) xbuf[d] = m.dev[d].xbuf;
+  const unsigned int pass = 0;   // the sequence words were just zeroed: every call is pass 0 on fresh flags
+  std::vector<int> status(G, 0);
+  std::vector<std::string> message(G);
   std::vector<std::thread> threads;
   for (int d = 0; d < G; d++) {
     threads.emplace_back([&, d]() {
-      DevState& s = m.dev[d];
-      bool promised = false;
-      std::vector<cudaEvent_t> events;
-      auto work = [&]() -> int {
-#define TCU(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) return (int)e_; } while (0)
-        TCU(cudaSetDevice(d));
-        int num_sms = 148;
-        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, d);
-        auto new_event = [&](cudaEvent_t* e) -> cudaError_t {
-          cudaError_t r = cudaEventCreateWithFlags(e, cudaEventDisableTiming);
-          if (r == cudaSuccess) events.push_back(*e);
-          return r;
-        };
-        const int n0 = nb[d], ncols = nb[d + 1] - nb[d];
-        const int k0 = kb[d], kc_own = kb[d + 1] - kb[d];
-        // column sub-panels: four main pieces, two narrow last ones; own slab in up to four sub-slabs
-        std::vector<int> sp{0};
-        {
-          const int tail[2] = {384, 128};
-          const int tails = ncols >= 4096 ? tail[0] + tail[1] : 0;
-          const int head = ncols - tails, parts = head >= 4 * 256 ? 4 : 1;
-          const int per = ((head + parts - 1) / parts + dg::BN - 1) / dg::BN * dg::BN;
-          for (int i = 1; i <= parts; i++) if (std::min(head, i * per) > sp.back()) sp.push_back(std::min(head, i * per));
-          if (tails) { sp.push_back(sp.back() + tail[0]); sp.push_back(ncols); }
-        }
-        const int SP = (int)sp.size() - 1;
-        std::vector<int> qb{k0};
-        {
-          const int parts = kc_own >= 4 * 512 ? 4 : 1;
-          const int per = ((kc_own + parts - 1) / parts + dg::BK - 1) / dg::BK * dg::BK;
-          for (int i = 1; i <= parts; i++) if (std::min(kc_own, i * per) + k0 > qb.back()) qb.push_back(k0 + std::min(kc_own, i * per));
-        }
-        const int Q = (int)qb.size() - 1;
-        std::vector<int> order;  // non-empty slabs in ring order starting at the own one
-        for (int i = 0; i < G; i++)
-          if (kb[(d + i) % G + 1] - kb[(d + i) % G] > 0) order.push_back((d + i) % G);
-        // ---- H2D queue, in need-order
-        auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols) {
-          return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
-                                   cudaMemcpyHostToDevice, s.s_h2d);
-        };
-        std::vector<std::vector<cudaEvent_t>> ev_b0(Q, std::vector<cudaEvent_t>(SP));  // own slab: [sub-slab][sub-panel]
-        std::vector<std::vector<cudaEvent_t>> ev_b(order.size(), std::vector<cudaEvent_t>(SP));
-        std::vector<cudaEvent_t> ev_x(SP);
-        for (int q = 0; q < Q; q++) {
-          const int ka = qb[q], kq = qb[q + 1] - qb[q];
-          TCU(h2d(s.a + (size_t)ka * ldaD, ldaD, A + (size_t)ka * LDA, LDA, M, kq));
-          for (int j = 0; j < SP; j++) {
-            const int c0 = sp[j], nc = sp[j + 1] - sp[j];
-            TCU(h2d(s.b + (size_t)c0 * ldbD + ka, ldbD, B + (size_t)(n0 + c0) * LDB + ka, LDB, kq, nc));
-            TCU(new_event(&ev_b0[q][j]));
-            TCU(cudaEventRecord(ev_b0[q][j], s.s_h2d));
-          }
-        }
-        TCU(cudaEventRecord(s.ev_slab, s.s_h2d));  // the own slab is complete in this GPU's HBM: peers may pull it
-        slab_recorded[d].set_value(0);
-        promised = true;
-        for (size_t i = 1; i < order.size(); i++) {
-          const int g = order[i];
-          for (int j = 0; j < SP; j++) {
-            const int c0 = sp[j], nc = sp[j + 1] - sp[j];
-            TCU(h2d(s.b + (size_t)c0 * ldbD + kb[g], ldbD, B + (size_t)(n0 + c0) * LDB + kb[g], LDB, kb[g + 1] - kb[g], nc));
-            TCU(new_event(&ev_b[i][j]));
-            TCU(cudaEventRecord(ev_b[i][j], s.s_h2d));
-          }
-        }
-        if (need_c_in)
-          for (int j = 0; j < SP; j++) {
-            const int c0 = sp[j], nc = sp[j + 1] - sp[j];
-            TCU(h2d(s.x + (size_t)c0 * ldcD, ldcD, C + (size_t)(n0 + c0) * LDC, LDC, M, nc));
-            TCU(new_event(&ev_x[j]));
-            TCU(cudaEventRecord(ev_x[j], s.s_h2d));
-          }
-        // ---- compute + D2H
-        bool first_call = true;
-        for (size_t i = 0; i < order.size(); i++) {
-          const int g = order[i];
-          const int subs = (g == d && i == 0) ? Q : 1;
-          for (int q = 0; q < subs; q++) {
-            const int ka = (g == d && i == 0) ? qb[q] : kb[g];
-            const int kq = (g == d && i == 0) ? qb[q + 1] - qb[q] : kb[g + 1] - kb[g];
-            for (int j = 0; j < SP; j++) {
-              const int c0 = sp[j], nc = sp[j + 1] - sp[j];
-              TCU(cudaStreamWaitEvent(s.s_compute, (g == d && i == 0) ? ev_b0[q][j] : ev_b[i][j], 0));
-              const void* fsrc = nullptr;
-              void* fdst = nullptr;
-              size_t fbytes = 0;
-              if (i + 1 < order.size()) {
-                const bool first_pull = i == 0 && q == subs - 1 && j == SP - 1;
-                if (first_pull || (i > 0 && j == 0)) {
-                  const int nx = order[i + 1];
-                  if (slab_fut[nx].get() != 0) return (int)cudaErrorUnknown;     // the owner has queued its upload ...
-                  TCU(cudaStreamWaitEvent(s.s_compute, m.dev[nx].ev_slab, 0));    // ... and it will be complete
-                  fsrc = m.dev[nx].a + (size_t)kb[nx] * ldaD;
-                  fdst = s.a + (size_t)kb[nx] * ldaD;
-                  fbytes = (size_t)(kb[nx + 1] - kb[nx]) * ldaD * 8;
-                }
-              }
-              const double b_eff = first_call || (i == 0 && q == 0) ? (need_c_in ? 0.0 : beta) : 1.0;
-              const int rc = dgemm_b200_internal_run_on(d, M, nc, kq, alpha, s.a + (size_t)ka * ldaD, ldaD,
-                                                        s.b + (size_t)c0 * ldbD + ka, ldbD, b_eff, s.c + (size_t)c0 * ldcD, ldcD,
-                                                        s.s_compute, fsrc, fdst, fbytes);
-              if (rc) return -rc;
-              if (i + 1 == order.size() && q == subs - 1) {  // last slab of this sub-panel: add beta*C_in, send it back
-                if (need_c_in) {
-                  TCU(cudaStreamWaitEvent(s.s_compute, ev_x[j], 0));
-                  TCU(dg::launch_add_scaled(s.c + (size_t)c0 * ldcD, ldcD, s.x + (size_t)c0 * ldcD, ldcD, M, nc, beta, num_sms,
-                                            s.s_compute));
-                }
-                cudaEvent_t done;
-                TCU(new_event(&done));
-                TCU(cudaEventRecord(done, s.s_compute));
-                TCU(cudaStreamWaitEvent(s.s_d2h, done, 0));
-                TCU(cudaMemcpy2DAsync(C + (size_t)(n0 + c0) * LDC, (size_t)LDC * 8, s.c + (size_t)c0 * ldcD, ldcD * 8,
-                                      (size_t)M * 8, nc, cudaMemcpyDeviceToHost, s.s_d2h));
-              }
-            }
-            first_call = false;
-          }
-        }
-        for (cudaStream_t q : {s.s_d2h, s.s_compute, s.s_h2d}) TCU(cudaStreamSynchronize(q));
-        return 0;
-#undef TCU
-      };
-      status[d] = work();
-      if (!promised) slab_recorded[d].set_value(1);
-      cudaSetDevice(d);
-      if (status[d]) cudaDeviceSynchronize();
-      for (cudaEvent_t e : events) cudaEventDestroy(e);
+      dg::RankArgs a;
+      a.M = M; a.ncols = nb[d + 1] - nb[d]; a.K = K; a.alpha = alpha; a.beta = beta;
+      a.A_slab = A + (size_t)kb[d] * LDA; a.LDA = LDA;
+      a.B = B + (size_t)nb[d] * LDB; a.LDB = LDB;
+      a.C = C + (size_t)nb[d] * LDC; a.LDC = LDC;
+      a.rank = d; a.world = G; a.kb = kb.data(); a.xbuf = xbuf.data(); a.pass = pass;
+      status[d] = dg::rank_pipeline_exec(d, a);
+      if (status[d]) message[d] = dgemm_b200_internal_errmsg();   // status and message are per thread: hand them to the parent
     });
   }
   for (auto& t : threads) t.join();
   cudaSetDevice(0);
-  for (int d = 0; d < G; d++) {
-    if (status[d] > 0) return dgemm_b200_internal_fail(DGEMM_B200_ERR_CUDA, cudaGetErrorString((cudaError_t)status[d]));
-    if (status[d] < 0) return -status[d];  // already reported
-  }
+  for (int d = 0; d < G; d++)
+    if (status[d]) return dgemm_b200_internal_fail(status[d], message[d].c_str());
   return dgemm_b200_internal_ok();
 }
 
@@ -380,9 +267,10 @@ int dgemm_b200_run_host_multi(int M, int N, int K, double alpha, const double* A
   std::vector<int> nb, kb;
   partition(N, G, dg::BN, nb);
   partition(K, G, dg::BK, kb);
-  // fused exchange and every GPU has a panel and a slab: the pipelined path (sub-slabs, sub-panels, deferred C)
-  if (m.fused && need_ab && nb[G] - nb[G - 1] > 0 && kb[G] - kb[G - 1] > 0 && !getenv("DGEMM_B200_MULTI_SIMPLE"))
-    return run_host_multi_pipelined(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC, G, nb, kb);
+  // fused exchange and every GPU has a K-slab of its own: the rank pipeline (dgemm_rank.cu); a GPU without columns still
+  // uploads and publishes its slab
+  if (m.fused && need_ab && kb[G] - kb[G - 1] > 0 && !getenv("DGEMM_B200_MULTI_SIMPLE"))
+    return run_host_multi_ranked(M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC, G, nb, kb);
 
   for (int d = 0; d < G; d++) {
     MCU(cudaSetDevice(d));

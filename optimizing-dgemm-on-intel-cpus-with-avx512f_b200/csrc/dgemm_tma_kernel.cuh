@@ -82,7 +82,7 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
   const uint32_t progress = bars + 16 * STAGES;            // segments the producer has started (paces the C prefetch)
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
-  if (tid == 0) stamp(P, 0);
+  if (tid == 0) stamp(P, 0);   // (debug timeline only; the one global write ahead of griddep_wait, into its own buffer)
 
   if (tid == 0) {
 #pragma unroll
@@ -95,6 +95,11 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
     fence_mbar_init();
   }
   __syncthreads();
+  // Programmatic dependent launch: everything above overlapped the tail of the previous kernel of the stream; nothing
+  // below (first global access) runs before that kernel has completed and its writes are visible.  No-ops when the launch
+  // did not carry the attribute.  The dependents of THIS grid may start their own prologue as soon as every CTA is here.
+  griddep_wait();
+  griddep_launch_dependents();
 
   if (warp >= CONSUMER_WARPS) {
     // ------------------------------- producer warpgroup: one elected lane issues TMA --------------------------

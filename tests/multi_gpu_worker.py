@@ -29,6 +29,8 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     sptr = torch.cuda.current_stream().cuda_stream
     nb, kb = partition(N, world, 128), partition(K, world, 16)
+    if mode == "pipeline":
+        return pipeline_mode(M, N, K, alpha, beta, rank, world, dev, nb, kb)
     n0, n1 = nb[rank], nb[rank + 1]
     ncols = n1 - n0
     k0, k1 = kb[rank], kb[rank + 1]
@@ -87,6 +89,47 @@ def main():
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(1 if flag.item() else 0)
+
+
+def pipeline_mode(M, N, K, alpha, beta, rank, world, dev, nb, kb):
+    """dgemm_b200_rank_pipeline from HOST operands, real peers: every rank uploads its own K-slab, pulls the others over
+    NVLink behind their sequence words, and its whole C panel is checked against the oracle.  Two passes (pass numbers 0, 1)."""
+    host = dist.new_group(backend="gloo")
+    n0, ncols = nb[rank], nb[rank + 1] - nb[rank]
+    k0, kc = kb[rank], kb[rank + 1] - kb[rank]
+    x = dg.exchange_alloc(M, K)
+    handles = [None] * world
+    dist.all_gather_object(handles, dg.ipc_export(x), group=host)
+    peers = {g: dg.ipc_open(handles[g]) for g in range(world) if g != rank}
+    xbuf = [x if g == rank else peers[g] for g in range(world)]
+    Ah = ol.fill_signed(M, K, M, 1)
+    Bh = ol.fill_signed(K, max(ncols, 1), max(K, 1), 2, col0=n0)
+    C0 = ol.fill_signed(M, max(ncols, 1), M, 3, col0=n0)
+    A_slab = np.asfortranarray(Ah[:, k0:k0 + kc])
+    ok = True
+    Cin = C0
+    for p in range(2):
+        Cg = Cin.copy(order="F")
+        dg.rank_pipeline(M, ncols, K, alpha, A_slab, M, Bh, Bh.shape[0], beta, Cg, M, rank, world, kb, xbuf, p)
+        dist.barrier(group=host)
+        if ncols > 0:
+            want = Cin.copy(order="F")
+            ol.oracle_k18(M, ncols, K, alpha, Ah, Bh, beta, want)
+            ratio, max_abs = ol.bound_ratio(M, ncols, K, alpha, Ah, Bh, beta, Cin, Cg, want)
+            good = ratio <= 2.0
+            ok = ok and good
+            print(f"rank {rank} pass {p}: panel [{n0},{n0 + ncols}) max |err|/bound = {ratio:.3g} (max abs {max_abs:.3g}) "
+                  f"{'OK' if good else 'FAIL'}", flush=True)
+        Cin = Cg
+    flag = torch.tensor([0 if ok else 1], device=dev)
+    dist.all_reduce(flag)
+    dist.barrier(group=host)
+    for q in peers.values():
+        dg.ipc_close(q)
+    dist.barrier(group=host)
+    dg.free(x)
     dist.destroy_process_group()
     sys.exit(1 if flag.item() else 0)
 

@@ -122,4 +122,5 @@ def test_odd_leading_dimensions_at_8192_sampled(dg, pads):
 
 def test_odd_leading_dimensions_at_8192_split_kernel_with_two_halves(dg, monkeypatch):
     monkeypatch.setenv("DGEMM_B200_SPLIT_MAX_FLOPS2", "1e30")   # keep the split kernel where the policy would realign
+    dg.reload_env()
     test_odd_leading_dimensions_at_8192_sampled(dg, (1, 1))

@@ -103,8 +103,10 @@ def test_pageable_staging_is_byte_exact(dg, shape, pad, alpha, beta, monkeypatch
     for staging in ("1", None, None):
         if staging:
             monkeypatch.setenv("DGEMM_B200_NO_STAGING", staging)
+            dg.reload_env()
         else:
             monkeypatch.delenv("DGEMM_B200_NO_STAGING", raising=False)
+            dg.reload_env()
         Cg = C0.copy(order="F")
         dg.mydgemm_gpu_v20(M, N, K, alpha, A, A.shape[0], B, B.shape[0], beta, Cg, Cg.shape[0])
         gu.check(M, N, K, alpha, A, B, beta, C0, Cg)

@@ -37,7 +37,23 @@ def test_torchrun_sharded_dgemm(shape, mode):
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("shape", [(1024, 2048, 1024), (1000, 1003, 997), (4096, 8192, 4096), (2048, 1024, 64)])
+def test_torchrun_rank_pipeline_from_host_operands(shape):
+    """dgemm_b200_rank_pipeline with REAL peers (tests/test_gpu_rank_pipeline.py covers it with emulated peers on one GPU)."""
+    M, N, K = shape
+    n = min(_ngpu(), 4)
+    port = 29500 + os.getpid() % 200
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_worker.py"), str(M), str(N),
+           str(K), "1.5", "0.5", "pipeline"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "FAIL" not in r.stdout
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
 @pytest.mark.parametrize("shape,pad,alpha,beta", [((1024, 2048, 1024), (0, 0, 0), 1.0, 1.0),
+                                                  ((4096, 6144, 4096), (0, 0, 0), 1.0, 1.0),
                                                   ((1000, 1003, 997), (3, 1, 5), 2.5, 0.5),
                                                   ((300, 700, 0), (0, 0, 0), 1.0, 0.5),
                                                   ((512, 900, 333), (0, 0, 0), -1.0, 0.0)])

@@ -153,6 +153,7 @@ def test_large_unaligned_operands(dg, case, monkeypatch):
     (M, N, K), pad, offset = case
     gu.run_device(dg, M, N, K, 1.5, 0.5, pad=pad, offset=offset)
     monkeypatch.setenv("DGEMM_B200_SPLIT_MAX_FLOPS2", "1e9")
+    dg.reload_env()
     gu.run_device(dg, M, N, K, 1.5, 0.5, pad=pad, offset=offset)
 
 
@@ -175,8 +176,10 @@ def test_k_lockstep_changes_no_bits(dg, monkeypatch):
     for no_lockstep in (None, None, "1"):
         if no_lockstep:
             monkeypatch.setenv("DGEMM_B200_NO_LOCKSTEP", no_lockstep)
+            dg.reload_env()
         else:
             monkeypatch.delenv("DGEMM_B200_NO_LOCKSTEP", raising=False)
+            dg.reload_env()
         dC = gu.DevMat(dg, C0)
         dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, TMA, 0)
         assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
@@ -249,6 +252,7 @@ def test_parity_split_tensor_maps(dg, case, ab):
 def test_odd_ld_modes_agree_with_the_oracle(dg, mode, monkeypatch):
     """DGEMM_B200_ODD_LD selects how TMA-ineligible operands are handled; every mode meets the bound."""
     monkeypatch.setenv("DGEMM_B200_ODD_LD", mode)
+    dg.reload_env()
     gu.run_device(dg, 1000, 1003, 997, 2.5, 0.5)
     gu.run_device(dg, 1001, 1003, 999, 1.0, 1.0, offset=(1, 0, 0))
 
@@ -284,6 +288,7 @@ def test_small_tile_and_big_tile_kernels(dg, shape, ab, monkeypatch):
     for pad in ((0, 0, 0), (2, 2, 1)):
         gu.run_device(dg, M, N, K, ab[0], ab[1], pad=pad, c_fill=np.nan if ab[1] == 0.0 else None, nan_pad=True)
     monkeypatch.setenv("DGEMM_B200_NO_SMALL_TILE", "1")
+    dg.reload_env()
     gu.run_device(dg, M, N, K, ab[0], ab[1], c_fill=np.nan if ab[1] == 0.0 else None)
 
 

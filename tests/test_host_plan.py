@@ -88,3 +88,19 @@ def test_deferred_c_only_when_c_is_read():
     assert all(p < d for (_, p, _) in order[:d])          # the first calls open the deferred panels
     dg.host_plan(16384, 16384, 16384, 1.0, 0.0)
     assert dg.host_plan.deferred_panels == 0
+
+
+@pytest.mark.parametrize("shape", [(128, 4000000, 128), (128, 128, 4000000), (64, 200000, 200000), (8, 3670017, 16)])
+def test_planner_always_returns_a_schedule_for_huge_thin_shapes(dg, shape):
+    """N or K in the millions with the other dimensions thin: even the widest pieces exceed the item budget; the planner
+    must widen them instead of returning an empty plan (which used to abort mydgemm_gpu_v20 with std::length_error)."""
+    M, N, K = shape
+    nb, kb, order, ms = dg.host_plan(M, N, K, cap=1 << 16)
+    assert nb[0] == 0 and nb[-1] == N and kb[0] == 0 and kb[-1] == K and order and ms < 1e12
+    assert (len(nb) - 1) * (len(kb) - 1) <= 448
+    seen = set()
+    for s, p, e in order:
+        for x in range(s, e):
+            assert (x, p) not in seen
+            seen.add((x, p))
+    assert len(seen) == (len(nb) - 1) * (len(kb) - 1)

@@ -17,6 +17,7 @@ for (M, N, K) in shapes:
         for k in ("DGEMM_B200_NO_SMALL_TILE", "DGEMM_B200_SMALL_TILE_MAX_TILES", "DGEMM_B200_SMALL_TILE_MAX_FLOPS"):
             os.environ.pop(k, None)
         os.environ.update(env)
+        dg.reload_env()   # the library reads its switches once
         ms = dg.time_device(M, N, K, 1.0, dA, M, dB, K, 1.0, dC, M, warmup=3, reps=20, flush_l2_bytes=256 << 20)
         row[name + "_us"] = round(ms * 1e3, 2); row[name + "_tflops"] = round(2.0 * M * N * K / ms / 1e9, 3)
         row[name + "_plan"] = dg.plan(M, N, K, dA, M, dB, K)
