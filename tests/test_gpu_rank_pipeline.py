@@ -126,9 +126,9 @@ def test_peer_slab_that_never_arrives_is_an_error_not_a_hang(dg, monkeypatch):
     own, dead = _exchange(dg, M, K), _exchange(dg, M, K)   # the "peer" never uploads: its word stays 0
     try:
         kb = partition(K, 2, 16)
+        Cg = C0.copy(order="F")   # (kept alive: the library writes the panel back before it reports the failure)
         with pytest.raises(dg.DgemmError) as e:
-            dg.rank_pipeline(M, 256, K, 1.0, A.ctypes.data, M, B.ctypes.data, K, 1.0, C0.copy(order="F").ctypes.data, M, 0, 2,
-                             kb, [own, dead], 0)
+            dg.rank_pipeline(M, 256, K, 1.0, A.ctypes.data, M, B.ctypes.data, K, 1.0, Cg.ctypes.data, M, 0, 2, kb, [own, dead], 0)
         assert "never arrived" in str(e.value)
     finally:
         dg.free(own); dg.free(dead)
