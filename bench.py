@@ -675,6 +675,8 @@ def run_v21(torch, dg, G, size, reps):
     copies inside the timed region.  Rank 0 only; the other ranks have released their GPUs and wait on a host barrier."""
     import numpy as np
     M = Nn = K = size
+    if dg.device_count() < G:
+        return {"value": None, "note": f"rank 0 sees {dg.device_count()} GPUs, needs {G} (CUDA_VISIBLE_DEVICES per rank?)"}
     dg.lib.dgemm_b200_set_max_gpus(G)
     nbytes = 8 * M * M
     hA, hB, hC = (dg.lib.dgemm_b200_host_alloc(nbytes) for _ in range(3))
