@@ -277,6 +277,50 @@ def reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------------------------------
+# host placement: pinned buffers next to the GPU that reads them
+# ------------------------------------------------------------------------------------------------------------------
+def bind_to_gpu_numa(torch, dev_index):
+    """Run this process on the CPUs of the NUMA node its GPU hangs off, so that the pinned host buffers it allocates next
+    (first touch) are local to that GPU's PCIe root: with 8 GPUs uploading at once, half of them would otherwise read
+    through the socket interconnect.  Best effort: returns a note for the JSON line, never raises."""
+    try:
+        p = torch.cuda.get_device_properties(dev_index)
+        bus = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return f"GPU {bus}: numa_node = -1 (single-node host), not bound"
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if not allowed:
+            return f"GPU {bus}: node {node} has no CPU this process may use, not bound"
+        os.sched_setaffinity(0, allowed)
+        return f"GPU {bus}: bound to NUMA node {node} ({len(allowed)} CPUs)"
+    except Exception as e:  # noqa: BLE001
+        return f"not bound ({type(e).__name__}: {e})"
+
+
+def interleave_host_memory():
+    """mydgemm_gpu_v21 hands ONE set of host matrices to all GPUs: spread their pages over every NUMA node (MPOL_INTERLEAVE)
+    so that both sockets' memory controllers feed the PCIe links.  Best effort."""
+    try:
+        import ctypes
+        nodes = [int(d[4:]) for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        if len(nodes) < 2:
+            return "single NUMA node"
+        mask = ctypes.c_ulong(sum(1 << n for n in nodes))
+        libc = ctypes.CDLL(None, use_errno=True)
+        rc = libc.syscall(238, 3, ctypes.byref(mask), ctypes.c_ulong(max(nodes) + 2))   # set_mempolicy(MPOL_INTERLEAVE)
+        return f"MPOL_INTERLEAVE over nodes {sorted(nodes)}" if rc == 0 else f"set_mempolicy failed (errno {ctypes.get_errno()})"
+    except Exception as e:  # noqa: BLE001
+        return f"not interleaved ({type(e).__name__}: {e})"
+
+
+# ------------------------------------------------------------------------------------------------------------------
 # the B200 arm
 # ------------------------------------------------------------------------------------------------------------------
 _REAL_STDOUT = None
@@ -323,6 +367,7 @@ def main():
         raise SystemExit("bench.py: no B200 visible — the DGEMM path is CUDA-only (no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_note = bind_to_gpu_numa(torch, local_rank) if os.environ.get("BENCH_NO_NUMA") != "1" else "BENCH_NO_NUMA=1"
     host_group = None
     if N > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -536,6 +581,7 @@ def main():
                    "l2": "operands (3 x %.1f GB) far exceed the 126 MB L2; no flush needed" % (8.0 * size * size / 1e9),
                    "inputs": "U(-1,1) 53-bit counter-based, generated on device (dgemm_b200_fill_signed)",
                    "timing": "CUDA events on the launching stream, max over ranks"},
+        "host_placement": numa_note,
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "cublas_ceiling": cublas,
         "spot_check_max_err_over_bound": value_check,
@@ -678,6 +724,11 @@ def run_v21(torch, dg, G, size, reps):
     if dg.device_count() < G:
         return {"value": None, "note": f"rank 0 sees {dg.device_count()} GPUs, needs {G} (CUDA_VISIBLE_DEVICES per rank?)"}
     dg.lib.dgemm_b200_set_max_gpus(G)
+    try:
+        os.sched_setaffinity(0, range(os.cpu_count() or 1))   # (rank 0 was bound to its own GPU's node for the per-rank legs)
+    except OSError:
+        pass
+    placement = interleave_host_memory()
     nbytes = 8 * M * M
     hA, hB, hC = (dg.lib.dgemm_b200_host_alloc(nbytes) for _ in range(3))
     if not (hA and hB and hC):
@@ -716,7 +767,7 @@ def run_v21(torch, dg, G, size, reps):
     if not check <= 1.0:
         raise SystemExit(f"bench.py: mydgemm_gpu_v21 result is WRONG: max |err|/bound = {check}")
     return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "unit": UNIT, "ms_per_step": 1e3 * dt / reps, "reps": reps,
-            "size": size, "gpus": G, "h2d_bytes_per_step": 3 * nbytes, "d2h_bytes_per_step": nbytes, "gpu_launches": launches,
+            "size": size, "gpus": G, "host_placement": placement, "h2d_bytes_per_step": 3 * nbytes, "d2h_bytes_per_step": nbytes, "gpu_launches": launches,
             "spot_check_max_err_over_bound": check,
             "spot_check": f"{len(idx)} entries (incl. both sides of every panel boundary) recomputed on the host in long double",
             "api": f"mydgemm_gpu_v21(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC), M=N=K={size}, pinned host pointers, one process "

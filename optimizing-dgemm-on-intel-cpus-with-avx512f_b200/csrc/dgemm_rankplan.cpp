@@ -155,14 +155,19 @@ RankPlan plan_rank_pipeline(int M, int ncols, int K, int G, int rank, const int*
       return R;
     }
     std::vector<char> started(SP, 0);
+    // j >= 0: one column sub-panel; j < 0: ALL columns in one call (slab-major calls that finish no sub-panel: the B block
+    // of a K piece is small, and one launch over 64 tile columns has less ramp and tail than seven over 15 or fewer)
     auto add_call = [&](int k0, int kc, int j, bool last, int a_piece) {
       RankCall c = {};
-      c.k0 = k0; c.kc = kc; c.c0 = R.sp[j]; c.nc = R.sp[j + 1] - R.sp[j]; c.sub = j;
-      c.first = started[j] ? 0 : 1;
+      c.k0 = k0; c.kc = kc; c.sub = j;
+      c.c0 = j >= 0 ? R.sp[j] : 0;
+      c.nc = j >= 0 ? R.sp[j + 1] - R.sp[j] : ncols;
+      const int j0 = j >= 0 ? j : 0, j1 = j >= 0 ? j + 1 : SP;
+      c.first = started[j0] ? 0 : 1;   // (sub-panels are always started together: phase 1 precedes phase 2)
       c.last = last ? 1 : 0;
       c.f_owner = -1; c.f_k0 = 0; c.f_kc = 0;
       c.wait_x_copy = -1;
-      started[j] = 1;
+      for (int jj = j0; jj < j1; jj++) started[jj] = 1;
       if (a_piece >= 0) {   // own slab: the piece goes up once, ahead of its first B block
         bool sent = false;
         for (const RankCopy& cp : R.copies) sent |= cp.kind == RANK_COPY_A && cp.piece == a_piece;
@@ -183,10 +188,18 @@ RankPlan plan_rank_pipeline(int M, int ncols, int K, int G, int rank, const int*
       const int g = order[i];
       const bool final_slab = (i == S - 1);
       if (i == 0) {
-        for (int q = 0; q < Q; q++)
-          for (int j = 0; j < SP; j++) add_call(R.pieces[q], R.pieces[q + 1] - R.pieces[q], j, final_slab && q == Q - 1, q);
+        for (int q = 0; q < Q; q++) {
+          if (final_slab && q == Q - 1)   // the calls that finish the sub-panels go one by one: staggered D2H
+            for (int j = 0; j < SP; j++) add_call(R.pieces[q], R.pieces[q + 1] - R.pieces[q], j, true, q);
+          else add_call(R.pieces[q], R.pieces[q + 1] - R.pieces[q], -1, false, q);
+        }
+      } else if (final_slab) {
+        for (int j = 0; j < SP; j++) add_call(kb[g], kb[g + 1] - kb[g], j, true, -1);
       } else {
-        for (int j = 0; j < SP; j++) add_call(kb[g], kb[g + 1] - kb[g], j, final_slab, -1);
+        // in K pieces of about 2048: every call carries one NVLink pull, and more, equal carriers pace the pulls evenly
+        const int kc = kb[g + 1] - kb[g], parts = std::max(1, (kc + 1024) / 2048);
+        const int per = round_up((kc + parts - 1) / parts, 16);
+        for (int k0 = 0; k0 < kc; k0 += per) add_call(kb[g] + k0, std::min(per, kc - k0), -1, false, -1);
       }
     }
     phase_begin.push_back((int)R.calls.size());
