@@ -105,21 +105,22 @@ def main():
         rng = np.random.default_rng(1234 + rank)
         idx = [(int(rng.integers(M)), int(rng.integers(ncols))) for _ in range(4)] + [(M - 1, ncols - 1), (0, 0)]
         check = 0.0
-        for p in range(args.passes + 1):
+        for p in range(args.passes + 2):   # pass 0 warms up (buffers grow), the last one carries the timeline and the check
+            last = p == args.passes + 1
             dist.barrier(group=host)
             before = [float(hC[j * M + i]) for i, j in idx]
             t0 = time.perf_counter()
             tl = dg.rank_pipeline(M, ncols, K, 1.0, hA.data_ptr(), M, hB.data_ptr(), K, 1.0, hC.data_ptr(), M, rank, N, kb, xbuf,
-                                  pass_no, 30000 if p == 0 else 0)
+                                  pass_no, 30000 if last else 0)
             dt = time.perf_counter() - t0
             pass_no += 1
             dist.barrier(group=host)
-            if p == 0:
+            if last:
                 after = [float(hC[j * M + i]) for i, j in idx]
                 check = bench.spot_check(before, after, idx, M, K, n0, 1.0, 1.0)
                 mine = bench.summarise_timeline(tl)
                 full_tl = tl
-            else:
+            elif p > 0:
                 times.append(dt)
         t = torch.tensor([max(times), min(times), check], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
