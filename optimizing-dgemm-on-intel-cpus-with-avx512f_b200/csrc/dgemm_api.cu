@@ -837,6 +837,10 @@ int dgemm_b200_internal_rank_ctx(int dev, size_t b_bytes, size_t c_bytes, size_t
   if (b_bytes && (st = grow(cp->b, b_bytes))) return st;
   if (c_bytes && (st = grow(cp->c, c_bytes))) return st;
   if (x_bytes && (st = grow(cp->x, x_bytes))) return st;
+  // the stream-K workspace at its largest (148 ranges x 2 partial tiles of 128 x 128): no call of the pass may have to grow
+  // it, because growing synchronises the device -- and a host thread that waits for its own device while that device waits
+  // for a peer is half of a deadlock
+  if ((st = grow(cp->ws, (size_t)cp->num_sms * 2 * dg::BM * dg::BN * sizeof(double)))) return st;
   *b = cp->b.p; *c = cp->c.p; *x = cp->x.p;
   *s_compute = cp->s_compute; *s_h2d = cp->s_h2d; *s_d2h = cp->s_d2h;
   *num_sms = cp->num_sms;

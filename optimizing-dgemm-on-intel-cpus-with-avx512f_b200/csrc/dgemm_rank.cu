@@ -196,13 +196,21 @@ int rank_pipeline_exec(int dev, const RankArgs& a) {
     return DGEMM_B200_OK;
   };
 
+  // EVERY copy of the pass is queued before the first kernel.  The peers' pulls depend on this rank's uploads, and this
+  // rank's calls depend on theirs: if the host queued uploads only as its own calls came up, anything that blocks the host
+  // for a moment (a pageable source, a buffer that has to grow) while a call waits for a peer would close a cycle across
+  // ranks.  With the uploads already in the copy queue no call of any rank can ever wait for a host thread.
   for (size_t i = 0; i < plan.calls.size(); i++) {
     const RankCall& c = plan.calls[i];
-    // (a sub-panel's C_in rides behind its last B block: queue both before the call so the link never idles on the host)
+    // (a sub-panel's C_in rides behind its last B block)
     if ((st = issue_copies_through(c.wait_copy, true))) return st;
     if (c.wait_x_copy >= 0 && (st = issue_copies_through(c.wait_x_copy, true))) return st;
-    RCU(cudaStreamWaitEvent(s_compute, copy_ev[c.wait_copy], 0));
     RCU(mark(RANK_TL_H2D_DONE, (int)i, s_h2d));
+  }
+  if ((st = issue_copies_through((int)plan.copies.size() - 1, false))) return st;
+  for (size_t i = 0; i < plan.calls.size(); i++) {
+    const RankCall& c = plan.calls[i];
+    RCU(cudaStreamWaitEvent(s_compute, copy_ev[c.wait_copy], 0));
     const void* fsrc = nullptr;
     void* fdst = nullptr;
     size_t fbytes = 0;

@@ -38,16 +38,21 @@ std::vector<int> rank_slab_pieces(int M, int k_begin, int k_end) {
   std::vector<int> b{k_begin};
   const int kc = k_end - k_begin;
   if (kc <= 0) return b;
-  // first piece ~128 MB of A (2-3 ms of PCIe), at least 128 columns; main pieces 2048 columns (or the first width if larger)
+  // first piece ~128 MB of A (2-3 ms of an idle PCIe link), at least 128 columns; widths w0, w0, 2 w0, 2 w0, then 4 w0.
+  // The pieces stay this small on purpose.  With 8 GPUs uploading at once the links of this pool's hosts drop to 23-35 GB/s
+  // (measured, profiles/r02_e2e_multi_n8.jsonl), which is barely faster than the own slab is multiplied (a 65536 x 8192 panel
+  // consumes a column of A in 29 us and receives one in 17-26 us): a piece that is twice as wide as the one before it then
+  // arrives AFTER the previous one has been multiplied, and a 2048-wide last piece would leave 60 ms of math behind the last
+  // upload.  A 1024-wide call costs ~1 % more than a 2048-wide one (one more epilogue per tile).
   long long w0 = (128ll << 20) / (8ll * std::max(M, 1));
   w0 = std::max(128ll, std::min(2048ll, (w0 + 127) / 128 * 128));
-  const int main_w = std::max(2048, (int)w0);
+  const int main_w = (int)std::min(4 * w0, std::max(2048ll, w0));
   int w = (int)w0, reps = 2;
   while (b.back() < k_end) {
     int nxt = b.back() + w;
     if (k_end - nxt < w / 2) nxt = k_end;   // fold a short remainder into the last piece
     b.push_back(std::min(nxt, k_end));
-    if (--reps == 0) { w = std::min(main_w, 2 * w); reps = 1; }
+    if (--reps == 0) { w = std::min(main_w, 2 * w); reps = 2; }
   }
   return b;
 }
@@ -117,6 +122,27 @@ static bool spread_pulls(RankPlan& R, int M, const int* kb, const std::vector<in
   return true;
 }
 
+// Shift the pulls of the calls [c_begin, c_end) (all of ONE slab, in column order) one call later: call i carries what call
+// i-1 carried, the last call carries the last two shares, the first none.  The owner uploads its slab piece by piece at the
+// pace of ITS link; a puller on a faster link would otherwise ask for piece q the moment its own piece q has landed.
+static void lag_pulls(RankPlan& R, int c_begin, int c_end) {
+  if (c_end - c_begin < 2) return;
+  RankCall& last = R.calls[c_end - 1];
+  const RankCall& before_last = R.calls[c_end - 2];
+  if (before_last.f_owner >= 0) {
+    if (last.f_owner < 0) {
+      last.f_owner = before_last.f_owner; last.f_k0 = before_last.f_k0; last.f_kc = before_last.f_kc;
+    } else {
+      last.f_kc += last.f_k0 - before_last.f_k0;   // contiguous: [before_last.f_k0, last.f_k0 + last.f_kc)
+      last.f_k0 = before_last.f_k0;
+    }
+  }
+  for (int i = c_end - 2; i > c_begin; i--) {
+    R.calls[i].f_owner = R.calls[i - 1].f_owner; R.calls[i].f_k0 = R.calls[i - 1].f_k0; R.calls[i].f_kc = R.calls[i - 1].f_kc;
+  }
+  R.calls[c_begin].f_owner = -1; R.calls[c_begin].f_k0 = 0; R.calls[c_begin].f_kc = 0;
+}
+
 RankPlan plan_rank_pipeline(int M, int ncols, int K, int G, int rank, const int* kb, bool need_c_in, int p1_override) {
   RankPlan R;
   R.ok = false;
@@ -140,7 +166,7 @@ RankPlan plan_rank_pipeline(int M, int ncols, int K, int G, int rank, const int*
   // spread over the phase-1 slabs, so a longer phase 1 means a gentler NVLink rate and a shorter window for the D2H.
   //   S = 1: 1;  S = 2: 1;  S >= 3: about half of the pass.  DGEMM_B200_RANK_P1 / p1_override force a value; p1 = S is the
   //   plain ring (slab i+1 pulled while slab i is multiplied, every sub-panel finishes behind the last slab).
-  int p1 = S <= 2 ? 1 : std::max(1, S / 2);
+  int p1 = S <= 2 ? 1 : std::max(2, S / 2);
   if (const char* e = getenv("DGEMM_B200_RANK_P1")) p1 = atoi(e);
   if (p1_override > 0) p1 = p1_override;
   p1 = std::max(1, std::min(S, p1));
@@ -218,9 +244,23 @@ RankPlan plan_rank_pipeline(int M, int ncols, int K, int G, int rank, const int*
     if (S > 1) {
       if (p1 == S) {   // plain ring: one slab per phase
         for (int i = 0; i + 1 < S && ok; i++) ok = spread_pulls(R, M, kb, {order[i + 1]}, phase_begin[i], phase_begin[i + 1]);
+        if (ok && Q >= 2 && phase_begin[1] - phase_begin[0] == Q) lag_pulls(R, phase_begin[0], phase_begin[1]);
       } else {
-        std::vector<int> targets(order.begin() + 1, order.end());
-        ok = spread_pulls(R, M, kb, targets, phase_begin[0], phase_begin[p1]);
+        // The calls of the OWN slab pull the next slab only, column for column at the pace the own slab is multiplied --
+        // which is the pace at which its owner uploads it (every rank's link carries the same load): asking for more, sooner,
+        // would make the DGEMM wait for another rank's PCIe link.  By the end of the own slab every owner's upload is
+        // complete, and the remaining slabs are spread over the other slab-major calls.
+        if (p1 >= 2) {
+          ok = spread_pulls(R, M, kb, {order[1]}, phase_begin[0], phase_begin[1]);
+          std::vector<int> targets(order.begin() + 2, order.end());
+          ok = ok && spread_pulls(R, M, kb, targets, phase_begin[1], phase_begin[p1]);
+        } else {
+          std::vector<int> targets(order.begin() + 1, order.end());
+          ok = spread_pulls(R, M, kb, targets, phase_begin[0], phase_begin[1]);
+        }
+        if (ok && Q >= 2 && R.calls[phase_begin[1] - 1].f_owner == order[1] && R.calls[phase_begin[0]].f_owner == order[1] &&
+            (p1 >= 2 || S == 2))
+          lag_pulls(R, phase_begin[0], phase_begin[1]);
         // deadline check: every pull of slab order[i] sits in a call before the first call that multiplies it
         for (int i = 1; i < S && ok; i++) {
           const int g = order[i];
