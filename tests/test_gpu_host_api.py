@@ -1,4 +1,6 @@
 """-m gpu: the 11-argument reference signature (host pointers) and the Python mirror of test_kernel."""
+import os
+
 import numpy as np
 import pytest
 
@@ -131,3 +133,34 @@ def test_add_scaled_is_exact(dg):
     assert np.array_equal(out, want)
     with pytest.raises(dg.DgemmError):
         dg.add_scaled(8, 8, 1.0, dX.ptr, 4, dC.ptr, 8)          # ldx < M
+
+
+# ---- ONE harness binary for kernel numbers 0..21 (reference test.c:8-19, utils.c:167-191, kernels.h:1-19) -----------------
+PATCHED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "dgemm_x86_patched")
+
+
+@pytest.mark.skipif(not os.path.exists(PATCHED), reason="oracle/_ref/dgemm_x86_patched not built (tools/patch_reference.sh "
+                                                        "needs the reference tree, which exists in the build container)")
+@pytest.mark.parametrize("kernel", [0, 18, 19, 20, 21])
+def test_patched_reference_harness_dispatches_every_kernel_number(kernel):
+    """The reference's own test.c / utils.c / kernels.h with the INTEGRATION.md patch applied (tools/patch_reference.sh), built
+    against libdgemm_b200.so: `./dgemm_x86 N` for the reference's kernels, for kernel 0 (cblas_dgemm, served by the B200) and
+    for the two GPU kernel numbers.  First five sizes; the harness verifies every kernel against cblas_dgemm with its own
+    1e-2 check (test.c:36-43) and exits -3 on a mismatch, -6 when a GPU kernel reports an error."""
+    import re
+    import subprocess
+    env = dict(os.environ, DGEMM_X86_MAX_SIZE="500", OMP_NUM_THREADS="2")   # two threads: even row bands (SURVEY.md F3)
+    r = subprocess.run([PATCHED, str(kernel)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    sizes = re.findall(r"^M=N=K=(\d+):$", r.stdout, flags=re.M)
+    perf = re.findall(r"^Average elasped time: ([0-9.]+) second, performance: ([0-9.]+) GFLOPS\.$", r.stdout, flags=re.M)
+    assert sizes == ["100", "200", "300", "400", "500"] and len(perf) == 5
+    assert all(float(g) > 0 for _t, g in perf)
+
+
+def test_patched_reference_harness_rejects_kernel_22():
+    if not os.path.exists(PATCHED):
+        pytest.skip("oracle/_ref/dgemm_x86_patched not built")
+    import subprocess
+    r = subprocess.run([PATCHED, "22"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 254 and "0-21" in r.stdout     # exit(-2), reference test.c:16-19 with the widened range
