@@ -45,7 +45,9 @@ enum {
   DGEMM_B200_VARIANT_CPASYNC8 = 2,   /* cp.async 8-byte loader: any alignment / odd leading dimensions */
   DGEMM_B200_VARIANT_CPASYNC16 = 3,  /* cp.async 16-byte loader */
   DGEMM_B200_VARIANT_NAIVE = 4,      /* optimisation-ladder rung 1: one thread per entry (never auto-selected) */
-  DGEMM_B200_VARIANT_DFMA = 5        /* ladder rung 2: smem tiles + 8x8 register tile on the CUDA-core FP64 pipe */
+  DGEMM_B200_VARIANT_DFMA = 5,       /* ladder rung 2: smem tiles + 8x8 register tile on the CUDA-core FP64 pipe */
+  DGEMM_B200_VARIANT_CLUSTER = 6     /* ladder rung 6: 2-CTA thread-block clusters, the shared A panel by TMA multicast
+                                        (data-parallel tile pairs, TMA-eligible operands only; never auto-selected) */
 };
 
 /* ---- the reference's kernel signature (replaces mydgemm_cpu_v18 / v19 at utils.c:159-165) ---------------- */
@@ -184,6 +186,10 @@ double dgemm_b200_time_device(int M, int N, int K, double alpha, const double *d
  * up to 16 %globaltimer stamps (entry, consumer start, then per segment: operands landed / main loop done / epilogue
  * done) into dbuf[cta*16 ...].  NULL switches it off (default). */
 int dgemm_b200_debug_timeline(unsigned long long *dbuf);
+/* test aid for the co-residency guarantee of the kernels that wait for each other (k-lockstep, parallel stream-K fix-up):
+ * launches, on a stream of its own, `ctas` CTAs that each hold `smem_bytes` of shared memory for `ms` milliseconds
+ * (<= 5000) and returns at once.  A DGEMM issued while they run must still finish with the right result. */
+int dgemm_b200_debug_occupy_sms(int ctas, unsigned smem_bytes, double ms);
 /* number of kernels this library has launched since the last reset (bench.py's gpu_launches) */
 int dgemm_b200_launch_count(void);
 void dgemm_b200_reset_launch_count(void);

@@ -22,9 +22,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("DGEMM_B200_LIB") or os.path.join(_HERE, "libdgemm_b200.so")  # env: experimental builds
 
 OK, ERR_NO_DEVICE, ERR_BAD_ARG, ERR_OOM, ERR_CUDA, ERR_NCCL = range(6)
-VARIANT_AUTO, VARIANT_TMA, VARIANT_CPASYNC8, VARIANT_CPASYNC16, VARIANT_NAIVE, VARIANT_DFMA = range(6)
+VARIANT_AUTO, VARIANT_TMA, VARIANT_CPASYNC8, VARIANT_CPASYNC16, VARIANT_NAIVE, VARIANT_DFMA, VARIANT_CLUSTER = range(7)
 VARIANT_NAMES = {VARIANT_AUTO: "auto", VARIANT_TMA: "tma_ws", VARIANT_CPASYNC8: "cpasync8",
-                 VARIANT_CPASYNC16: "cpasync16", VARIANT_NAIVE: "naive", VARIANT_DFMA: "dfma_regtile"}
+                 VARIANT_CPASYNC16: "cpasync16", VARIANT_NAIVE: "naive", VARIANT_DFMA: "dfma_regtile",
+                 VARIANT_CLUSTER: "tma_cluster_multicast"}
 
 # every symbol include/dgemm_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
@@ -34,7 +35,7 @@ EXPORTS = [
     "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
-    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_host_plan",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_host_plan",
     "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled", "dgemm_b200_rank_pipeline",
     "dgemm_b200_exchange_bytes", "dgemm_b200_exchange_alloc", "dgemm_b200_rank_plan", "dgemm_b200_reload_env",
 ]
@@ -105,6 +106,7 @@ lib.dgemm_b200_fill_signed.argtypes = [_vp, C.c_int, C.c_int, _ll, C.c_ulonglong
 lib.dgemm_b200_time_device.argtypes = _DEV_ARGS + [C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t]
 lib.dgemm_b200_time_device.restype = C.c_double
 lib.dgemm_b200_debug_timeline.argtypes = [_vp]
+lib.dgemm_b200_debug_occupy_sms.argtypes = [C.c_int, C.c_uint, C.c_double]
 lib.dgemm_b200_reset_launch_count.restype = None
 lib.dgemm_b200_sm_clock_mhz.restype = C.c_double
 

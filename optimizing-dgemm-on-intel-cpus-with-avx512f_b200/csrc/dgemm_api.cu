@@ -320,7 +320,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
     plan_stream_k(P, num_sms);
     return DGEMM_B200_OK;
   }
-  if (variant == dg::VARIANT_NAIVE || variant == dg::VARIANT_DFMA) splits = 1;  // ladder rungs: whole K per CTA
+  if (variant == dg::VARIANT_NAIVE || variant == dg::VARIANT_DFMA || variant == dg::VARIANT_CLUSTER) splits = 1;  // ladder rungs: whole K per CTA
   if (splits <= 0) splits = choose_splits(tiles, P.k_tiles, num_sms);
   splits = std::max(1, std::min(splits, P.k_tiles));
   P.k_tiles_per_split = (P.k_tiles + splits - 1) / splits;
@@ -416,7 +416,9 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   const bool use_split = can_split && !realigned;
   const bool auto_variant = variant == dg::VARIANT_AUTO;
   if (variant == dg::VARIANT_AUTO) variant = (tma_ok || use_split) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
-  if (variant < 0 || variant > dg::VARIANT_DFMA) return fail(DGEMM_B200_ERR_BAD_ARG, "unknown kernel variant %d", variant);
+  if (variant < 0 || variant > dg::VARIANT_CLUSTER) return fail(DGEMM_B200_ERR_BAD_ARG, "unknown kernel variant %d", variant);
+  if (variant == dg::VARIANT_CLUSTER && (!tma_ok || fetch.bytes))
+    return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d (clusters + multicast) needs 16-byte aligned A/B, even LDA/LDB and no fused fetch", variant);
   if (variant == dg::VARIANT_CPASYNC16 && !tma_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d needs 16-byte aligned A/B and even LDA/LDB", variant);
   if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
@@ -1227,6 +1229,29 @@ double dgemm_b200_time_device(int M, int N, int K, double alpha, const double* d
 
 int dgemm_b200_debug_timeline(unsigned long long* dbuf) {
   g_timeline = dbuf;
+  return DGEMM_B200_OK;
+}
+
+// test aid for the co-residency guarantee: `ctas` CTAs that each hold `smem_bytes` of shared memory and spin for `ms`
+__global__ void occupy_sms_kernel(unsigned long long ns) {
+  extern __shared__ unsigned char hog[];
+  if (threadIdx.x == 0) hog[0] = 1;
+  const unsigned long long t0 = dg::globaltimer_ns();
+  while (dg::globaltimer_ns() - t0 < ns) __nanosleep(1000);
+}
+
+int dgemm_b200_debug_occupy_sms(int ctas, unsigned smem_bytes, double ms) {
+  DeviceCtx* c;
+  if (int st = current_ctx(&c)) return st;
+  if (ctas <= 0 || ms < 0 || ms > 5000.0) return fail(DGEMM_B200_ERR_BAD_ARG, "debug_occupy_sms: ctas > 0 and 0 <= ms <= 5000");
+  if (cudaFuncSetAttribute(occupy_sms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes) != cudaSuccess)
+    return fail(DGEMM_B200_ERR_CUDA, "debug_occupy_sms: %u bytes of shared memory: %s", smem_bytes, cudaGetErrorString(cudaGetLastError()));
+  cudaStream_t s;
+  if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return fail(DGEMM_B200_ERR_CUDA, "debug_occupy_sms: stream");
+  occupy_sms_kernel<<<ctas, 32, smem_bytes, s>>>((unsigned long long)(ms * 1e6));
+  cudaError_t e = cudaGetLastError();
+  cudaStreamDestroy(s);   // released by the runtime once the kernel has finished
+  if (e != cudaSuccess) return fail(DGEMM_B200_ERR_CUDA, "debug_occupy_sms: %s", cudaGetErrorString(e));
   return DGEMM_B200_OK;
 }
 

@@ -15,6 +15,8 @@ enum Variant {
   VARIANT_CPASYNC16 = 3,  // dgemm_cpasync_kernel<2>: same eligibility as TMA
   VARIANT_NAIVE = 4,      // ladder rung 1 (dgemm_ladder.cu): never chosen by VARIANT_AUTO
   VARIANT_DFMA = 5,       // ladder rung 2: shared-memory tiles + 8x8 register tile on the CUDA-core FP64 pipe
+  VARIANT_CLUSTER = 6,    // ladder rung 6 (dgemm_kernels_cluster.cu): 2-CTA clusters, A panel by TMA multicast; data-parallel
+                          // tile pairs only, TMA-eligible operands only; never chosen by VARIANT_AUTO
 };
 
 bool tma_eligible(const Params& P);
@@ -35,6 +37,7 @@ constexpr int SMALL_BM = 64, SMALL_BN = 64;
 cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                              cudaStream_t stream, bool cooperative, bool pdl);
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
+cudaError_t launch_tma_cluster(const void* const maps[2], const Params& P, int num_sms, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);
 // C += beta * X, both M x N column-major
 cudaError_t launch_add_scaled(double* C, long long ldc, const double* X, long long ldx, int M, int N, double beta,

@@ -360,6 +360,15 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     g_launches++;
     return launch_ladder(P, variant, stream);
   }
+  if (variant == VARIANT_CLUSTER) {
+    if (!tma_eligible(P) || tma_split_bits(P) || P.fetch_bytes || P.splits != 1 || P.sk_tiles > 0 || P.tile_small)
+      return cudaErrorInvalidValue;
+    CUtensorMap tmA, tmB;
+    if (!make_tmap(&tmA, P.A, P.M, P.K, P.lda, 16, BK) || !make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, BN)) return cudaErrorInvalidValue;
+    const void* maps[2] = {&tmA, &tmB};
+    g_launches++;
+    return launch_tma_cluster(maps, P, num_sms, stream);
+  }
   if (variant == VARIANT_TMA) {
     const int split = tma_split_bits(P);
     if (split && !tma_split_ok(P)) return cudaErrorInvalidValue;

@@ -165,6 +165,79 @@ def test_ladder_rungs(dg, variant, case):
     gu.run_device(dg, M, N, K, alpha, beta, pad=pad, variant=variant, c_fill=np.nan if beta == 0.0 else None)
 
 
+@pytest.mark.parametrize("case", [((256, 256, 256), (0, 0, 0), 1.0, 1.0),        # one pair
+                                  ((1024, 1024, 1024), (0, 0, 0), 1.0, 1.0),
+                                  ((1000, 1003, 998), (0, 0, 0), 2.5, 0.5),       # ragged edges, 8 tile columns
+                                  ((640, 384, 4096), (0, 0, 0), -1.0, 0.0),       # ODD number of tile columns: a half-empty pair
+                                  ((130, 70, 18), (2, 2, 4), 1.5, 1.0),           # a single tile: the pair's second CTA has no output
+                                  ((2304, 2560, 2048), (0, 0, 0), 1.0, 1.0)])     # more pairs than clusters: the pipeline crosses tiles
+def test_cluster_multicast_rung(dg, case):
+    """Ladder rung 6 (csrc/dgemm_kernels_cluster.cu): 2-CTA clusters, the shared A panel by TMA multicast."""
+    (M, N, K), pad, alpha, beta = case
+    gu.run_device(dg, M, N, K, alpha, beta, pad=pad, variant=dg.VARIANT_CLUSTER, c_fill=np.nan if beta == 0.0 else None)
+
+
+def test_cluster_rung_same_bits_as_the_shipped_tile_loop(dg):
+    """Same 128x128 tile, same k order, same DMMA schedule: only how A reaches shared memory differs."""
+    M, N, K = 1100, 900, 777
+    A, B, C0 = gu.make_inputs(M, N, K, pad=(0, 1, 0))
+    outs = []
+    for variant in (TMA, dg.VARIANT_CLUSTER):
+        dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, variant, 1)
+        dg.lib.dgemm_b200_sync(None)
+        outs.append(dC.to_host())
+        dA.free(); dB.free(); dC.free()
+    assert np.array_equal(outs[0], outs[1])
+
+
+def test_cluster_rung_rejects_operands_tma_cannot_address(dg):
+    A, B, C0 = gu.make_inputs(256, 256, 255)   # odd LDB
+    dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+    with pytest.raises(dg.DgemmError) as e:
+        dg.dgemm_device(256, 256, 255, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, dg.VARIANT_CLUSTER, 1)
+    assert e.value.status == dg.ERR_BAD_ARG
+    dA.free(); dB.free(); dC.free()
+
+
+@pytest.mark.parametrize("no_wait", [None, "1"])
+@pytest.mark.parametrize("splits", [0, 1])
+def test_waiting_kernels_survive_a_busy_device(dg, monkeypatch, no_wait, splits):
+    """Co-residency guarantee of the configurations whose CTAs wait for each other (k-lockstep of the data-parallel waves,
+    parallel stream-K fix-up): another stream holds most of every SM's shared memory for 300 ms while a lockstep-size
+    DGEMM is issued.  With the cooperative-launch attribute the grid starts only once all its CTAs fit (after the hog);
+    with DGEMM_B200_NO_WAIT=1 the waits are dropped and the kernel shares the device.  Either way: done, and right."""
+    import time
+    if no_wait:
+        monkeypatch.setenv("DGEMM_B200_NO_WAIT", no_wait)
+    dg.reload_env()
+    M, N, K = 3072, 3072, 4096
+    A, B, C0 = gu.make_inputs(M, N, K)
+    dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+    try:
+        assert dg.lib.dgemm_b200_sync(None) == 0
+        # 148 CTAs x 150 KB: at most one per SM, and no SM is left with room for a 199 KB DGEMM CTA while they run
+        assert dg.lib.dgemm_b200_debug_occupy_sms(148, 150 * 1024, 300.0) == 0, dg.last_error()
+        t0 = time.perf_counter()
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC.ptr, dC.ld, 0, 0, splits)
+        assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+        dt = time.perf_counter() - t0
+        assert dt < 5.0, f"{dt:.1f} s: the DGEMM sat behind the hog for far longer than the hog ran"
+        gu.check(M, N, K, 1.0, A, B, 1.0, C0, dC.to_host())
+        # and half the SMs held for the whole run of the DGEMM: the grid cannot be co-resident until they are released
+        assert dg.lib.dgemm_b200_debug_occupy_sms(74, 150 * 1024, 300.0) == 0, dg.last_error()
+        dC2 = gu.DevMat(dg, C0)
+        dg.dgemm_device(M, N, K, 1.0, dA.ptr, dA.ld, dB.ptr, dB.ld, 1.0, dC2.ptr, dC2.ld, 0, 0, splits)
+        assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+        gu.check(M, N, K, 1.0, A, B, 1.0, C0, dC2.to_host())
+        dC2.free()
+    finally:
+        dA.free(); dB.free(); dC.free()
+        if no_wait:
+            monkeypatch.delenv("DGEMM_B200_NO_WAIT")
+        dg.reload_env()
+
+
 def test_k_lockstep_changes_no_bits(dg, monkeypatch):
     """Large enough for the k-lockstep of the data-parallel waves (2 full waves, operands > 96 MB, K >= 4096): the
     producers' pacing must not change a single bit, twice in a row (the counters are re-zeroed per launch), and the

@@ -5,7 +5,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import dgemm_b200 as dg
 RUNGS = [("1 naive (one thread per entry)", 4, 1), ("2 smem tiles + 8x8 register tile, DFMA", 5, 1),
          ("3 DMMA + cp.async 4-stage", 3, 1), ("4 DMMA + TMA/mbarrier warp-specialised persistent", 1, 1),
-         ("5 + stream-K tail (product path)", 1, 0)]
+         ("5 + stream-K tail (product path)", 1, 0),
+         ("6 rung 4 on 2-CTA clusters, A by TMA multicast", 6, 1)]
 for n in [int(x) for x in sys.argv[1:]] or [2048, 4096, 8192]:
     dA, dB, dC = dg.malloc(8 * n * n), dg.malloc(8 * n * n), dg.malloc(8 * n * n)
     dg.fill_signed(dA, n, n, n, 1); dg.fill_signed(dB, n, n, n, 2); dg.fill_signed(dC, n, n, n, 3)
