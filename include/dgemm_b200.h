@@ -182,7 +182,8 @@ int dgemm_b200_fill_signed(double *dX, int rows, int cols, long long ld, unsigne
 double dgemm_b200_time_device(int M, int N, int K, double alpha, const double *dA, long long lda, const double *dB,
                               long long ldb, double beta, double *dC, long long ldc, int variant, int splits,
                               int warmup, int reps, size_t flush_l2_bytes);
-/* profiling aid: when dbuf != NULL (device buffer of 148*16 unsigned long long), every CTA of the TMA kernel writes
+/* profiling aid: when dbuf != NULL (device buffer of 16 unsigned long long per CTA of the grid; 1024 * 16 is always enough),
+ * every CTA of the TMA kernel writes
  * up to 16 %globaltimer stamps (entry, consumer start, then per segment: operands landed / main loop done / epilogue
  * done) into dbuf[cta*16 ...].  NULL switches it off (default). */
 int dgemm_b200_debug_timeline(unsigned long long *dbuf);

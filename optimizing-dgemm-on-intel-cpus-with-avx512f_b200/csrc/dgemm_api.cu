@@ -55,6 +55,7 @@ struct Env {
   int max_gpus = 0;                     // DGEMM_B200_MAX_GPUS (0 = all)
   int odd_ld = 0;                       // DGEMM_B200_ODD_LD / DGEMM_B200_NO_REALIGN: ODD_SPLIT / ODD_REALIGN / ODD_CPASYNC
   bool no_small_tile = false;           // DGEMM_B200_NO_SMALL_TILE
+  int small_ctas = 2;                   // DGEMM_B200_SMALL_CTAS: 1 = the one-CTA-per-SM build of the 64 x 64 kernel, 2 = dg64x2
   long long small_max_tiles = 64;       // DGEMM_B200_SMALL_TILE_MAX_TILES
   double small_max_flops = 4e9;         // DGEMM_B200_SMALL_TILE_MAX_FLOPS
   bool no_lockstep = false;             // DGEMM_B200_NO_LOCKSTEP
@@ -84,6 +85,7 @@ struct Env {
     if (has("DGEMM_B200_NO_REALIGN") || (o && !strcmp(o, "cpasync"))) odd_ld = 2;
     else odd_ld = (o && !strcmp(o, "realign")) ? 1 : 0;
     no_small_tile = has("DGEMM_B200_NO_SMALL_TILE");
+    small_ctas = geti("DGEMM_B200_SMALL_CTAS", 2) == 1 ? 1 : 2;
     if (const char* e = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) small_max_tiles = atoll(e);
     small_max_flops = getd("DGEMM_B200_SMALL_TILE_MAX_FLOPS", small_max_flops);
     no_lockstep = has("DGEMM_B200_NO_LOCKSTEP");
@@ -296,11 +298,12 @@ bool want_small_tile(int M, int N, int K, bool tma_kernel, bool has_fetch) {
 
 int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
                 long long ldb, double beta, double* dC, long long ldc, int splits, int variant, int num_sms,
-                bool small_tile = false) {
+                int small_tile = 0) {   // small_tile: 0, or the build of the 64 x 64 kernel to plan for (1 / 2 CTAs per SM)
   P.M = M; P.N = N; P.K = K;
   P.alpha = alpha; P.beta = beta;
   P.A = dA; P.lda = lda; P.B = dB; P.ldb = ldb; P.C = dC; P.ldc = ldc;
-  P.tile_small = (small_tile && variant == dg::VARIANT_TMA && splits <= 0) ? 1 : 0;
+  P.tile_small = (small_tile && variant == dg::VARIANT_TMA && splits <= 0) ? small_tile : 0;
+  if (P.tile_small == 2) num_sms *= dg::SMALL_X2_CTAS_PER_SM;   // CTA slots the grid and the stream-K ranges are sized for
   const int bm = P.tile_small ? dg::SMALL_BM : dg::BM, bn = P.tile_small ? dg::SMALL_BN : dg::BN;
   P.tiles_m = (M + bm - 1) / bm;
   P.tiles_n = (N + bn - 1) / bn;
@@ -424,7 +427,9 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d: unaligned operands need K >= 2 and N >= 2 for parity-split tensor maps", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms,
-              auto_variant && want_small_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0));
+              auto_variant && want_small_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0) ? env().small_ctas : 0);
+  // CTA slots of the device for the kernel build that will run (the dg64x2 build keeps two CTAs per SM resident)
+  const int cta_slots = P.tile_small == 2 ? dg::SMALL_X2_CTAS_PER_SM * c.num_sms : c.num_sms;
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
   // k-lockstep of the data-parallel waves (see Params::sync_ctr): only worth it when the operands do not fit in L2 and
   // there are at least two full waves; every CTA must be resident, i.e. the grid is one CTA per SM
@@ -434,9 +439,9 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (variant == dg::VARIANT_TMA && P.splits == 1 && !kNoSync) {
     const int tiles = P.tiles_m * P.tiles_n;
     const int dp_tiles = P.sk_tiles > 0 ? P.sk_tile0 : tiles;
-    const int full_waves = dp_tiles / c.num_sms;
+    const int full_waves = dp_tiles / cta_slots;
     const double operand_bytes = 8.0 * ((double)M * K + (double)K * N);
-    if (full_waves >= 2 && dp_tiles >= c.num_sms && operand_bytes > 96e6 && P.k_tiles >= 4 * kSyncKt) {
+    if (full_waves >= 2 && dp_tiles >= cta_slots && operand_bytes > 96e6 && P.k_tiles >= 4 * kSyncKt) {
       int kt = kSyncKt;
       while ((long long)full_waves * ((P.k_tiles + kt - 1) / kt) > SYNC_POINTS) kt *= 2;
       P.sync_ctr = c.sync_ctr; P.sync_waves = full_waves; P.sync_kt = kt;
@@ -455,8 +460,8 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   };
   if (variant == dg::VARIANT_TMA && (lockstep || P.sk_parallel)) {
     const int tiles = P.tiles_m * P.tiles_n;
-    const int grid = P.sk_tiles > 0 ? P.sk_grid : std::min(tiles, c.num_sms);
-    if (env().no_wait_kernels || grid > dg::tma_coresident_capacity(P.tile_small != 0, c.num_sms)) drop_waits();
+    const int grid = P.sk_tiles > 0 ? P.sk_grid : std::min(tiles, cta_slots);
+    if (env().no_wait_kernels || grid > dg::tma_coresident_capacity(P.tile_small, c.num_sms)) drop_waits();
   }
   const bool shares_ctx = uses_ws || lockstep;  // workspace / flags / counters: one launch at a time
   // previous user on another stream (the same stream is ordered anyway, and an event wait between two kernels would
@@ -1120,12 +1125,13 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
                        !env().realign_min_set;
   const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms,
-              want_small_tile(M, N, std::max(K, 1), tma_ok || split || realign, false));
+              want_small_tile(M, N, std::max(K, 1), tma_ok || split || realign, false) ? env().small_ctas : 0);
   if (variant) *variant = v;
   if (splits) *splits = P.splits;
   if (sk_tiles) *sk_tiles = P.sk_tiles;
   const int units = P.tiles_m * P.tiles_n * P.splits;
-  if (ctas) *ctas = v == dg::VARIANT_TMA ? (P.sk_tiles > 0 ? P.sk_grid : std::min(units, c->num_sms)) : units;
+  const int cta_slots = P.tile_small == 2 ? dg::SMALL_X2_CTAS_PER_SM * c->num_sms : c->num_sms;
+  if (ctas) *ctas = v == dg::VARIANT_TMA ? (P.sk_tiles > 0 ? P.sk_grid : std::min(units, cta_slots)) : units;
   return ok();
 }
 

@@ -28,14 +28,20 @@ bool tma_split_ok(const Params& P);   // needs P.A, P.B, P.lda, P.ldb, P.K, P.N
 // programmatic dependent launch behind the previous kernel of the stream (ignored when cooperative).  TMA variants only.
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream, bool cooperative = false,
                         bool pdl = false);
-int tma_coresident_capacity(bool small_tile, int num_sms);   // CTAs of the TMA kernel the current device can hold at once
+// CTAs of the TMA kernel the current device can hold at once; tile_small as in Params (0: 128 x 128, 1: dg64, 2: dg64x2)
+int tma_coresident_capacity(int tile_small, int num_sms);
 cudaError_t small_tile_occupancy(int* ctas_per_sm);
+cudaError_t small_tile_occupancy_x2(int* ctas_per_sm);
 void tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
 // the TMA kernel on 64 x 64 tiles (dgemm_kernels_small.cu); maps = {tmA, tmA1, tmB, tmB1} (CUtensorMap*, the second of a
 // pair only read when the operand's SPLIT bit is set), boxes 16 x 16 (or 16 x 8 per k parity) / 16 x 64 (16 x 32)
 constexpr int SMALL_BM = 64, SMALL_BN = 64;
 cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                              cudaStream_t stream, bool cooperative, bool pdl);
+// the same at two CTAs per SM (dgemm_kernels_small2.cu); Params::tile_small == 2
+cudaError_t launch_tma_small_x2(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
+                                cudaStream_t stream, bool cooperative, bool pdl);
+constexpr int SMALL_X2_CTAS_PER_SM = 2;
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_tma_cluster(const void* const maps[2], const Params& P, int num_sms, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);

@@ -332,15 +332,16 @@ static cudaError_t set_smem(Kern k, int bytes) {
 
 // how many CTAs of the TMA kernel (either tile size, any split variant: same block size and shared memory) can be
 // resident on the current device at once; what a grid whose CTAs wait on each other must not exceed
-int tma_coresident_capacity(bool small_tile, int num_sms) {
-  static std::atomic<int> per_sm[2][64];
+int tma_coresident_capacity(int tile_small, int num_sms) {
+  static std::atomic<int> per_sm[3][64];
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-  std::atomic<int>& slot = per_sm[small_tile ? 1 : 0][dev & 63];
+  if (cudaGetDevice(&dev) != cudaSuccess || tile_small < 0 || tile_small > 2) return 0;
+  std::atomic<int>& slot = per_sm[tile_small][dev & 63];
   int n = slot.load(std::memory_order_relaxed);
   if (n == 0) {
     cudaError_t e;
-    if (small_tile) e = small_tile_occupancy(&n);
+    if (tile_small == 1) e = small_tile_occupancy(&n);
+    else if (tile_small == 2) e = small_tile_occupancy_x2(&n);
     else {
       const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
       e = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem);
@@ -394,12 +395,14 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
       ok = ok && make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, bn);
     }
     if (!ok) return cudaErrorInvalidValue;
-    if (P.tile_small) {   // 64 x 64 tiles: dgemm_kernels_small.cu
+    if (P.tile_small) {   // 64 x 64 tiles: dgemm_kernels_small.cu (one CTA per SM), dgemm_kernels_small2.cu (two)
+      const int slots = P.tile_small == 2 ? SMALL_X2_CTAS_PER_SM * num_sms : num_sms;
       const int dp_units = P.sk_tiles > 0 ? P.sk_tile0 : tiles;
-      const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < num_sms ? dp_units : num_sms);
+      const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < slots ? dp_units : slots);
       const void* maps[4] = {&tmA, &tmA1, &tmB, &tmB1};
       g_launches++;
-      return launch_tma_small(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
+      return P.tile_small == 2 ? launch_tma_small_x2(maps, split, Q, grid, dp_units, stream, cooperative, pdl)
+                               : launch_tma_small(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
     }
     const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
     static std::atomic<bool> attr_done[64];  // function attributes are per device

@@ -8,74 +8,10 @@
 // 32), which does not matter where the launch is a few microseconds long; run_device picks it only for small,
 // TMA-eligible problems (see dgemm_api.cu) and the 128 x 128 kernel stays the performance path.
 // Same role in the reference: the 8x8 / 2x8 ... edge micro-kernels beside the 24x8 one (include/kernel18.h:533-600).
+//
+// Two builds of it (dgemm_small_tile.cuh): this one keeps ONE CTA per SM with 8 pipeline stages; dgemm_kernels_small2.cu
+// runs TWO CTAs per SM with 4 stages each, so that one CTA's epilogue / partial exchange overlaps the other's main loop.
 #define DG_NAMESPACE dg64
-#define DG_SMALL_TILE 1
-#define DG_BM 64
-#define DG_BN 64
-#include "dgemm_tma_kernel.cuh"
-#include "dgemm_host.h"
-#include "dgemm_launch.h"
-
-#include <atomic>
-
-namespace dg {
-
-static_assert(dg64::BM == SMALL_BM && dg64::BN == SMALL_BN, "dgemm_host.h must state the small tile's size");
-
-constexpr int SMALL_STAGES = 8;   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
-constexpr int SMALL_SMEM = SMALL_STAGES * dg64::STAGE_BYTES + 2 * SMALL_STAGES * 8 + 16 + 1024;
-
-static cudaError_t small_attrs() {
-  constexpr int STAGES = SMALL_STAGES;
-  const int smem = SMALL_SMEM;
-  static std::atomic<bool> attr_done[64];  // function attributes are per device
-  int dev = 0;
-  cudaError_t err = cudaGetDevice(&dev);
-  if (err != cudaSuccess) return err;
-  if (!attr_done[dev & 63]) {
-    const cudaFuncAttribute a = cudaFuncAttributeMaxDynamicSharedMemorySize;
-    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_kernel<STAGES>, a, smem)) != cudaSuccess) return err;
-    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A>, a, smem)) != cudaSuccess) return err;
-    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_B>, a, smem)) != cudaSuccess) return err;
-    if ((err = cudaFuncSetAttribute(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A | SPLIT_B>, a, smem)) != cudaSuccess)
-      return err;
-    attr_done[dev & 63] = true;
-  }
-  return cudaSuccess;
-}
-
-cudaError_t small_tile_occupancy(int* ctas_per_sm) {
-  cudaError_t err = small_attrs();
-  if (err != cudaSuccess) return err;
-  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, dg64::dgemm_tma_ws_kernel<SMALL_STAGES>, dg64::TMA_THREADS,
-                                                       SMALL_SMEM);
-}
-
-cudaError_t launch_tma_small(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
-                             cudaStream_t stream, bool cooperative, bool pdl) {
-  constexpr int STAGES = SMALL_STAGES;
-  cudaError_t err = small_attrs();
-  if (err != cudaSuccess) return err;
-  const CUtensorMap &tmA = *reinterpret_cast<const CUtensorMap*>(maps[0]), &tmA1 = *reinterpret_cast<const CUtensorMap*>(maps[1]),
-                    &tmB = *reinterpret_cast<const CUtensorMap*>(maps[2]), &tmB1 = *reinterpret_cast<const CUtensorMap*>(maps[3]);
-  LaunchCfg cfg;
-  cfg.grid = grid; cfg.threads = dg64::TMA_THREADS; cfg.smem = SMALL_SMEM; cfg.stream = stream;
-  cfg.cooperative = cooperative; cfg.pdl = pdl;
-  switch (split) {
-    case SPLIT_NONE:
-      err = launch_ex(dg64::dgemm_tma_ws_kernel<STAGES>, cfg, tmA, tmB, P, dp_units);
-      break;
-    case SPLIT_A:
-      err = launch_ex(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A>, cfg, tmA, tmA1, tmB, tmB1, P, dp_units);
-      break;
-    case SPLIT_B:
-      err = launch_ex(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_B>, cfg, tmA, tmA1, tmB, tmB1, P, dp_units);
-      break;
-    default:
-      err = launch_ex(dg64::dgemm_tma_ws_split_kernel<STAGES, SPLIT_A | SPLIT_B>, cfg, tmA, tmA1, tmB, tmB1, P, dp_units);
-  }
-  if (err != cudaSuccess) cudaGetLastError();
-  return err;
-}
-
-}  // namespace dg
+#define DG_SMALL_STAGES 8   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
+#define DG_SMALL_FN(name) name
+#include "dgemm_small_tile.cuh"

@@ -1,0 +1,22 @@
+// dgemm_kernels_small2.cu — the 64 x 64 build of the persistent TMA kernel at TWO CTAs per SM (namespace dg64x2).
+//
+// Why: at small and mid sizes a CTA spends a visible share of its life outside the DMMA loop: start-up (barrier init,
+// descriptor fetch, first operands from cold HBM: ~2 us), one epilogue or partial store per segment (1-3 us each: C is
+// read, combined, written), the stream-K fix-up.  With one CTA per SM the FP64 pipe idles through all of it (ncu at
+// 1024^3, profiles/r01_ncu_full_dg64_1024x1024x1024.json: DMMA busy 77 % of elapsed, the busy cycles exactly the
+// algorithmic minimum).  Two resident CTAs with four consumer warps per SM sub-partition between them take turns: while
+// one drains, stores or waits for a partial, the other one's main loop has the pipe to itself.
+//
+// Budget per CTA: 384 threads compiled at 65536 / 768 = 80 registers (launch bounds (384, 2)), re-balanced to
+// 40 (producer warpgroup) / 96 (consumers: 32 accumulator registers + two fragment sets; the DMMA loop compiles without
+// local-memory traffic, with 24 / 104 it has two LDL per k-tile); 4 stages x 16 KB = 65 KB of
+// shared memory, so two CTAs hold the same 128 KB of operands in flight per SM as the one-CTA build.
+// run_device sizes the grid and the stream-K ranges for 2 x #SMs CTA slots (DGEMM_B200_SMALL_CTAS=1 selects the
+// one-CTA build).  The reference has no counterpart (one thread per core, kernel19.h:678-755).
+#define DG_NAMESPACE dg64x2
+#define DG_SMALL_STAGES 4
+#define DG_MIN_CTAS 2
+#define DG_PRODUCER_REGS 40
+#define DG_CONSUMER_REGS 96
+#define DG_SMALL_FN(name) name##_x2
+#include "dgemm_small_tile.cuh"

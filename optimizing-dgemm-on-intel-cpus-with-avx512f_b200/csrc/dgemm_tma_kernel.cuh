@@ -6,6 +6,10 @@
 
 #include <cuda.h>
 
+#ifndef DG_MIN_CTAS
+#define DG_MIN_CTAS 1   // resident CTAs per SM the kernels are compiled for (register budget = 65536 / (threads x this))
+#endif
+
 namespace DG_NAMESPACE {
 
 // =========================================================================================================
@@ -439,14 +443,14 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
 }
 
 template <int STAGES>
-__global__ void __launch_bounds__(TMA_THREADS, 1)
+__global__ void __launch_bounds__(TMA_THREADS, DG_MIN_CTAS)
 dgemm_tma_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params P,
                     int num_units) {
   tma_ws_body<STAGES, SPLIT_NONE>(tmA, tmA, tmB, tmB, P, num_units);
 }
 // operands TMA cannot describe with one map (odd LDA / LDB, 8-byte aligned bases): parity-split maps, no copy
 template <int STAGES, int SPLIT>
-__global__ void __launch_bounds__(TMA_THREADS, 1)
+__global__ void __launch_bounds__(TMA_THREADS, DG_MIN_CTAS)
 dgemm_tma_ws_split_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA1,
                           const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmB1,
                           const Params P, int num_units) {

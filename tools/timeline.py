@@ -6,19 +6,20 @@ import numpy as np
 import dgemm_b200 as dg
 M, N, K = (int(x) for x in sys.argv[1:4])
 splits = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+ROWS = 1024   # one row of 16 stamps per CTA (the grid is at most 2 CTAs x 148 SMs)
 dA, dB, dC = dg.malloc(8 * M * K), dg.malloc(8 * K * N), dg.malloc(8 * M * N)
 dg.fill_signed(dA, M, K, M, 1); dg.fill_signed(dB, K, N, K, 2); dg.fill_signed(dC, M, N, M, 3)
-tl = dg.malloc(8 * 148 * 16)
-host = np.zeros((148, 16), dtype=np.uint64)
+tl = dg.malloc(8 * ROWS * 16)
+host = np.zeros((ROWS, 16), dtype=np.uint64)
 for rep in range(3):
-    dg.lib.dgemm_b200_h2d(tl, 148 * 16, host.ctypes.data, 148 * 16, 148 * 16, 1, None)
+    dg.lib.dgemm_b200_h2d(tl, ROWS * 16, host.ctypes.data, ROWS * 16, ROWS * 16, 1, None)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(tl)
     dg.dgemm_device(M, N, K, 1.0, dA, M, dB, K, 1.0, dC, M, 0, int(os.environ.get("TL_VARIANT", "1")), splits)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(None)
-out = np.zeros((148, 16), dtype=np.uint64)
-dg.lib.dgemm_b200_d2h(out.ctypes.data, 148 * 16, tl, 148 * 16, 148 * 16, 1, None)
+out = np.zeros((ROWS, 16), dtype=np.uint64)
+dg.lib.dgemm_b200_d2h(out.ctypes.data, ROWS * 16, tl, ROWS * 16, ROWS * 16, 1, None)
 dg.lib.dgemm_b200_sync(None)
 act = out[out[:, 0] > 0]
 t0 = act[:, 0].min()
