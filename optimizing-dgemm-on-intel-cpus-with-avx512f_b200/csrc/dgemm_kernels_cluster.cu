@@ -44,20 +44,13 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t cta) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
   return r;
 }
+// arrive on the barrier at shared::cluster address `remote_bar` (a peer CTA's).  Default semantics (release at CTA scope), as
+// the local arrive: the consumer's reads of the slot are complete once their values have been used (register dependence),
+// so no fence is needed.  The first version used .release.cluster here and .acquire.cluster in the waits; ptxas turns those
+// into MEMBAR.ALL.GPU + ERRBAR + CGAERRBAR per arrive and CCTL.IVALL (L1 invalidate) per wait, and ncu showed 1.9 warps per
+// issue stalled on "membar" and the DMMA pipe 83 % busy instead of 98 % (profiles/r02_ncu_cluster_vs_tma_16384.json, v1).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t remote_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {   // acquire at cluster scope
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAITC_%=:\n\t"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONEC_%=;\n\t"
-      "bra WAITC_%=;\n\t"
-      "DONEC_%=:\n\t"
-      "}" ::"r"(bar), "r"(parity)
-      : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
 }
 // TMA 2-D tiled load, written to the same shared-memory offset of every CTA in `mask`, completion bytes counted on the
 // mbarrier at the same offset in each of them.  SASS: UTMALDG.2D.MULTICAST
@@ -111,7 +104,7 @@ dgemm_tma_cluster_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         decode_pair(pair, tm, tnp);
         const int m0 = tm * BM, n0 = (2 * tnp + (int)rank) * BN;   // (n0 >= N for the odd last pair's second tile: TMA zero-fills)
         for (int kt = 0; kt < P.k_tiles; kt++) {
-          mbar_wait_cluster(bars + 8 * (CL_STAGES + s), ph ^ 1);   // slot s is free in BOTH CTAs
+          mbar_wait(bars + 8 * (CL_STAGES + s), ph ^ 1);   // slot s is free in BOTH CTAs
           const uint32_t full = bars + 8 * s;
           const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
           mbar_arrive_expect_tx(full, STAGE_BYTES);
@@ -149,7 +142,7 @@ dgemm_tma_cluster_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       int tm, tnp;
       decode_pair(pair, tm, tnp);
       zero_acc(acc);
-      mbar_wait_cluster(bars + 8 * s, ph);
+      mbar_wait(bars + 8 * s, ph);
       load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
       for (int kt = 0; kt < P.k_tiles; kt++) {
         const uint32_t sA = smem_base + s * STAGE_BYTES, sB = sA + A_STAGE_BYTES;
@@ -161,9 +154,10 @@ dgemm_tma_cluster_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         load_frags(f0, sA, sB, lo, 2);
         mma_frags(acc, f1);
         load_frags(f1, sA, sB, lo, 3);
+        const uint32_t next_ready = has_next ? mbar_test_wait(bars + 8 * s, ph) : 0u;   // as in the shipped kernel
         mma_frags(acc, f0);
         if (has_next) {
-          mbar_wait_cluster(bars + 8 * s, ph);
+          if (!next_ready) mbar_wait(bars + 8 * s, ph);
           load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
         }
         mma_frags(acc, f1);
