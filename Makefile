@@ -32,6 +32,12 @@ $(PKG)/bin/peak_probe: $(CSRC)/peak_probe.cu
 	mkdir -p $(PKG)/bin
 	$(NVCC) $(ARCH) -O3 -lineinfo -ccbin $(HOSTCXX) -o $@ $<
 
+# measurement aid for the pageable-memory staging (tools/stage_probe.cu)
+stage_probe: $(PKG)/bin/stage_probe
+$(PKG)/bin/stage_probe: tools/stage_probe.cu
+	mkdir -p $(PKG)/bin
+	$(NVCC) $(ARCH) -O3 -std=c++17 -ccbin $(HOSTCXX) -o $@ $< -lpthread
+
 harness: $(PKG)/bin/dgemm_b200
 $(PKG)/bin/dgemm_b200: $(PKG)/harness/test.c $(PKG)/harness/utils.c $(PKG)/harness/utils.h include/kernel20.h include/dgemm_b200.h $(LIB)
 	mkdir -p $(PKG)/bin
@@ -47,4 +53,4 @@ sass: $(LIB)
 clean:
 	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
 	$(MAKE) -C oracle clean
-.PHONY: all build lib lib16 probe harness oracle sass clean
+.PHONY: all build lib lib16 probe stage_probe harness oracle sass clean

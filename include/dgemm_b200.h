@@ -162,6 +162,16 @@ int dgemm_b200_plan(int M, int N, int K, const double *dA, long long lda, const 
 int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int *panels, int *n_panels, int *slabs,
                          int *n_slabs, int *order, int *n_items, int cap, double *predicted_ms, int *deferred_panels);
 
+/* Out of core (one GPU, host-pointer entries): when A, B, C and the pipeline's side buffers exceed the HBM budget
+ * (DGEMM_B200_HBM_BUDGET bytes, default 90 % of the free HBM), mydgemm_gpu_v20 / dgemm_b200_host cut C into Mb x Nb blocks
+ * (and K into chunks of Kb only if one block's operands still do not fit) and run the in-core pipeline block by block.
+ * This reports the blocking a budget leads to and the PCIe bytes it moves (no device needed; whole dimensions = in core).
+ * Counterpart of the reference's outer N / K blocking loops (include/kernel18.h:652-669), one memory level further out. */
+int dgemm_b200_host_blocking(int M, int N, int K, double alpha, double beta, double budget_bytes, int *Mb, int *Nb, int *Kb,
+                             double *pcie_bytes);
+/* bytes of device memory the library's cached buffers hold on the current device (operand staging, workspaces) */
+size_t dgemm_b200_device_bytes(void);
+
 /* ---- helpers so a plain-C harness needs no CUDA headers -------------------------------------------------------- */
 void *dgemm_b200_malloc(size_t bytes);                 /* device memory on the current device (NULL on failure) */
 void dgemm_b200_free(void *dptr);

@@ -35,7 +35,8 @@ EXPORTS = [
     "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
-    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_host_plan",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_host_plan", "dgemm_b200_host_blocking",
+    "dgemm_b200_device_bytes",
     "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled", "dgemm_b200_rank_pipeline",
     "dgemm_b200_exchange_bytes", "dgemm_b200_exchange_alloc", "dgemm_b200_rank_plan", "dgemm_b200_reload_env",
 ]
@@ -106,6 +107,10 @@ lib.dgemm_b200_fill_signed.argtypes = [_vp, C.c_int, C.c_int, _ll, C.c_ulonglong
 lib.dgemm_b200_time_device.argtypes = _DEV_ARGS + [C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t]
 lib.dgemm_b200_time_device.restype = C.c_double
 lib.dgemm_b200_debug_timeline.argtypes = [_vp]
+lib.dgemm_b200_host_blocking.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_int),
+                                         C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double)]
+lib.dgemm_b200_device_bytes.restype = C.c_size_t
+lib.dgemm_b200_device_bytes.argtypes = []
 lib.dgemm_b200_debug_occupy_sms.argtypes = [C.c_int, C.c_uint, C.c_double]
 lib.dgemm_b200_reset_launch_count.restype = None
 lib.dgemm_b200_sm_clock_mhz.restype = C.c_double
@@ -157,6 +162,20 @@ def host_plan(M, N, K, alpha=1.0, beta=1.0, cap=4096):
     host_plan.deferred_panels = n_d.value
     return (list(nb[: n_p.value + 1]), list(kb[: n_s.value + 1]),
             [(od[3 * i], od[3 * i + 1], od[3 * i + 2]) for i in range(n_i.value)], ms.value)
+
+
+def host_blocking(M, N, K, budget_bytes, alpha=1.0, beta=1.0):
+    """Out-of-core blocking of mydgemm_gpu_v20 under an HBM budget: {"Mb", "Nb", "Kb", "pcie_bytes"} (whole dimensions when
+    the call fits in core).  Pure host logic — works without a GPU."""
+    mb, nb, kb, by = C.c_int(), C.c_int(), C.c_int(), C.c_double()
+    _check(lib.dgemm_b200_host_blocking(M, N, K, alpha, beta, float(budget_bytes), C.byref(mb), C.byref(nb), C.byref(kb),
+                                        C.byref(by)))
+    return {"Mb": mb.value, "Nb": nb.value, "Kb": kb.value, "pcie_bytes": by.value}
+
+
+def device_bytes():
+    """Bytes of device memory the library's cached buffers hold on the current device."""
+    return int(lib.dgemm_b200_device_bytes())
 
 
 def device_count():
