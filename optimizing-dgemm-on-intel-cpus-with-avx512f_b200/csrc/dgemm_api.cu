@@ -197,6 +197,7 @@ int ensure_ctx(int dev, DeviceCtx** out) {
   return DGEMM_B200_OK;
 }
 
+thread_local bool g_grow_exact = false;   // out-of-core runs: buffers are sized to the HBM budget, no head-room
 int grow(Buf& b, size_t bytes) {
   if (b.cap >= bytes) return DGEMM_B200_OK;
   if (b.p) {
@@ -205,7 +206,7 @@ int grow(Buf& b, size_t bytes) {
     b.p = nullptr;
     b.cap = 0;
   }
-  size_t want = bytes + bytes / 8;
+  size_t want = g_grow_exact ? bytes : bytes + bytes / 8;
   cudaError_t e = cudaMalloc(&b.p, want);
   if (e != cudaSuccess) {
     cudaGetLastError();
@@ -616,12 +617,6 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
   const bool stage = moved >= env().stage_min_bytes && !env().no_staging && dg::staging_usable(dev);
   const bool pa = stage && need_ab && dg::host_pointer_is_pageable(A), pb = stage && need_ab && dg::host_pointer_is_pageable(B),
              pc = stage && dg::host_pointer_is_pageable(C);
-  auto h2d = [&](double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
-                 bool pageable) -> cudaError_t {
-    if (pageable) return dg::staged_h2d(dst, ldd, src, lds, rows, cols, c.s_h2d, dev);
-    return cudaMemcpy2DAsync(dst, (size_t)ldd * 8, src, (size_t)lds * 8, (size_t)rows * 8, (size_t)cols,
-                             cudaMemcpyHostToDevice, c.s_h2d);
-  };
   const dg::HostPlan plan = dg::plan_host_pipeline(M, N, K, need_ab, need_c_in, c.num_sms, pa || pb || pc);
   const std::vector<int>& nb = plan.nb;
   const std::vector<int>& kb = plan.kb;
@@ -648,23 +643,66 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
   std::vector<cudaEvent_t> ev_in(order.size()), ev_done(P, nullptr);
   for (auto& e : ev_in) CU_TRY(events.make(&e));
   for (auto& e : ev_done) CU_TRY(events.make(&e));
-  std::vector<char> a_sent(S, 0), first_done(P, 0);
-  int result = DGEMM_B200_OK;
-  auto body = [&]() -> int {
+  // the H2D blocks every call needs first (pre) and, for a deferred-C panel, the C_in block queued behind its last call (post)
+  struct Copy { double* dst; long long ldd; const double* src; long long lds; long long rows, cols; bool pageable; };
+  std::vector<std::vector<Copy>> pre(order.size()), post(order.size());
+  {
+    std::vector<char> a_sent(S, 0), c_sent(P, 0);
     for (size_t i = 0; i < order.size(); i++) {
       const int sI = order[i].s, sE = order[i].s_end, pI = order[i].p;
       const int n0 = nb[pI], ncol = nb[pI + 1] - nb[pI];
       const int k0 = kb[sI], kc = need_ab ? kb[sE] - kb[sI] : K;
       for (int sl = sI; need_ab && sl < sE; sl++) {
         if (a_sent[sl]) continue;
-        CU_TRY(h2d(c.a.p + (size_t)kb[sl] * ldaD, ldaD, A + (size_t)kb[sl] * LDA, LDA, M, kb[sl + 1] - kb[sl], pa));
+        pre[i].push_back({c.a.p + (size_t)kb[sl] * ldaD, ldaD, A + (size_t)kb[sl] * LDA, LDA, M, kb[sl + 1] - kb[sl], pa});
         a_sent[sl] = 1;
       }
       const bool defer = pI < deferred;
-      if (need_c_in && !defer && !first_done[pI])
-        CU_TRY(h2d(c.c.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc));
+      if (need_c_in && !defer && !c_sent[pI])
+        pre[i].push_back({c.c.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc});
+      c_sent[pI] = 1;
       if (need_ab)  // B block (s,p); sending whole B panels at s == 0 front-loads the stream (measured 6 % slower)
-        CU_TRY(h2d(c.b.p + (size_t)n0 * ldbD + k0, ldbD, B + (size_t)n0 * LDB + k0, LDB, kc, ncol, pb));
+        pre[i].push_back({c.b.p + (size_t)n0 * ldbD + k0, ldbD, B + (size_t)n0 * LDB + k0, LDB, kc, ncol, pb});
+      if (defer && (int)i == last_item[pI])
+        post[i].push_back({c.x.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc});
+    }
+  }
+  // Pageable operands: every block of the whole call is handed to the staging team NOW, in stream order, so that the
+  // team streams through them without waiting for the schedule below (which only waits, per call, until that call's blocks
+  // have been queued on the copy stream).  Pinned operands: plain asynchronous copies, issued in line.
+  const bool streamed = pa || pb || pc;
+  std::vector<long long> t_pre(order.size(), -1), t_post(order.size(), -1);
+  std::vector<char> first_done(P, 0);
+  int result = DGEMM_B200_OK;
+  auto body = [&]() -> int {
+    if (streamed) {
+      long long last = -1;
+      for (size_t i = 0; i < order.size(); i++) {
+        for (const std::vector<Copy>* list : {&pre[i], &post[i]}) {
+          for (const Copy& q : *list) {
+            cudaError_t e = cudaSuccess;
+            last = dg::staging_submit_h2d(q.dst, q.ldd, q.src, q.lds, q.rows, q.cols, c.s_h2d, dev, q.pageable, &e);
+            CU_TRY(e);
+          }
+          (list == &pre[i] ? t_pre : t_post)[i] = last;
+        }
+      }
+    }
+    auto issue = [&](const std::vector<Copy>& list, long long ticket) -> cudaError_t {
+      if (streamed) return dg::staging_wait_submitted(ticket);
+      for (const Copy& q : list) {
+        cudaError_t e = cudaMemcpy2DAsync(q.dst, (size_t)q.ldd * 8, q.src, (size_t)q.lds * 8, (size_t)q.rows * 8, (size_t)q.cols,
+                                          cudaMemcpyHostToDevice, c.s_h2d);
+        if (e != cudaSuccess) return e;
+      }
+      return cudaSuccess;
+    };
+    for (size_t i = 0; i < order.size(); i++) {
+      const int sI = order[i].s, sE = order[i].s_end, pI = order[i].p;
+      const int n0 = nb[pI], ncol = nb[pI + 1] - nb[pI];
+      const int k0 = kb[sI], kc = need_ab ? kb[sE] - kb[sI] : K;
+      const bool defer = pI < deferred;
+      CU_TRY(issue(pre[i], t_pre[i]));
       CU_TRY(cudaEventRecord(ev_in[i], c.s_h2d));
       CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[i], 0));
       int s2 = run_device(c, M, ncol, kc, alpha, c.a.p + (size_t)k0 * ldaD, ldaD, c.b.p + (size_t)n0 * ldbD + k0, ldbD,
@@ -673,7 +711,7 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
       if (s2) return s2;
       first_done[pI] = 1;
       if (defer && (int)i == last_item[pI]) {
-        CU_TRY(h2d(c.x.p + (size_t)n0 * ldcD, ldcD, C + (size_t)n0 * LDC, LDC, M, ncol, pc));
+        CU_TRY(issue(post[i], t_post[i]));
         CU_TRY(cudaEventRecord(ev_x, c.s_h2d));
         CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_x, 0));
         CU_TRY(dg::launch_add_scaled(c.c.p + (size_t)n0 * ldcD, ldcD, c.x.p + (size_t)n0 * ldcD, ldcD, M, ncol, beta, c.num_sms,
@@ -703,7 +741,7 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
     const int saved = g_status;
     char msg[sizeof(g_errmsg)];
     memcpy(msg, g_errmsg, sizeof(msg));
-    if (pc) dg::staged_d2h_wait();  // the D2H team may still hold ev_done events
+    if (streamed) dg::staging_drain();  // the teams may still read A / B / C, write C, or hold ev_done events
     for (cudaStream_t q : {c.s_d2h, c.s_compute, c.s_h2d}) cudaStreamSynchronize(q);
     cudaGetLastError();
     g_status = saved;
@@ -797,6 +835,7 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   HostBlocking hb;
   if (!choose_host_blocking(M, N, K, need_ab, need_c_in, cp->num_sms, (size_t)budget, &hb))
     return fail(DGEMM_B200_ERR_OOM, "HBM budget of %.0f MB is too small for any block of M=%d N=%d K=%d", budget / 1048576.0, M, N, K);
+  struct Exact { Exact() { g_grow_exact = true; } ~Exact() { g_grow_exact = false; } } exact;
   for (int n0 = 0; n0 < N; n0 += hb.Nb) {
     const int nc = std::min(hb.Nb, N - n0);
     for (int m0 = 0; m0 < M; m0 += hb.Mb) {

@@ -128,6 +128,11 @@ cudaError_t staged_h2d(double* dst, long long ldd, const double* src, long long 
 cudaError_t staged_d2h_async(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
                              cudaEvent_t ready, cudaStream_t stream, int dev);
 cudaError_t staged_d2h_wait();
+// the streaming form of staged_h2d: submit every block ahead (ticket per block, < 0 on error), wait per ticket
+long long staging_submit_h2d(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
+                             cudaStream_t stream, int dev, bool pageable, cudaError_t* err);
+cudaError_t staging_wait_submitted(long long ticket);
+void staging_drain();   // returns when neither team holds a block any more (error paths)
 void staging_shutdown();
 
 int launch_count();

@@ -33,7 +33,10 @@ namespace {
 
 struct Model {
   double h2d = 55e9, d2h = 55e9;  // bytes/s, pinned host memory, PCIe gen5 x16 (measured; tools/pcie_probe.py)
-  double h2d_pageable = 30e9, d2h_pageable = 30e9;  // pageable memory staged by dgemm_staging.cu (measured)
+  // pageable memory staged by dgemm_staging.cu: the fill -> DMA pipeline sustains 50 GB/s alone (tools/stage_probe.cu); with
+  // the way back running beside it, planning for 45 gave 27.7 TFLOP/s at 8192^3 against 25.5 when planning for 30
+  // (profiles/r02_pageable_matrix.txt); DGEMM_B200_PAGEABLE_GBPS overrides
+  double h2d_pageable = 45e9, d2h_pageable = 45e9;
   double hbm = 5.0e12;            // bytes/s an elementwise kernel sustains (beta*C fix-up of deferred panels)
   double t_ktile = 2.13e-6;       // s per 128x128x16 k-tile per SM: 4096 clk at the DMMA issue limit, 1.965 GHz
   double t_epi = 2.2e-6;          // s per output tile per call: the fused epilogue reads and writes the C tile once per
@@ -45,6 +48,7 @@ struct Model {
   Model() {
     if (const char* e = getenv("DGEMM_B200_H2D_GBPS")) h2d = atof(e) * 1e9;
     if (const char* e = getenv("DGEMM_B200_D2H_GBPS")) d2h = atof(e) * 1e9;
+    if (const char* e = getenv("DGEMM_B200_PAGEABLE_GBPS")) h2d_pageable = d2h_pageable = atof(e) * 1e9;
   }
   double flops_per_s() const { return sms * 2.0 * BM_ * BN_ * BK_ / t_ktile; }
   static constexpr int BM_ = 128, BN_ = 128, BK_ = 16;

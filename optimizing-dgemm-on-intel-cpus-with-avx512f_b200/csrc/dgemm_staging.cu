@@ -2,11 +2,23 @@
 //
 // The reference harness hands its kernels plain malloc'ed matrices (test.c:27-30), and mydgemm_gpu_v20 keeps that
 // contract.  cudaMemcpy from pageable memory is staged by the driver through one internal bounce buffer on the
-// calling thread (~12 GB/s measured on this pool's hosts, against 55 GB/s for pinned memory), which would make the
-// drop-in call 4x slower than the same call on pinned buffers.  This file does the staging itself: a small pool of
-// host threads copies 4 MB chunks of the caller's matrix into per-thread pinned slots (two per thread, so the next
-// memcpy overlaps the previous slot's DMA) and queues the DMA of every filled slot on the copy stream; the way
-// back is the mirror image.  No arithmetic happens here — the bytes are moved, never touched.
+// calling thread (11 GB/s measured on this pool's hosts, against 55 GB/s for pinned memory), which would make the
+// drop-in call several times slower than the same call on pinned buffers.  This file does the staging itself.
+//
+// Up (host -> device): a STREAM of copy jobs.  The caller submits every block it will need, in the order it will need
+// them, and gets a ticket per block; a team of host threads walks the blocks chunk by chunk (4 MB) without stopping at
+// block boundaries: copy the chunk of the caller's matrix into one of the thread's two pinned slots, queue the slot's DMA on
+// the copy stream, go on with the other slot.  staging_wait_submitted(ticket) returns once every chunk of every block up
+// to that ticket has been queued, i.e. an event recorded on the copy stream from then on covers them.  The first
+// version ran one blocking parallel-for per block and reached 30 GB/s (every block ramped the team up and down and
+// the caller could not look ahead); tools/stage_probe.cu measures what the host can do: one thread fills slots at
+// 11.5 GB/s, 6-8 threads with two 4 MB slots each sustain 50 GB/s through the whole fill -> DMA pipeline, any copy
+// routine (glibc memcpy, rep movsb, AVX-512 non-temporal: 50.6 / 50.4 / 51.5 GB/s; profiles/r02_stage_probe.jsonl).
+//
+// Down (device -> host): the mirror image, two DMAs in flight per thread (the next chunk's DMA is requested before
+// the previous one is copied out); 4 threads reach 40 GB/s, 8 reach 50 (same probe).
+//
+// No arithmetic happens here — the bytes are moved, never touched.
 #include "dgemm_host.h"
 
 #include <algorithm>
@@ -15,7 +27,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
-#include <functional>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -23,63 +35,10 @@
 namespace dg {
 namespace {
 
-constexpr size_t CHUNK_BYTES = 4u << 20;
-
-// fixed team of threads; parallel_for(n, fn) runs fn(worker, index) for index in [0, n) and returns when all are done
-class Pool {
- public:
-  explicit Pool(int n) : n_(n) {
-    for (int w = 0; w < n_; w++) threads_.emplace_back([this, w] { loop(w); });
-  }
-  ~Pool() {
-    {
-      std::lock_guard<std::mutex> lk(mu_);
-      stop_ = true;
-    }
-    cv_.notify_all();
-    for (auto& t : threads_) t.join();
-  }
-  int size() const { return n_; }
-  void parallel_for(int n, const std::function<void(int, int)>& fn) {
-    if (n <= 0) return;
-    std::unique_lock<std::mutex> lk(mu_);
-    fn_ = &fn;
-    total_ = n;
-    next_ = 0;
-    pending_ = n;
-    generation_++;
-    cv_.notify_all();
-    done_cv_.wait(lk, [this] { return pending_ == 0; });
-    fn_ = nullptr;
-  }
-
- private:
-  void loop(int w) {
-    unsigned long long seen = 0;
-    std::unique_lock<std::mutex> lk(mu_);
-    for (;;) {
-      cv_.wait(lk, [&] { return stop_ || (generation_ != seen && next_ < total_); });
-      if (stop_) return;
-      seen = generation_;
-      while (next_ < total_) {
-        const int i = next_++;
-        const std::function<void(int, int)>* fn = fn_;
-        lk.unlock();
-        (*fn)(w, i);
-        lk.lock();
-        if (--pending_ == 0) done_cv_.notify_all();
-      }
-    }
-  }
-  int n_;
-  std::vector<std::thread> threads_;
-  std::mutex mu_;
-  std::condition_variable cv_, done_cv_;
-  const std::function<void(int, int)>* fn_ = nullptr;
-  int total_ = 0, next_ = 0, pending_ = 0;
-  unsigned long long generation_ = 0;
-  bool stop_ = false;
-};
+constexpr size_t SLOT_BYTES = 4u << 20;   // size of a pinned slot = largest chunk
+// chunk size in use (DGEMM_B200_STAGE_CHUNK_KB, 64 ... 4096; read when the teams start)
+size_t g_chunk_bytes = SLOT_BYTES;
+#define CHUNK_BYTES g_chunk_bytes
 
 struct Slot {
   char* host = nullptr;
@@ -104,32 +63,196 @@ std::vector<Chunk> make_chunks(long long rows, long long cols) {
   return out;
 }
 
-struct Team {
-  Pool pool;
-  std::vector<Slot> slots;  // 2 per worker
-  int dev;
-  explicit Team(int n, int dev_) : pool(n), slots(2 * n), dev(dev_) {}
+struct Job {
+  double* dev_ptr = nullptr;     // device side
+  long long ldd = 0;
+  double* host_ptr = nullptr;    // caller's side (read for up, written for down)
+  long long ldh = 0;
+  long long rows = 0, cols = 0;
+  bool staged = true;            // false: pinned caller memory, one direct 2-D copy (up only)
+  cudaEvent_t ready = nullptr;   // down only: the device block is complete once this has fired
+  cudaStream_t stream = nullptr;
+  int dev = 0;
+  std::vector<Chunk> chunks;
+  size_t next = 0;               // first chunk nobody has taken yet
+  size_t remaining = 0;          // chunks not yet finished
+  std::atomic<bool> ready_seen{false};
 };
 
-struct D2HJob {
-  double* dst;
-  long long ldd;
-  const double* src;
-  long long lds, rows, cols;
-  cudaEvent_t ready;
-  cudaStream_t stream;
-  int dev;
+std::atomic<int> g_err{0};
+void note(cudaError_t e) {
+  if (e != cudaSuccess) {
+    int expected = 0;
+    g_err.compare_exchange_strong(expected, (int)e);
+  }
+}
+
+// FIFO of jobs handed out chunk by chunk to a fixed team of threads; jobs retire in submission order
+class Engine {
+ public:
+  Engine(int n, int dev, bool up) : n_(n), dev_(dev), up_(up), slots_(2 * n) {}
+  ~Engine() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+    }
+    work_cv_.notify_all();
+    for (auto& t : threads_) t.join();
+    for (Slot& s : slots_) {
+      if (s.host) cudaFreeHost(s.host);
+      if (s.done) cudaEventDestroy(s.done);
+    }
+  }
+  int dev() const { return dev_; }
+  cudaError_t start() {
+    for (Slot& s : slots_) {
+      if (s.host) continue;
+      cudaError_t e = cudaHostAlloc((void**)&s.host, SLOT_BYTES, cudaHostAllocPortable);
+      if (e != cudaSuccess) return e;
+      if ((e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+    if (threads_.empty())
+      for (int w = 0; w < n_; w++) threads_.emplace_back([this, w] { up_ ? loop_up(w) : loop_down(w); });
+    return cudaSuccess;
+  }
+  long long submit(std::unique_ptr<Job> j) {
+    j->remaining = j->chunks.size();
+    std::lock_guard<std::mutex> lk(mu_);
+    live_.push_back(std::move(j));
+    const long long ticket = base_ticket_ + (long long)live_.size() - 1;
+    work_cv_.notify_all();
+    return ticket;
+  }
+  void wait_retired(long long ticket) {
+    std::unique_lock<std::mutex> lk(mu_);
+    done_cv_.wait(lk, [&] { return base_ticket_ > ticket; });
+  }
+  void wait_idle() {
+    std::unique_lock<std::mutex> lk(mu_);
+    done_cv_.wait(lk, [&] { return live_.empty(); });
+  }
+
+ private:
+  // next chunk in FIFO order; block == false returns at once when there is none
+  bool take(bool block, Job** job, size_t* chunk) {
+    std::unique_lock<std::mutex> lk(mu_);
+    if (block) work_cv_.wait(lk, [&] { return stop_ || issue_ < live_.size(); });
+    if (issue_ >= live_.size()) return false;
+    Job* j = live_[issue_].get();
+    *job = j;
+    *chunk = j->next++;
+    if (j->next == j->chunks.size()) issue_++;
+    return true;
+  }
+  void finish(Job* j) {
+    std::lock_guard<std::mutex> lk(mu_);
+    if (--j->remaining != 0) return;
+    while (!live_.empty() && live_.front()->remaining == 0) {   // (a retiring job is fully issued: it sits before issue_)
+      live_.pop_front();
+      base_ticket_++;
+      issue_--;
+    }
+    done_cv_.notify_all();
+  }
+  bool stopping() {
+    std::lock_guard<std::mutex> lk(mu_);
+    return stop_;
+  }
+
+  void loop_up(int w) {
+    int turn = 0;
+    for (;;) {
+      Job* j;
+      size_t ci;
+      if (!take(true, &j, &ci)) {
+        if (stopping()) return;
+        continue;
+      }
+      cudaSetDevice(j->dev);
+      const Chunk& c = j->chunks[ci];
+      if (j->rows <= 0 || j->cols <= 0) {
+        // (an empty block: only there to keep the tickets dense)
+      } else if (!j->staged) {
+        note(cudaMemcpy2DAsync(j->dev_ptr, (size_t)j->ldd * 8, j->host_ptr, (size_t)j->ldh * 8, (size_t)j->rows * 8, (size_t)j->cols,
+                               cudaMemcpyHostToDevice, j->stream));
+      } else {
+        Slot& s = slots_[2 * w + (turn++ & 1)];
+        if (s.used) note(cudaEventSynchronize(s.done));  // the slot's previous DMA has read it
+        const double* src = j->host_ptr;
+        if (j->ldh == c.rows && c.row0 == 0)
+          memcpy(s.host, src + c.col0 * j->ldh, (size_t)c.rows * c.cols * 8);
+        else
+          for (long long cc = 0; cc < c.cols; cc++)
+            memcpy(s.host + (size_t)cc * c.rows * 8, src + (c.col0 + cc) * j->ldh + c.row0, (size_t)c.rows * 8);
+        if (j->ldd == c.rows && c.row0 == 0)
+          note(cudaMemcpyAsync(j->dev_ptr + c.col0 * j->ldd, s.host, (size_t)c.rows * c.cols * 8, cudaMemcpyHostToDevice, j->stream));
+        else
+          note(cudaMemcpy2DAsync(j->dev_ptr + c.col0 * j->ldd + c.row0, (size_t)j->ldd * 8, s.host, (size_t)c.rows * 8,
+                                 (size_t)c.rows * 8, (size_t)c.cols, cudaMemcpyHostToDevice, j->stream));
+        note(cudaEventRecord(s.done, j->stream));
+        s.used = true;
+      }
+      finish(j);
+    }
+  }
+
+  void loop_down(int w) {
+    struct Pending { Job* j; size_t ci; int slot; };
+    std::deque<Pending> pending;   // DMAs requested, not yet copied out (at most two: one per slot)
+    int turn = 0;
+    for (;;) {
+      while (pending.size() < 2) {
+        Job* j;
+        size_t ci;
+        if (!take(pending.empty(), &j, &ci)) break;
+        cudaSetDevice(j->dev);
+        if (!j->ready_seen.load(std::memory_order_acquire)) {   // the block is complete on the device
+          note(cudaEventSynchronize(j->ready));
+          j->ready_seen.store(true, std::memory_order_release);
+        }
+        const Chunk& c = j->chunks[ci];
+        const int k = 2 * w + (turn++ & 1);   // (the other slot is the pending one, or free)
+        Slot& s = slots_[k];
+        note(cudaMemcpy2DAsync(s.host, (size_t)c.rows * 8, j->dev_ptr + c.col0 * j->ldd + c.row0, (size_t)j->ldd * 8,
+                               (size_t)c.rows * 8, (size_t)c.cols, cudaMemcpyDeviceToHost, j->stream));
+        note(cudaEventRecord(s.done, j->stream));
+        pending.push_back({j, ci, k});
+      }
+      if (pending.empty()) {
+        if (stopping()) return;
+        continue;
+      }
+      const Pending p = pending.front();
+      pending.pop_front();
+      Slot& s = slots_[p.slot];
+      note(cudaEventSynchronize(s.done));
+      const Chunk& c = p.j->chunks[p.ci];
+      double* dst = p.j->host_ptr;
+      if (p.j->ldh == c.rows && c.row0 == 0)
+        memcpy(dst + c.col0 * p.j->ldh, s.host, (size_t)c.rows * c.cols * 8);
+      else
+        for (long long cc = 0; cc < c.cols; cc++)
+          memcpy(dst + (c.col0 + cc) * p.j->ldh + c.row0, s.host + (size_t)cc * c.rows * 8, (size_t)c.rows * 8);
+      finish(p.j);
+    }
+  }
+
+  const int n_, dev_;
+  const bool up_;
+  std::vector<Slot> slots_;   // two per thread
+  std::vector<std::thread> threads_;
+  std::mutex mu_;
+  std::condition_variable work_cv_, done_cv_;
+  std::deque<std::unique_ptr<Job>> live_;   // submitted, not yet retired, in ticket order
+  long long base_ticket_ = 0;               // ticket of live_.front()
+  size_t issue_ = 0;                        // index in live_ of the first job with chunks nobody has taken
+  bool stop_ = false;
 };
 
 struct State {
   std::mutex mu;
-  Team* up = nullptr;    // host -> device
-  Team* down = nullptr;  // device -> host
-  std::thread d2h_thread;
-  std::deque<D2HJob> jobs;
-  std::condition_variable job_cv, idle_cv;
-  bool busy = false, stop = false, started = false;
-  std::atomic<int> err{0};
+  Engine* up = nullptr;
+  Engine* down = nullptr;
 };
 State& state() {
   static State* s = new State;  // leaked on purpose: worker threads may outlive static destruction order
@@ -138,80 +261,29 @@ State& state() {
 
 int stage_threads() {
   if (const char* e = getenv("DGEMM_B200_STAGE_THREADS")) return std::max(1, std::min(32, atoi(e)));
-  // measured on this pool's 16-vCPU hosts at 8192^3: 2 threads 16.0, 4 threads 20.1, 8 threads 18.0, 12 threads 16.2
-  // TFLOP/s end to end (profiles/r01_e2e_pageable.jsonl) — a quarter of the hardware threads saturates the memory system
+  // tools/stage_probe.cu on this pool's 16-vCPU hosts: the fill -> DMA pipeline sustains 24 / 47 / 50.6 / 50.1 / 49 GB/s with
+  // 2 / 4 / 6 / 8 / 12 threads (4 MB slots, two per thread); the main thread and the four threads of the way back
+  // need cores too
   const unsigned hc = std::thread::hardware_concurrency();
-  return (int)std::max(2u, std::min(8u, hc / 4));
-}
-
-cudaError_t ensure_slots(Team& t) {
-  for (Slot& s : t.slots) {
-    if (s.host) continue;
-    cudaError_t e = cudaHostAlloc((void**)&s.host, CHUNK_BYTES, cudaHostAllocPortable);
-    if (e != cudaSuccess) return e;
-    if ((e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess) return e;
-  }
-  return cudaSuccess;
-}
-
-void note(cudaError_t e) {
-  if (e != cudaSuccess) {
-    int expected = 0;
-    state().err.compare_exchange_strong(expected, (int)e);
-  }
-}
-
-void run_d2h(Team& t, const D2HJob& j) {
-  cudaSetDevice(j.dev);
-  note(cudaEventSynchronize(j.ready));
-  const std::vector<Chunk> chunks = make_chunks(j.rows, j.cols);
-  std::vector<int> turn(t.pool.size(), 0);
-  t.pool.parallel_for((int)chunks.size(), [&](int w, int i) {
-    cudaSetDevice(j.dev);
-    const Chunk& c = chunks[i];
-    Slot& s = t.slots[2 * w + (turn[w]++ & 1)];
-    note(cudaMemcpy2DAsync(s.host, (size_t)c.rows * 8, j.src + c.col0 * j.lds + c.row0, (size_t)j.lds * 8,
-                           (size_t)c.rows * 8, (size_t)c.cols, cudaMemcpyDeviceToHost, j.stream));
-    note(cudaEventRecord(s.done, j.stream));
-    note(cudaEventSynchronize(s.done));
-    for (long long cc = 0; cc < c.cols; cc++)
-      memcpy(j.dst + (c.col0 + cc) * j.ldd + c.row0, s.host + (size_t)cc * c.rows * 8, (size_t)c.rows * 8);
-  });
-}
-
-void d2h_loop() {
-  State& st = state();
-  std::unique_lock<std::mutex> lk(st.mu);
-  for (;;) {
-    st.job_cv.wait(lk, [&] { return st.stop || !st.jobs.empty(); });
-    if (st.stop && st.jobs.empty()) return;
-    D2HJob j = st.jobs.front();
-    st.jobs.pop_front();
-    st.busy = true;
-    Team* t = st.down;
-    lk.unlock();
-    run_d2h(*t, j);
-    lk.lock();
-    st.busy = false;
-    if (st.jobs.empty()) st.idle_cv.notify_all();
-  }
+  return (int)std::max(2u, std::min(8u, hc / 2));
 }
 
 cudaError_t ensure_started(int dev) {
   State& st = state();
   std::lock_guard<std::mutex> lk(st.mu);
-  if (!st.started) {
+  if (!st.up) {
+    if (const char* e = getenv("DGEMM_B200_STAGE_CHUNK_KB"))
+      g_chunk_bytes = std::max<size_t>(64u << 10, std::min<size_t>(SLOT_BYTES, (size_t)atoll(e) << 10));
     const int n = stage_threads();
-    st.up = new Team(n, dev);
-    st.down = new Team(std::max(2, n / 2), dev);
-    st.stop = false;
-    st.d2h_thread = std::thread(d2h_loop);
-    st.started = true;
+    st.up = new Engine(n, dev, true);
+    st.down = new Engine(std::max(2, n / 2), dev, false);
   }
-  cudaError_t e = ensure_slots(*st.up);
-  if (e == cudaSuccess) e = ensure_slots(*st.down);
+  cudaError_t e = st.up->start();
+  if (e == cudaSuccess) e = st.down->start();
   return e;
 }
+
+cudaError_t take_error() { return (cudaError_t)g_err.exchange(0); }
 
 }  // namespace
 
@@ -219,7 +291,7 @@ cudaError_t ensure_started(int dev) {
 bool staging_usable(int dev) {
   State& st = state();
   std::lock_guard<std::mutex> lk(st.mu);
-  return !st.started || st.up->dev == dev;
+  return !st.up || st.up->dev() == dev;
 }
 
 bool host_pointer_is_pageable(const void* p) {
@@ -232,79 +304,78 @@ bool host_pointer_is_pageable(const void* p) {
   return a.type == cudaMemoryTypeUnregistered;
 }
 
-// Blocking: returns once the DMA of every chunk has been queued on `stream` (so an event recorded on `stream` after
+// Queues one block for the team (host -> device) and returns its ticket at once (< 0: error, see *err).  pageable: the
+// block goes through the pinned slots; otherwise (pinned caller memory) it is one direct copy, kept in the same queue so
+// that the copy stream sees all blocks in submission order.
+long long staging_submit_h2d(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
+                             cudaStream_t stream, int dev, bool pageable, cudaError_t* err) {
+  *err = ensure_started(dev);
+  if (*err != cudaSuccess) return -1;
+  std::unique_ptr<Job> j(new Job);
+  j->dev_ptr = dst; j->ldd = ldd; j->host_ptr = const_cast<double*>(src); j->ldh = lds; j->rows = rows; j->cols = cols;
+  j->staged = pageable; j->stream = stream; j->dev = dev;
+  if (rows > 0 && cols > 0) {
+    if (pageable) j->chunks = make_chunks(rows, cols);
+    else j->chunks.push_back({0, rows, 0, cols});
+  }
+  if (j->chunks.empty()) j->chunks.push_back({0, 0, 0, 0}), j->staged = false, j->rows = j->cols = 0;   // keeps tickets dense
+  return state().up->submit(std::move(j));
+}
+
+// returns once every chunk of every block up to `ticket` has been queued on its stream
+cudaError_t staging_wait_submitted(long long ticket) {
+  State& st = state();
+  if (!st.up || ticket < 0) return cudaSuccess;
+  st.up->wait_retired(ticket);
+  return take_error();
+}
+
+// Blocking form: returns once the DMA of every chunk has been queued on `stream` (so an event recorded on `stream` after
 // this call covers the whole block).  `src` is pageable host memory, `dst` device memory.
 cudaError_t staged_h2d(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
                        cudaStream_t stream, int dev) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
-  cudaError_t e = ensure_started(dev);
-  if (e != cudaSuccess) return e;
-  State& st = state();
-  Team& t = *st.up;
-  const std::vector<Chunk> chunks = make_chunks(rows, cols);
-  std::vector<int> turn(t.pool.size(), 0);
-  t.pool.parallel_for((int)chunks.size(), [&](int w, int i) {
-    cudaSetDevice(dev);
-    const Chunk& c = chunks[i];
-    Slot& s = t.slots[2 * w + (turn[w]++ & 1)];
-    if (s.used) note(cudaEventSynchronize(s.done));  // the slot's previous DMA has read it
-    if (lds == c.rows && c.row0 == 0)
-      memcpy(s.host, src + c.col0 * lds, (size_t)c.rows * c.cols * 8);
-    else
-      for (long long cc = 0; cc < c.cols; cc++)
-        memcpy(s.host + (size_t)cc * c.rows * 8, src + (c.col0 + cc) * lds + c.row0, (size_t)c.rows * 8);
-    note(cudaMemcpy2DAsync(dst + c.col0 * ldd + c.row0, (size_t)ldd * 8, s.host, (size_t)c.rows * 8, (size_t)c.rows * 8,
-                           (size_t)c.cols, cudaMemcpyHostToDevice, stream));
-    note(cudaEventRecord(s.done, stream));
-    s.used = true;
-  });
-  const int err = st.err.exchange(0);
-  return (cudaError_t)err;
+  cudaError_t e;
+  const long long t = staging_submit_h2d(dst, ldd, src, lds, rows, cols, stream, dev, true, &e);
+  if (t < 0) return e;
+  return staging_wait_submitted(t);
 }
 
-// Asynchronous: once `ready` has fired, the block is copied device -> pinned slots -> `dst` (pageable) by the D2H team.
+// Asynchronous: once `ready` has fired, the block is copied device -> pinned slots -> `dst` (pageable) by the down team.
 // staged_d2h_wait() returns when every queued block has reached the caller's memory.
 cudaError_t staged_d2h_async(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
                              cudaEvent_t ready, cudaStream_t stream, int dev) {
   if (rows <= 0 || cols <= 0) return cudaSuccess;
   cudaError_t e = ensure_started(dev);
   if (e != cudaSuccess) return e;
-  State& st = state();
-  {
-    std::lock_guard<std::mutex> lk(st.mu);
-    st.jobs.push_back({dst, ldd, src, lds, rows, cols, ready, stream, dev});
-  }
-  st.job_cv.notify_one();
+  std::unique_ptr<Job> j(new Job);
+  j->dev_ptr = const_cast<double*>(src); j->ldd = lds; j->host_ptr = dst; j->ldh = ldd; j->rows = rows; j->cols = cols;
+  j->ready = ready; j->stream = stream; j->dev = dev;
+  j->chunks = make_chunks(rows, cols);
+  state().down->submit(std::move(j));
   return cudaSuccess;
 }
 
 cudaError_t staged_d2h_wait() {
   State& st = state();
-  if (!st.started) return cudaSuccess;
-  std::unique_lock<std::mutex> lk(st.mu);
-  st.idle_cv.wait(lk, [&] { return st.jobs.empty() && !st.busy; });
-  const int err = st.err.exchange(0);
-  return (cudaError_t)err;
+  if (!st.down) return cudaSuccess;
+  st.down->wait_idle();
+  return take_error();
+}
+
+// (error paths: nothing of the caller's memory may still be read by the up team when the call returns)
+void staging_drain() {
+  State& st = state();
+  if (st.up) st.up->wait_idle();
+  if (st.down) st.down->wait_idle();
 }
 
 void staging_shutdown() {
   State& st = state();
-  {
-    std::lock_guard<std::mutex> lk(st.mu);
-    if (!st.started) return;
-    st.stop = true;
-  }
-  st.job_cv.notify_all();
-  st.d2h_thread.join();
-  for (Team* t : {st.up, st.down}) {
-    for (Slot& s : t->slots) {
-      if (s.host) cudaFreeHost(s.host);
-      if (s.done) cudaEventDestroy(s.done);
-    }
-    delete t;
-  }
+  std::lock_guard<std::mutex> lk(st.mu);
+  delete st.up;
+  delete st.down;
   st.up = st.down = nullptr;
-  st.started = false;
 }
 
 }  // namespace dg

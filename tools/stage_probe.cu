@@ -166,6 +166,7 @@ int main(int argc, char** argv) {
   for (const Method& m : methods)
     for (int T : {2, 4, 8}) {
       if ((unsigned)T > hc) continue;
+      if (m.fn == copy_nt512 || m.fn == copy_nt512_prefetch) continue;   // (their 64-byte stores need an aligned destination)
       const size_t S = 4u << 20, chunks = total / S;
       std::atomic<size_t> next{0};
       cudaDeviceSynchronize();
