@@ -201,6 +201,10 @@ int dgemm_b200_debug_timeline(unsigned long long *dbuf);
  * launches, on a stream of its own, `ctas` CTAs that each hold `smem_bytes` of shared memory for `ms` milliseconds
  * (<= 5000) and returns at once.  A DGEMM issued while they run must still finish with the right result. */
 int dgemm_b200_debug_occupy_sms(int ctas, unsigned smem_bytes, double ms);
+/* measurement aid: microseconds an EMPTY kernel of the given launch shape takes when timed the way dgemm_b200_time_device
+ * times a DGEMM (event, launch, event, synchronise).  flags: 1 cooperative launch, 2 programmatic-dependent-launch
+ * attribute, 4 with 512 bytes of kernel parameters.  < 0 on failure. */
+double dgemm_b200_debug_launch_floor(int ctas, int threads, unsigned smem_bytes, int flags, int reps);
 /* number of kernels this library has launched since the last reset (bench.py's gpu_launches) */
 int dgemm_b200_launch_count(void);
 void dgemm_b200_reset_launch_count(void);

@@ -35,7 +35,7 @@ EXPORTS = [
     "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
-    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_host_plan", "dgemm_b200_host_blocking",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_debug_launch_floor", "dgemm_b200_host_plan", "dgemm_b200_host_blocking",
     "dgemm_b200_device_bytes",
     "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled", "dgemm_b200_rank_pipeline",
     "dgemm_b200_exchange_bytes", "dgemm_b200_exchange_alloc", "dgemm_b200_rank_plan", "dgemm_b200_reload_env",
@@ -107,6 +107,8 @@ lib.dgemm_b200_fill_signed.argtypes = [_vp, C.c_int, C.c_int, _ll, C.c_ulonglong
 lib.dgemm_b200_time_device.argtypes = _DEV_ARGS + [C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t]
 lib.dgemm_b200_time_device.restype = C.c_double
 lib.dgemm_b200_debug_timeline.argtypes = [_vp]
+lib.dgemm_b200_debug_launch_floor.restype = C.c_double
+lib.dgemm_b200_debug_launch_floor.argtypes = [C.c_int, C.c_int, C.c_uint, C.c_int, C.c_int]
 lib.dgemm_b200_host_blocking.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_int),
                                          C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double)]
 lib.dgemm_b200_device_bytes.restype = C.c_size_t

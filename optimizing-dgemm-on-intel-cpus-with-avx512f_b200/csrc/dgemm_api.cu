@@ -5,8 +5,10 @@
 #include "../../include/dgemm_b200.h"
 #include "dgemm_device.cuh"
 #include "dgemm_host.h"
+#include "dgemm_launch.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -73,6 +75,7 @@ struct Env {
   bool no_tmap_cache = false;           // DGEMM_B200_NO_TMAP_CACHE
   bool no_pdl = false;                  // DGEMM_B200_NO_PDL
   double flag_timeout_ms = 20000.0;     // DGEMM_B200_FLAG_TIMEOUT_MS: bound of the multi-GPU layer's wait for a peer's upload
+  bool host_trace = false;              // DGEMM_B200_HOST_TRACE: run_host_incore prints host-side timestamps of one call to stderr
   double hbm_budget = 0.0;              // DGEMM_B200_HBM_BUDGET (bytes; 0 = 90 % of the free HBM): out-of-core threshold
   void load() {
     *this = Env();
@@ -105,6 +108,7 @@ struct Env {
     no_tmap_cache = has("DGEMM_B200_NO_TMAP_CACHE");
     no_pdl = has("DGEMM_B200_NO_PDL");
     hbm_budget = getd("DGEMM_B200_HBM_BUDGET", 0.0);
+    host_trace = has("DGEMM_B200_HOST_TRACE");
     flag_timeout_ms = std::max(1.0, getd("DGEMM_B200_FLAG_TIMEOUT_MS", flag_timeout_ms));
   }
 };
@@ -674,6 +678,11 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
   std::vector<long long> t_pre(order.size(), -1), t_post(order.size(), -1);
   std::vector<char> first_done(P, 0);
   int result = DGEMM_B200_OK;
+  const bool trace = env().host_trace;
+  const auto t_start = std::chrono::steady_clock::now();
+  auto since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count(); };
+  std::vector<double> t_ready(trace ? order.size() : 0);
+  double t_submitted = 0.0, t_issued = 0.0, t_d2h = 0.0, t_end = 0.0;
   auto body = [&]() -> int {
     if (streamed) {
       long long last = -1;
@@ -688,6 +697,7 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
         }
       }
     }
+    if (trace) t_submitted = since();
     auto issue = [&](const std::vector<Copy>& list, long long ticket) -> cudaError_t {
       if (streamed) return dg::staging_wait_submitted(ticket);
       for (const Copy& q : list) {
@@ -703,6 +713,7 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
       const int k0 = kb[sI], kc = need_ab ? kb[sE] - kb[sI] : K;
       const bool defer = pI < deferred;
       CU_TRY(issue(pre[i], t_pre[i]));
+      if (trace) t_ready[i] = since();
       CU_TRY(cudaEventRecord(ev_in[i], c.s_h2d));
       CU_TRY(cudaStreamWaitEvent(c.s_compute, ev_in[i], 0));
       int s2 = run_device(c, M, ncol, kc, alpha, c.a.p + (size_t)k0 * ldaD, ldaD, c.b.p + (size_t)n0 * ldbD + k0, ldbD,
@@ -729,10 +740,20 @@ int run_host_incore(int dev, int M, int N, int K, double alpha, const double* A,
         }
       }
     }
+    if (trace) t_issued = since();
     if (pc) CU_TRY(dg::staged_d2h_wait());
+    if (trace) t_d2h = since();
     CU_TRY(cudaStreamSynchronize(c.s_d2h));
     CU_TRY(cudaStreamSynchronize(c.s_compute));
     CU_TRY(cudaStreamSynchronize(c.s_h2d));
+    if (trace) {
+      t_end = since();
+      fprintf(stderr, "{\"host_trace_ms\": {\"M\": %d, \"N\": %d, \"K\": %d, \"streamed\": %d, \"submitted\": %.3f, \"call_blocks_queued\": [",
+              M, N, K, (int)streamed, t_submitted);
+      for (size_t i = 0; i < t_ready.size(); i++) fprintf(stderr, "%s%.3f", i ? ", " : "", t_ready[i]);
+      fprintf(stderr, "], \"all_calls_issued\": %.3f, \"staged_d2h_done\": %.3f, \"end\": %.3f}}\n", t_issued, t_d2h, t_end);
+      if (streamed) dg::staging_trace_dump(std::chrono::duration<double, std::milli>(t_start.time_since_epoch()).count());
+    }
     return DGEMM_B200_OK;
   };
   result = body();
@@ -1404,6 +1425,52 @@ int dgemm_b200_debug_occupy_sms(int ctas, unsigned smem_bytes, double ms) {
   cudaStreamDestroy(s);   // released by the runtime once the kernel has finished
   if (e != cudaSuccess) return fail(DGEMM_B200_ERR_CUDA, "debug_occupy_sms: %s", cudaGetErrorString(e));
   return DGEMM_B200_OK;
+}
+
+// measurement aid: what does the timing method itself cost?  An empty kernel with the given launch shape, timed exactly like
+// dgemm_b200_time_device times a DGEMM (event, launch, event, synchronise; average over reps).  flags: 1 = cooperative launch,
+// 2 = programmatic-dependent-launch attribute, 4 = 512 bytes of kernel parameters (two tensor maps + Params are about that)
+struct BigParams { unsigned long long v[64]; };
+__global__ void empty_kernel_small(int* sink) {
+  extern __shared__ unsigned char sm_empty[];
+  if (sink && threadIdx.x == 0x7fffffff) sink[0] = sm_empty[0];
+}
+__global__ void empty_kernel_big(const __grid_constant__ BigParams p, int* sink) {
+  extern __shared__ unsigned char sm_empty[];
+  if (sink && threadIdx.x == 0x7fffffff) sink[0] = sm_empty[0] + (int)p.v[5];
+}
+double dgemm_b200_debug_launch_floor(int ctas, int threads, unsigned smem_bytes, int flags, int reps) {
+  std::lock_guard<std::recursive_mutex> lk(g_mu);
+  DeviceCtx* c;
+  if (current_ctx(&c)) return -1.0;
+  if (ctas <= 0 || threads <= 0 || threads > 1024 || reps <= 0) return -1.0;
+  if (cudaFuncSetAttribute(empty_kernel_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes) != cudaSuccess ||
+      cudaFuncSetAttribute(empty_kernel_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes) != cudaSuccess) {
+    cudaGetLastError();
+    return -1.0;
+  }
+  dg::LaunchCfg cfg;
+  cfg.grid = ctas; cfg.threads = threads; cfg.smem = (int)smem_bytes; cfg.stream = c->s_compute;
+  cfg.cooperative = (flags & 1) != 0; cfg.pdl = (flags & 2) != 0;
+  cudaEvent_t e0, e1;
+  if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return -1.0;
+  BigParams bp = {};
+  int* sink = nullptr;
+  double total = 0.0;
+  bool bad = false;
+  for (int i = -3; i < reps && !bad; i++) {
+    cudaEventRecord(e0, cfg.stream);
+    cudaError_t e = (flags & 4) ? dg::launch_ex(empty_kernel_big, cfg, bp, sink) : dg::launch_ex(empty_kernel_small, cfg, sink);
+    cudaEventRecord(e1, cfg.stream);
+    if (e != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) bad = true;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (i >= 0) total += ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (bad) { cudaGetLastError(); return -1.0; }
+  return total / reps * 1e3;   // microseconds
 }
 
 size_t dgemm_b200_device_bytes(void) {

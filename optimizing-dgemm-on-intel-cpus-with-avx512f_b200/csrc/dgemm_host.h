@@ -132,6 +132,7 @@ cudaError_t staged_d2h_wait();
 long long staging_submit_h2d(double* dst, long long ldd, const double* src, long long lds, long long rows, long long cols,
                              cudaStream_t stream, int dev, bool pageable, cudaError_t* err);
 cudaError_t staging_wait_submitted(long long ticket);
+void staging_trace_dump(double t0_ms);   // DGEMM_B200_HOST_TRACE
 void staging_drain();   // returns when neither team holds a block any more (error paths)
 void staging_shutdown();
 

@@ -16,13 +16,16 @@
 // routine (glibc memcpy, rep movsb, AVX-512 non-temporal: 50.6 / 50.4 / 51.5 GB/s; profiles/r02_stage_probe.jsonl).
 //
 // Down (device -> host): the mirror image, two DMAs in flight per thread (the next chunk's DMA is requested before
-// the previous one is copied out); 4 threads reach 40 GB/s, 8 reach 50 (same probe).
+// the previous one is copied out); 4 threads reach 40 GB/s, 8 reach 50 (same probe).  A block becomes visible to the
+// team when a host function queued behind its last kernel has run; until then the threads sleep.
 //
 // No arithmetic happens here — the bytes are moved, never touched.
 #include "dgemm_host.h"
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <condition_variable>
 #include <cstdlib>
 #include <cstring>
@@ -50,9 +53,9 @@ struct Chunk {
   long long row0, rows, col0, cols;
 };
 
-std::vector<Chunk> make_chunks(long long rows, long long cols) {
+std::vector<Chunk> make_chunks(long long rows, long long cols, size_t chunk_bytes) {
   std::vector<Chunk> out;
-  const long long max_elems = CHUNK_BYTES / 8;
+  const long long max_elems = chunk_bytes / 8;
   if (rows <= max_elems) {
     const long long cpc = std::max(1ll, max_elems / rows);
     for (long long c = 0; c < cols; c += cpc) out.push_back({0, rows, c, std::min(cpc, cols - c)});
@@ -76,8 +79,19 @@ struct Job {
   std::vector<Chunk> chunks;
   size_t next = 0;               // first chunk nobody has taken yet
   size_t remaining = 0;          // chunks not yet finished
-  std::atomic<bool> ready_seen{false};
+  std::atomic<bool> is_ready{false};  // down only
+  double t_submit = 0.0, t_ready = 0.0, t_first = 0.0;   // trace
 };
+
+// DGEMM_B200_HOST_TRACE: when each block of the way back became ready / was taken first / was retired, and when each
+// block of the way up was retired (steady-clock milliseconds; staging_trace_dump prints and clears them)
+bool g_trace = false;
+std::mutex g_trace_mu;
+struct TraceRow { char dir; long long bytes; double t_submit, t_ready, t_first, t_done; };
+std::vector<TraceRow> g_trace_rows;
+double trace_now() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 std::atomic<int> g_err{0};
 void note(cudaError_t e) {
@@ -102,6 +116,7 @@ class Engine {
       if (s.host) cudaFreeHost(s.host);
       if (s.done) cudaEventDestroy(s.done);
     }
+    if (sig_) cudaStreamDestroy(sig_);
   }
   int dev() const { return dev_; }
   cudaError_t start() {
@@ -117,6 +132,7 @@ class Engine {
   }
   long long submit(std::unique_ptr<Job> j) {
     j->remaining = j->chunks.size();
+    if (g_trace) j->t_submit = trace_now();
     std::lock_guard<std::mutex> lk(mu_);
     live_.push_back(std::move(j));
     const long long ticket = base_ticket_ + (long long)live_.size() - 1;
@@ -127,19 +143,33 @@ class Engine {
     std::unique_lock<std::mutex> lk(mu_);
     done_cv_.wait(lk, [&] { return base_ticket_ > ticket; });
   }
+  void mark_ready(Job* j) {   // (called from a CUDA host function: no CUDA calls in here)
+    std::lock_guard<std::mutex> lk(mu_);
+    j->is_ready.store(true, std::memory_order_release);
+    if (g_trace) j->t_ready = trace_now();
+    work_cv_.notify_all();
+  }
+  cudaStream_t signal_stream() {
+    if (!sig_) cudaStreamCreateWithFlags(&sig_, cudaStreamNonBlocking);
+    return sig_;
+  }
   void wait_idle() {
     std::unique_lock<std::mutex> lk(mu_);
     done_cv_.wait(lk, [&] { return live_.empty(); });
   }
 
  private:
-  // next chunk in FIFO order; block == false returns at once when there is none
+  // next chunk in FIFO order; block == false returns at once when there is none.  Way back: a block can only be taken
+  // once it is complete on the device (Job::is_ready, set by a host function queued behind the block's last kernel), so no
+  // thread ever waits for the GPU while it still holds a chunk it could copy out, and nobody spins.
   bool take(bool block, Job** job, size_t* chunk) {
     std::unique_lock<std::mutex> lk(mu_);
-    if (block) work_cv_.wait(lk, [&] { return stop_ || issue_ < live_.size(); });
-    if (issue_ >= live_.size()) return false;
+    auto avail = [&] { return issue_ < live_.size() && (up_ || live_[issue_]->is_ready.load(std::memory_order_acquire)); };
+    if (block) work_cv_.wait(lk, [&] { return stop_ || avail(); });
+    if (!avail()) return false;
     Job* j = live_[issue_].get();
     *job = j;
+    if (g_trace && j->next == 0) j->t_first = trace_now();
     *chunk = j->next++;
     if (j->next == j->chunks.size()) issue_++;
     return true;
@@ -148,6 +178,11 @@ class Engine {
     std::lock_guard<std::mutex> lk(mu_);
     if (--j->remaining != 0) return;
     while (!live_.empty() && live_.front()->remaining == 0) {   // (a retiring job is fully issued: it sits before issue_)
+      if (g_trace) {
+        const Job& f = *live_.front();
+        std::lock_guard<std::mutex> tl(g_trace_mu);
+        g_trace_rows.push_back({up_ ? 'u' : 'd', f.rows * f.cols * 8, f.t_submit, f.t_ready, f.t_first, trace_now()});
+      }
       live_.pop_front();
       base_ticket_++;
       issue_--;
@@ -206,10 +241,6 @@ class Engine {
         size_t ci;
         if (!take(pending.empty(), &j, &ci)) break;
         cudaSetDevice(j->dev);
-        if (!j->ready_seen.load(std::memory_order_acquire)) {   // the block is complete on the device
-          note(cudaEventSynchronize(j->ready));
-          j->ready_seen.store(true, std::memory_order_release);
-        }
         const Chunk& c = j->chunks[ci];
         const int k = 2 * w + (turn++ & 1);   // (the other slot is the pending one, or free)
         Slot& s = slots_[k];
@@ -247,6 +278,7 @@ class Engine {
   long long base_ticket_ = 0;               // ticket of live_.front()
   size_t issue_ = 0;                        // index in live_ of the first job with chunks nobody has taken
   bool stop_ = false;
+  cudaStream_t sig_ = nullptr;              // way back: carries the "block is complete" host functions
 };
 
 struct State {
@@ -272,11 +304,12 @@ cudaError_t ensure_started(int dev) {
   State& st = state();
   std::lock_guard<std::mutex> lk(st.mu);
   if (!st.up) {
+    g_trace = getenv("DGEMM_B200_HOST_TRACE") != nullptr;
     if (const char* e = getenv("DGEMM_B200_STAGE_CHUNK_KB"))
       g_chunk_bytes = std::max<size_t>(64u << 10, std::min<size_t>(SLOT_BYTES, (size_t)atoll(e) << 10));
     const int n = stage_threads();
     st.up = new Engine(n, dev, true);
-    st.down = new Engine(std::max(2, n / 2), dev, false);
+    st.down = new Engine(n, dev, false);   // (asleep unless a finished block is waiting; see Engine::take)
   }
   cudaError_t e = st.up->start();
   if (e == cudaSuccess) e = st.down->start();
@@ -315,7 +348,7 @@ long long staging_submit_h2d(double* dst, long long ldd, const double* src, long
   j->dev_ptr = dst; j->ldd = ldd; j->host_ptr = const_cast<double*>(src); j->ldh = lds; j->rows = rows; j->cols = cols;
   j->staged = pageable; j->stream = stream; j->dev = dev;
   if (rows > 0 && cols > 0) {
-    if (pageable) j->chunks = make_chunks(rows, cols);
+    if (pageable) j->chunks = make_chunks(rows, cols, CHUNK_BYTES);
     else j->chunks.push_back({0, rows, 0, cols});
   }
   if (j->chunks.empty()) j->chunks.push_back({0, 0, 0, 0}), j->staged = false, j->rows = j->cols = 0;   // keeps tickets dense
@@ -351,8 +384,26 @@ cudaError_t staged_d2h_async(double* dst, long long ldd, const double* src, long
   std::unique_ptr<Job> j(new Job);
   j->dev_ptr = const_cast<double*>(src); j->ldd = lds; j->host_ptr = dst; j->ldh = ldd; j->rows = rows; j->cols = cols;
   j->ready = ready; j->stream = stream; j->dev = dev;
-  j->chunks = make_chunks(rows, cols);
-  state().down->submit(std::move(j));
+  // (1 MB chunks on the way back: a C panel of a mid-size call is a few MB, and all threads of the team should get a part)
+  j->chunks = make_chunks(rows, cols, std::min<size_t>(CHUNK_BYTES, 1u << 20));
+  Engine* down = state().down;
+  Job* raw = j.get();
+  down->submit(std::move(j));   // (alive until its last chunk has been copied out, which needs is_ready first)
+  struct Signal { Engine* e; Job* j; };
+  Signal* sg = new Signal{down, raw};
+  cudaStream_t sig = down->signal_stream();
+  e = cudaStreamWaitEvent(sig, ready, 0);
+  if (e == cudaSuccess)
+    e = cudaLaunchHostFunc(sig, [](void* p) {
+      Signal* s = static_cast<Signal*>(p);
+      s->e->mark_ready(s->j);
+      delete s;
+    }, sg);
+  if (e != cudaSuccess) {   // cannot be signalled: release the block now, the DMA itself is ordered behind `ready` below
+    cudaStreamWaitEvent(stream, ready, 0);
+    down->mark_ready(raw);
+    delete sg;
+  }
   return cudaSuccess;
 }
 
@@ -361,6 +412,17 @@ cudaError_t staged_d2h_wait() {
   if (!st.down) return cudaSuccess;
   st.down->wait_idle();
   return take_error();
+}
+
+// DGEMM_B200_HOST_TRACE: one line per block since the last dump, times in ms relative to t0_ms (a steady-clock reading)
+void staging_trace_dump(double t0_ms) {
+  if (!g_trace) return;
+  std::lock_guard<std::mutex> tl(g_trace_mu);
+  for (const TraceRow& r : g_trace_rows)
+    fprintf(stderr, "{\"staging_block\": \"%s\", \"mb\": %.2f, \"submitted\": %.3f, \"ready\": %.3f, \"first_chunk_taken\": %.3f, \"retired\": %.3f}\n",
+            r.dir == 'u' ? "up" : "down", r.bytes / 1048576.0, r.t_submit - t0_ms, r.t_ready > 0 ? r.t_ready - t0_ms : -1.0,
+            r.t_first - t0_ms, r.t_done - t0_ms);
+  g_trace_rows.clear();
 }
 
 // (error paths: nothing of the caller's memory may still be read by the up team when the call returns)

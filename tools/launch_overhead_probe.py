@@ -43,3 +43,17 @@ for n in (256, 512):
     run(f"{n}^3 beta = 0", n, n, n, beta=0.0)
     run(f"{n}^3 big tile data-parallel (splits=1)", n, n, n, variant=1, splits=1)
     run(f"{n}^3 cp.async kernel auto split", n, n, n, variant=3, splits=0)
+
+# ---- what the timing method costs for an EMPTY kernel, by launch shape (dgemm_b200_debug_launch_floor)
+for label, ctas, threads, smem, flags in [
+        ("empty kernel <<<1, 32>>>", 1, 32, 0, 0),
+        ("empty kernel <<<148, 384>>>", 148, 384, 0, 0),
+        ("empty kernel <<<148, 384, 199 KB>>> (the 128x128 kernel's shape)", 148, 384, 199 * 1024, 0),
+        ("empty kernel <<<148, 384, 132 KB>>> (dg64)", 148, 384, 132 * 1024, 0),
+        ("empty kernel <<<296, 384, 66 KB>>> (dg64x2)", 296, 384, 66 * 1024, 0),
+        ("empty kernel <<<148, 384, 199 KB>>> + 512 B of parameters", 148, 384, 199 * 1024, 4),
+        ("empty kernel <<<148, 384, 199 KB>>> + PDL attribute", 148, 384, 199 * 1024, 2),
+        ("empty kernel <<<148, 384, 199 KB>>> cooperative", 148, 384, 199 * 1024, 1),
+        ("empty kernel <<<128, 128, 48 KB>>> (a light data-parallel kernel)", 128, 128, 48 * 1024, 0)]:
+    us = dg.lib.dgemm_b200_debug_launch_floor(ctas, threads, smem, flags, 50)
+    print(json.dumps({"what": label, "ctas": ctas, "threads": threads, "smem": smem, "flags": flags, "us": round(us, 2)}), flush=True)
