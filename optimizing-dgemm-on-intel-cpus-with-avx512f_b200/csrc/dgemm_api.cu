@@ -57,7 +57,10 @@ struct Env {
   int max_gpus = 0;                     // DGEMM_B200_MAX_GPUS (0 = all)
   int odd_ld = 0;                       // DGEMM_B200_ODD_LD / DGEMM_B200_NO_REALIGN: ODD_SPLIT / ODD_REALIGN / ODD_CPASYNC
   bool no_small_tile = false;           // DGEMM_B200_NO_SMALL_TILE
-  int small_ctas = 2;                   // DGEMM_B200_SMALL_CTAS: 1 = the one-CTA-per-SM build of the 64 x 64 kernel, 2 = dg64x2
+  // DGEMM_B200_SMALL_CTAS: 1 = the one-CTA-per-SM build of the 64 x 64 kernel (default), 2 = dg64x2.  Measured on one box
+  // (profiles/r02_small_tile_probe_one_vs_two_ctas.jsonl): two CTAs per SM are never faster -- 512^3 10.6 vs 11.9, 1024^3
+  // 27.4 vs 27.8, 1000x1003x997 24.7 vs 25.1 TFLOP/s -- because the co-resident CTAs start, switch tiles and finish together
+  int small_ctas = 1;
   long long small_max_tiles = 64;       // DGEMM_B200_SMALL_TILE_MAX_TILES
   double small_max_flops = 4e9;         // DGEMM_B200_SMALL_TILE_MAX_FLOPS
   bool no_lockstep = false;             // DGEMM_B200_NO_LOCKSTEP
@@ -88,7 +91,7 @@ struct Env {
     if (has("DGEMM_B200_NO_REALIGN") || (o && !strcmp(o, "cpasync"))) odd_ld = 2;
     else odd_ld = (o && !strcmp(o, "realign")) ? 1 : 0;
     no_small_tile = has("DGEMM_B200_NO_SMALL_TILE");
-    small_ctas = geti("DGEMM_B200_SMALL_CTAS", 2) == 1 ? 1 : 2;
+    small_ctas = geti("DGEMM_B200_SMALL_CTAS", 1) == 2 ? 2 : 1;
     if (const char* e = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) small_max_tiles = atoll(e);
     small_max_flops = getd("DGEMM_B200_SMALL_TILE_MAX_FLOPS", small_max_flops);
     no_lockstep = has("DGEMM_B200_NO_LOCKSTEP");

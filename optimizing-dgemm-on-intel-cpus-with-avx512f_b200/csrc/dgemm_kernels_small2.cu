@@ -11,8 +11,13 @@
 // 40 (producer warpgroup) / 96 (consumers: 32 accumulator registers + two fragment sets; the DMMA loop compiles without
 // local-memory traffic, with 24 / 104 it has two LDL per k-tile); 4 stages x 16 KB = 65 KB of
 // shared memory, so two CTAs hold the same 128 KB of operands in flight per SM as the one-CTA build.
-// run_device sizes the grid and the stream-K ranges for 2 x #SMs CTA slots (DGEMM_B200_SMALL_CTAS=1 selects the
-// one-CTA build).  The reference has no counterpart (one thread per core, kernel19.h:678-755).
+// run_device sizes the grid and the stream-K ranges for 2 x #SMs CTA slots when DGEMM_B200_SMALL_CTAS=2 selects this build.
+//
+// RESULT (profiles/r02_small_tile_probe_one_vs_two_ctas.jsonl, r02_timelines_small_tile_one_vs_two_ctas.txt,
+// r02_ncu_full_dg64x2_1024.json): never faster than the one-CTA build -- 512^3 10.6 vs 11.9 TFLOP/s, 1024^3 27.4 vs 27.8,
+// 1000x1003x997 24.7 vs 25.1, 2048^3 32.8 vs 33.2.  The two CTAs of an SM are launched together, reach their tile switches
+// and their fix-up together and finish together, so there is little for one to overlap with in the other; the DMMA pipe
+// is busy 76 % of the elapsed cycles (83 % of the active ones), as before.  Kept selectable, not the default.  The reference has no counterpart (one thread per core, kernel19.h:678-755).
 #define DG_NAMESPACE dg64x2
 #define DG_SMALL_STAGES 4
 #define DG_MIN_CTAS 2

@@ -238,6 +238,34 @@ def test_waiting_kernels_survive_a_busy_device(dg, monkeypatch, no_wait, splits)
         dg.reload_env()
 
 
+@pytest.mark.parametrize("case", [((256, 256, 256), (0, 0, 0), 1.0, 1.0), ((512, 512, 512), (0, 0, 0), 2.5, 0.5),
+                                  ((1000, 1003, 997), (0, 0, 0), -1.0, 1.0),      # odd LDB: parity-split kernel of the build
+                                  ((1000, 1003, 997), (7, 7, 7), 1.5, 0.0),       # odd LDA
+                                  ((1024, 1024, 1024), (0, 0, 0), 1.0, 1.0), ((300, 700, 64), (2, 0, 0), 1.0, 1.0)])
+def test_small_tile_build_at_two_ctas_per_sm(dg, monkeypatch, case):
+    """DGEMM_B200_SMALL_CTAS=2: the 64 x 64 kernel compiled for two resident CTAs per SM (csrc/dgemm_kernels_small2.cu),
+    grid and stream-K ranges sized for 296 CTA slots.  Same bound; bit-identical to itself run to run."""
+    (M, N, K), pad, alpha, beta = case
+    monkeypatch.setenv("DGEMM_B200_SMALL_CTAS", "2")
+    dg.reload_env()
+    try:
+        A, B, C0 = gu.make_inputs(M, N, K, pad, c_fill=np.nan if beta == 0.0 else None)
+        outs = []
+        for _ in range(2):
+            dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+            dg.dgemm_device(M, N, K, alpha, dA.ptr, dA.ld, dB.ptr, dB.ld, beta, dC.ptr, dC.ld)
+            assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+            outs.append(dC.to_host())
+            dA.free(); dB.free(); dC.free()
+        if beta == 0.0:
+            C0[:M, :] = 0.0
+        gu.check(M, N, K, alpha, A, B, beta, C0, outs[0])
+        assert np.array_equal(outs[0], outs[1])
+    finally:
+        monkeypatch.delenv("DGEMM_B200_SMALL_CTAS")
+        dg.reload_env()
+
+
 def test_k_lockstep_changes_no_bits(dg, monkeypatch):
     """Large enough for the k-lockstep of the data-parallel waves (2 full waves, operands > 96 MB, K >= 4096): the
     producers' pacing must not change a single bit, twice in a row (the counters are re-zeroed per launch), and the
