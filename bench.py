@@ -873,8 +873,11 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
     torch.cuda.synchronize()
     dg.reset_launch_count()
     t0 = time.perf_counter()
+    per_rep = []
     for _ in range(reps):
+        t1 = time.perf_counter()
         one()
+        per_rep.append(time.perf_counter() - t1)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     launches = dg.launch_count()
@@ -910,7 +913,8 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
         raise SystemExit(f"bench.py: end-to-end result is WRONG: max |err|/bound = {check}")
     return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "spot_check_max_err_over_bound": check,
             "spot_check": f"{len(idx)} entries per rank recomputed on the host in long double", "unit": UNIT, "h2d_bytes_per_step": h2d,
-            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps, "gpu_launches": launches,
+            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps,
+            "ms_per_rep_this_rank": [round(1e3 * x, 2) for x in per_rep], "gpu_launches": launches,
             "timeline": timeline,
             "api": "mydgemm_gpu_v20(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC) with pinned host pointers" if N == 1 else
                    "dgemm_b200_rank_pipeline(M,ncols,K,alpha,A_slab,LDA,B_panel,LDB,beta,C_panel,LDC,rank,world,kb,xbuf,pass,...): "

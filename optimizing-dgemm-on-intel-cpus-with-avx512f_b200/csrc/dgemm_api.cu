@@ -130,6 +130,7 @@ struct Buf {
 struct DeviceCtx {
   int dev = -1;
   int num_sms = 0;
+  size_t total_mem = 0;       // bytes of HBM on the device
   bool ready = false;
   cudaStream_t s_compute = nullptr, s_h2d = nullptr, s_d2h = nullptr;
   Buf ws;                     // split-K / stream-K workspace
@@ -186,6 +187,10 @@ int ensure_ctx(int dev, DeviceCtx** out) {
     CU_TRY(cudaSetDevice(dev));
     c.dev = dev;
     CU_TRY(cudaDeviceGetAttribute(&c.num_sms, cudaDevAttrMultiProcessorCount, dev));
+    {
+      size_t free_b = 0;
+      CU_TRY(cudaMemGetInfo(&free_b, &c.total_mem));
+    }
     CU_TRY(cudaStreamCreateWithFlags(&c.s_compute, cudaStreamNonBlocking));
     CU_TRY(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
     CU_TRY(cudaStreamCreateWithFlags(&c.s_d2h, cudaStreamNonBlocking));
@@ -845,7 +850,13 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
   const size_t need = host_footprint(M, N, std::max(K, 1), need_ab, cp->num_sms);
   double budget = env().hbm_budget;
   if (budget <= 0.0) {
-    if (need < ((size_t)4 << 30)) return run_host_incore(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);  // (no query)
+    // No budget given: a call that needs less than half of the device's HBM is simply tried in core (no query on the
+    // way of every call); if its buffers cannot be allocated after all -- the memory is somebody else's -- or if it is
+    // larger than that, the budget is 90 % of what is free now plus what this library's own buffers already hold.
+    if ((double)need <= 0.5 * (double)cp->total_mem) {
+      st = run_host_incore(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
+      if (st != DGEMM_B200_ERR_OOM) return st;   // (the buffers are grown before anything is copied or computed)
+    }
     int prev = 0;
     cudaGetDevice(&prev);
     CU_TRY(cudaSetDevice(dev));
