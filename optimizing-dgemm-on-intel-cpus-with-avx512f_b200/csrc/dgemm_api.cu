@@ -63,6 +63,12 @@ struct Env {
   int small_ctas = 1;
   long long small_max_tiles = 64;       // DGEMM_B200_SMALL_TILE_MAX_TILES
   double small_max_flops = 4e9;         // DGEMM_B200_SMALL_TILE_MAX_FLOPS
+  // DGEMM_B200_TILE: "auto" (default) / "big" / "small" / "mid": force the CTA tile of the TMA kernel where it is eligible
+  // (probes and tests); DGEMM_B200_MID_TILE_MIN_TILES / _MAX_TILES: the range of 128 x 128-tile counts for which "auto"
+  // picks the 128 x 64 build (dgemm_kernels_mid.cu)
+  int force_tile = -1;
+  long long mid_min_tiles = 49, mid_max_tiles = 100;   // measured: profiles/r02_tile_probe_big_small_mid.jsonl
+  double mid_max_flops = 5e9;           // DGEMM_B200_MID_TILE_MAX_FLOPS (long K: the big tile's 98 % main loop wins)
   bool no_lockstep = false;             // DGEMM_B200_NO_LOCKSTEP
   int sync_kt = 64;                     // DGEMM_B200_SYNC_KT
   int group_m = 16;                     // DGEMM_B200_GROUP_M
@@ -94,6 +100,11 @@ struct Env {
     small_ctas = geti("DGEMM_B200_SMALL_CTAS", 1) == 2 ? 2 : 1;
     if (const char* e = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) small_max_tiles = atoll(e);
     small_max_flops = getd("DGEMM_B200_SMALL_TILE_MAX_FLOPS", small_max_flops);
+    if (const char* t = getenv("DGEMM_B200_TILE"))
+      force_tile = !strcmp(t, "big") ? dg::TILE_BIG : !strcmp(t, "small") ? dg::TILE_SMALL : !strcmp(t, "mid") ? dg::TILE_MID : -1;
+    if (const char* e = getenv("DGEMM_B200_MID_TILE_MIN_TILES")) mid_min_tiles = atoll(e);
+    if (const char* e = getenv("DGEMM_B200_MID_TILE_MAX_TILES")) mid_max_tiles = atoll(e);
+    mid_max_flops = getd("DGEMM_B200_MID_TILE_MAX_FLOPS", mid_max_flops);
     no_lockstep = has("DGEMM_B200_NO_LOCKSTEP");
     sync_kt = std::max(1, geti("DGEMM_B200_SYNC_KT", 64));
     group_m = std::max(1, geti("DGEMM_B200_GROUP_M", 16));
@@ -263,7 +274,7 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
 void plan_stream_k(dg::Params& P, int num_sms) {
   const int SK_MIN_ITERS = env().sk_min_iters, SK_ALIGNED_MIN_ITERS = env().sk_aligned_min_iters;
   // the parallel fix-up hands out a tile's fragments (32 per thread on the 128 x 128 tile, 8 on the 64 x 64 one)
-  const int max_ranges = P.tile_small ? 8 : 64;
+  const int max_ranges = P.tile_small == dg::TILE_MID ? 16 : (P.tile_small ? 8 : 64);
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0;
   if (P.k_tiles < 8) return;
@@ -303,10 +314,16 @@ void plan_stream_k(dg::Params& P, int num_sms) {
 // 256^3 15.4 / 20.5, 512^3 22.6 / 25.0, 640^3 28.8 / 35.8, 1000^3 76.4 / 86.9, 1024^3 77.3 / 80.8, 1280^3 equal,
 // 1536^3 226.6 / 218.4 (the small tile's main loop loads 6 fragments per 8 DMMAs instead of 12 per 32), 512x512x4096
 // 77.8 / 80.2, 512x512x16384 264.1 / 259.5.
-bool want_small_tile(int M, int N, int K, bool tma_kernel, bool has_fetch) {
-  if (!tma_kernel || has_fetch || env().no_small_tile) return false;
+// The 128 x 64 build (dgemm_kernels_mid.cu) takes the band of 128 x 128-tile counts [DGEMM_B200_MID_TILE_MIN_TILES,
+// DGEMM_B200_MID_TILE_MAX_TILES] in between.  Returns Params::tile_small (dg::TILE_*).
+int choose_tile(int M, int N, int K, bool tma_kernel, bool has_fetch) {
+  if (!tma_kernel || has_fetch) return dg::TILE_BIG;
+  if (env().force_tile >= 0) return env().force_tile == dg::TILE_SMALL ? env().small_ctas : env().force_tile;
+  if (env().no_small_tile) return dg::TILE_BIG;
   const long long big_tiles = (long long)((M + dg::BM - 1) / dg::BM) * ((N + dg::BN - 1) / dg::BN);
-  return big_tiles <= env().small_max_tiles && 2.0 * M * (double)N * K <= env().small_max_flops;
+  const double flops = 2.0 * M * (double)N * K;
+  if (big_tiles >= env().mid_min_tiles && big_tiles <= env().mid_max_tiles && flops <= env().mid_max_flops) return dg::TILE_MID;
+  return big_tiles <= env().small_max_tiles && flops <= env().small_max_flops ? env().small_ctas : dg::TILE_BIG;
 }
 
 int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
@@ -317,7 +334,7 @@ int fill_params(dg::Params& P, int M, int N, int K, double alpha, const double* 
   P.A = dA; P.lda = lda; P.B = dB; P.ldb = ldb; P.C = dC; P.ldc = ldc;
   P.tile_small = (small_tile && variant == dg::VARIANT_TMA && splits <= 0) ? small_tile : 0;
   if (P.tile_small == 2) num_sms *= dg::SMALL_X2_CTAS_PER_SM;   // CTA slots the grid and the stream-K ranges are sized for
-  const int bm = P.tile_small ? dg::SMALL_BM : dg::BM, bn = P.tile_small ? dg::SMALL_BN : dg::BN;
+  const int bm = dg::tile_bm(P.tile_small), bn = dg::tile_bn(P.tile_small);
   P.tiles_m = (M + bm - 1) / bm;
   P.tiles_n = (N + bn - 1) / bn;
   P.k_tiles = (K + dg::BK - 1) / dg::BK;
@@ -440,7 +457,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d: unaligned operands need K >= 2 and N >= 2 for parity-split tensor maps", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms,
-              auto_variant && want_small_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0) ? env().small_ctas : 0);
+              auto_variant ? choose_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0) : 0);
   // CTA slots of the device for the kernel build that will run (the dg64x2 build keeps two CTAs per SM resident)
   const int cta_slots = P.tile_small == 2 ? dg::SMALL_X2_CTAS_PER_SM * c.num_sms : c.num_sms;
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
@@ -483,7 +500,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (uses_ws) {
     const size_t slots = P.splits > 1 ? (size_t)P.tiles_m * P.tiles_n * P.splits
                                       : (size_t)P.sk_grid * (P.sk_parallel ? 2 : 1);
-    const size_t need = slots * (P.tile_small ? dg::SMALL_BM * dg::SMALL_BN : dg::BM * dg::BN) * sizeof(double);
+    const size_t need = slots * (size_t)(dg::tile_bm(P.tile_small) * dg::tile_bn(P.tile_small)) * sizeof(double);
     if (c.ws.cap < need) {
       int st = grow(c.ws, need);
       if (st) return st;   // (grow synchronises the device before it frees the old buffer)
@@ -1305,7 +1322,7 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
                        !env().realign_min_set;
   const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms,
-              want_small_tile(M, N, std::max(K, 1), tma_ok || split || realign, false) ? env().small_ctas : 0);
+              choose_tile(M, N, std::max(K, 1), tma_ok || split || realign, false));
   if (variant) *variant = v;
   if (splits) *splits = P.splits;
   if (sk_tiles) *sk_tiles = P.sk_tiles;

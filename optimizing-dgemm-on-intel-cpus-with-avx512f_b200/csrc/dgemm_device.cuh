@@ -565,10 +565,21 @@ __device__ __forceinline__ void add_partial_cg(double (&acc)[FRAG_N][FRAG_M][2],
 
 // stream-K partial that the producer brought into a pipeline stage with bulk_load_1d: chunk c of the [reg][thread]
 // layout holds fragments q = c*FPC .. c*FPC+FPC-1 for all consumer threads (16-byte LDS, conflict free)
-constexpr int PARTIAL_CHUNKS = (BM * BN * 8) / STAGE_BYTES;              // 4 stages per 128 KB partial
-constexpr int PARTIAL_FPC = (FRAG_N * FRAG_M) / PARTIAL_CHUNKS;          // fragments per chunk
-static_assert(PARTIAL_CHUNKS * STAGE_BYTES == BM * BN * 8 && PARTIAL_FPC * PARTIAL_CHUNKS == FRAG_N * FRAG_M &&
-              PARTIAL_FPC * CONSUMER_THREADS * 16 == STAGE_BYTES, "partial tile must split into whole stages");
+// A partial is PARTIAL_FRAGS fragments of CONSUMER_THREADS x 16 bytes; a chunk is the largest whole number of fragments
+// that divides the partial and fits one pipeline stage (128 x 128: 4 chunks of 32 KB = a whole stage; 64 x 64: 2 of 16 KB;
+// 128 x 64 with 32 x 32 warp tiles: 4 chunks of 16 KB in 24 KB stages).
+constexpr int PARTIAL_FRAGS = FRAG_N * FRAG_M;
+constexpr int PARTIAL_FRAG_BYTES = CONSUMER_THREADS * 16;
+constexpr int partial_fpc() {
+  int f = PARTIAL_FRAGS;
+  while (f > 1 && (f * PARTIAL_FRAG_BYTES > STAGE_BYTES || PARTIAL_FRAGS % f != 0)) f--;
+  return f;
+}
+constexpr int PARTIAL_FPC = partial_fpc();                               // fragments per chunk
+constexpr int PARTIAL_CHUNKS = PARTIAL_FRAGS / PARTIAL_FPC;              // stages per partial
+constexpr int PARTIAL_CHUNK_BYTES = PARTIAL_FPC * PARTIAL_FRAG_BYTES;
+static_assert(PARTIAL_CHUNKS * PARTIAL_CHUNK_BYTES == BM * BN * 8 && PARTIAL_FPC * PARTIAL_CHUNKS == PARTIAL_FRAGS &&
+              PARTIAL_CHUNK_BYTES <= STAGE_BYTES, "partial tile must split into chunks of at most one stage");
 __device__ __forceinline__ void add_partial_smem(double (&acc)[FRAG_N][FRAG_M][2], uint32_t stage, int chunk, int tid) {
 #pragma unroll
   for (int c = 0; c < PARTIAL_CHUNKS; c++) {

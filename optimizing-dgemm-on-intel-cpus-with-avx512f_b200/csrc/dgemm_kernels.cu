@@ -333,15 +333,16 @@ static cudaError_t set_smem(Kern k, int bytes) {
 // how many CTAs of the TMA kernel (either tile size, any split variant: same block size and shared memory) can be
 // resident on the current device at once; what a grid whose CTAs wait on each other must not exceed
 int tma_coresident_capacity(int tile_small, int num_sms) {
-  static std::atomic<int> per_sm[3][64];
+  static std::atomic<int> per_sm[4][64];
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || tile_small < 0 || tile_small > 2) return 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || tile_small < 0 || tile_small > 3) return 0;
   std::atomic<int>& slot = per_sm[tile_small][dev & 63];
   int n = slot.load(std::memory_order_relaxed);
   if (n == 0) {
     cudaError_t e;
     if (tile_small == 1) e = small_tile_occupancy(&n);
     else if (tile_small == 2) e = small_tile_occupancy_x2(&n);
+    else if (tile_small == 3) e = small_tile_occupancy_mid(&n);
     else {
       const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
       e = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem);
@@ -374,7 +375,7 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
     const int split = tma_split_bits(P);
     if (split && !tma_split_ok(P)) return cudaErrorInvalidValue;
     if (P.tile_small && (P.splits != 1 || P.fetch_bytes)) return cudaErrorInvalidValue;
-    const int bn = P.tile_small ? SMALL_BN : BN;   // (the A boxes are 16 rows high in both tile configurations)
+    const int bn = tile_bn(P.tile_small);   // (the A boxes are 16 rows high in every tile configuration)
     Params Q = P;
     Q.a_mis[0] = Q.a_mis[1] = Q.b_mis[0] = Q.b_mis[1] = 0;
     CUtensorMap tmA, tmA1, tmB, tmB1;
@@ -395,12 +396,13 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
       ok = ok && make_tmap(&tmB, P.B, P.K, P.N, P.ldb, BK, bn);
     }
     if (!ok) return cudaErrorInvalidValue;
-    if (P.tile_small) {   // 64 x 64 tiles: dgemm_kernels_small.cu (one CTA per SM), dgemm_kernels_small2.cu (two)
+    if (P.tile_small) {   // 64 x 64 tiles: dgemm_kernels_small.cu (one CTA per SM), dgemm_kernels_small2.cu (two); 128 x 64: dgemm_kernels_mid.cu
       const int slots = P.tile_small == 2 ? SMALL_X2_CTAS_PER_SM * num_sms : num_sms;
       const int dp_units = P.sk_tiles > 0 ? P.sk_tile0 : tiles;
       const int grid = P.sk_tiles > 0 ? P.sk_grid : (dp_units < slots ? dp_units : slots);
       const void* maps[4] = {&tmA, &tmA1, &tmB, &tmB1};
       g_launches++;
+      if (P.tile_small == TILE_MID) return launch_tma_small_mid(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
       return P.tile_small == 2 ? launch_tma_small_x2(maps, split, Q, grid, dp_units, stream, cooperative, pdl)
                                : launch_tma_small(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
     }

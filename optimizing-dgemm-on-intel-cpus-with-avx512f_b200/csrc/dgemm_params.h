@@ -17,7 +17,8 @@ struct Params {
   int k_tiles;            // ceil(K / BK)
   int splits;             // split-K factor, 1 = none
   int k_tiles_per_split;  // ceil(k_tiles / splits)
-  int tile_small;         // 1 / 2: tiles_m / tiles_n count 64 x 64 tiles and the dg64 (one CTA per SM) / dg64x2 (two) build runs
+  int tile_small;         // 1 / 2: tiles_m / tiles_n count 64 x 64 tiles and the dg64 (one CTA per SM) / dg64x2 (two) build runs;
+                          // 3: 128 x 64 tiles, the dg128x64 build (dgemm_host.h: TILE_*)
   int group_m;            // rasterisation: tiles are walked in bands of group_m tile-rows
   int c_vec2;             // C base 16-byte aligned and ldc even -> 16-byte epilogue accesses
   double* workspace;      // splits > 1: [unit][ACC_PER_THREAD][CONSUMER_THREADS] partial accumulators;

@@ -1,10 +1,13 @@
-// dgemm_small_tile.cuh — the 64 x 64 build(s) of the persistent TMA kernel plus their launchers.  Included by
-// dgemm_kernels_small.cu (namespace dg64: one CTA per SM, 8 stages) and dgemm_kernels_small2.cu (namespace dg64x2: two
-// CTAs per SM, 4 stages each), which set DG_NAMESPACE / DG_SMALL_STAGES / DG_MIN_CTAS / the register split and
-// DG_SMALL_FN (the suffix of the two host entry points) before including it.
+// dgemm_small_tile.cuh — the smaller-tile builds of the persistent TMA kernel plus their launchers.  Included by
+// dgemm_kernels_small.cu (namespace dg64: 64 x 64, one CTA per SM, 8 stages), dgemm_kernels_small2.cu (namespace dg64x2:
+// 64 x 64, two CTAs per SM, 4 stages each) and dgemm_kernels_mid.cu (namespace dg128x64: 128 x 64, 32 x 32 warp tiles),
+// which set DG_NAMESPACE / DG_SMALL_STAGES / DG_MIN_CTAS / the register split, optionally DG_BM / DG_BN / the warp grid,
+// and DG_SMALL_FN (the suffix of the two host entry points) before including it.
 #define DG_SMALL_TILE 1
+#ifndef DG_BM
 #define DG_BM 64
 #define DG_BN 64
+#endif
 #include "dgemm_tma_kernel.cuh"
 #include "dgemm_host.h"
 #include "dgemm_launch.h"
@@ -15,7 +18,8 @@
 namespace dg {
 
 namespace ks = DG_NAMESPACE;
-static_assert(ks::BM == SMALL_BM && ks::BN == SMALL_BN, "dgemm_host.h must state the small tile's size");
+static_assert((ks::BM == SMALL_BM && ks::BN == SMALL_BN) || (ks::BM == MID_BM && ks::BN == MID_BN),
+              "dgemm_host.h must state the tile's size");
 
 namespace {
 constexpr int SMALL_STAGES = DG_SMALL_STAGES;

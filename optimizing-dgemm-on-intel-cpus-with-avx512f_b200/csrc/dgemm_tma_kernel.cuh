@@ -166,7 +166,7 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
         }
         if (sg.kind == SEG_SK_OWNER && !P.sk_parallel) {
           // serial stream-K fix-up: the partials of the ranges that hold the rest of this tile come in through the
-          // SAME ring, four stages per partial, as soon as their flag is up, so the owner's consumers find them in
+          // SAME ring, PARTIAL_CHUNKS stages per partial, as soon as their flag is up, so the owner's consumers find them in
           // shared memory when their main loop ends instead of paying two global round trips per partial.  An owner
           // segment is the last of its range, and a contributor never waits for anybody: no cycle.
           const long long total = (long long)P.sk_tiles * P.k_tiles;
@@ -179,8 +179,8 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
             for (int c = 0; c < PARTIAL_CHUNKS; c++) {
               mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
               const uint32_t full = bars + 8 * s;
-              mbar_arrive_expect_tx(full, STAGE_BYTES);
-              bulk_load_1d(smem_base + s * STAGE_BYTES, src + (size_t)c * STAGE_BYTES, STAGE_BYTES, full);
+              mbar_arrive_expect_tx(full, PARTIAL_CHUNK_BYTES);
+              bulk_load_1d(smem_base + s * STAGE_BYTES, src + (size_t)c * PARTIAL_CHUNK_BYTES, PARTIAL_CHUNK_BYTES, full);
               if (++s == STAGES) { s = 0; ph ^= 1; }
             }
           }

@@ -266,6 +266,40 @@ def test_small_tile_build_at_two_ctas_per_sm(dg, monkeypatch, case):
         dg.reload_env()
 
 
+@pytest.mark.parametrize("case", [((128, 64, 16), (0, 0, 0), 1.0, 1.0), ((256, 256, 256), (0, 0, 0), 1.0, 1.0),
+                                  ((512, 512, 512), (0, 0, 0), 2.5, 0.5),          # all stream-K, ranges shorter than a tile
+                                  ((1000, 1003, 997), (0, 0, 0), -1.0, 1.0),      # odd LDB: parity-split kernel of the build
+                                  ((1000, 1003, 997), (7, 7, 7), 1.5, 0.0),       # odd LDA, beta = 0 over NaN
+                                  ((1001, 999, 1003), (1, 1, 1), 1.0, 1.0),       # both operands split, odd LDC
+                                  ((1024, 1024, 1024), (0, 0, 0), 1.0, 1.0), ((1536, 1536, 1536), (0, 0, 0), 1.0, 1.0),
+                                  ((2048, 2048, 512), (0, 0, 0), 1.0, 1.0),       # data-parallel wave + stream-K tail
+                                  ((300, 700, 64), (2, 0, 0), 1.0, 1.0), ((129, 65, 4096), (0, 0, 0), 1.0, 0.5),
+                                  ((7, 9, 33), (0, 0, 0), 1.0, 1.0)])
+def test_mid_tile_build(dg, monkeypatch, case):
+    """DGEMM_B200_TILE=mid: the TMA kernel compiled for 128 x 64 CTA tiles with 32 x 32 warp tiles
+    (csrc/dgemm_kernels_mid.cu; 24 KB stages, stream-K partials in 16 KB chunks).  Same bound as every other path;
+    bit-identical to itself run to run."""
+    (M, N, K), pad, alpha, beta = case
+    monkeypatch.setenv("DGEMM_B200_TILE", "mid")
+    dg.reload_env()
+    try:
+        A, B, C0 = gu.make_inputs(M, N, K, pad, c_fill=np.nan if beta == 0.0 else None)
+        outs = []
+        for _ in range(2):
+            dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+            dg.dgemm_device(M, N, K, alpha, dA.ptr, dA.ld, dB.ptr, dB.ld, beta, dC.ptr, dC.ld)
+            assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+            outs.append(dC.to_host())
+            dA.free(); dB.free(); dC.free()
+        if beta == 0.0:
+            C0[:M, :] = 0.0
+        gu.check(M, N, K, alpha, A, B, beta, C0, outs[0])
+        assert np.array_equal(outs[0], outs[1])
+    finally:
+        monkeypatch.delenv("DGEMM_B200_TILE")
+        dg.reload_env()
+
+
 def test_k_lockstep_changes_no_bits(dg, monkeypatch):
     """Large enough for the k-lockstep of the data-parallel waves (2 full waves, operands > 96 MB, K >= 4096): the
     producers' pacing must not change a single bit, twice in a row (the counters are re-zeroed per launch), and the

@@ -18,9 +18,12 @@ for (M, N, K) in shapes:
                                  "DGEMM_B200_SMALL_CTAS": "1"}),
                       ("small_x2", {"DGEMM_B200_SMALL_TILE_MAX_TILES": "100000", "DGEMM_B200_SMALL_TILE_MAX_FLOPS": "1e30",
                                     "DGEMM_B200_SMALL_CTAS": "2"}),
+                      ("mid", {"DGEMM_B200_TILE": "mid"}),
                       ("auto", {})):
+        if name == "small_x2" and os.environ.get("PROBE_NO_X2"):
+            continue
         for k in ("DGEMM_B200_NO_SMALL_TILE", "DGEMM_B200_SMALL_TILE_MAX_TILES", "DGEMM_B200_SMALL_TILE_MAX_FLOPS",
-                  "DGEMM_B200_SMALL_CTAS"):
+                  "DGEMM_B200_SMALL_CTAS", "DGEMM_B200_TILE"):
             os.environ.pop(k, None)
         os.environ.update(env)
         dg.reload_env()   # the library reads its switches once
@@ -28,7 +31,9 @@ for (M, N, K) in shapes:
         row[name + "_us"] = round(ms * 1e3, 2); row[name + "_tflops"] = round(2.0 * M * N * K / ms / 1e9, 3)
         row[name + "_plan"] = dg.plan(M, N, K, dA, M, dB, K)
     row["small_over_big"] = round(row["big_us"] / row["small_us"], 3)
-    row["x2_over_big"] = round(row["big_us"] / row["small_x2_us"], 3)
-    row["x2_over_small"] = round(row["small_us"] / row["small_x2_us"], 3)
+    if "small_x2_us" in row:
+        row["x2_over_big"] = round(row["big_us"] / row["small_x2_us"], 3)
+        row["x2_over_small"] = round(row["small_us"] / row["small_x2_us"], 3)
+    row["mid_over_best"] = round(min(row["big_us"], row["small_us"]) / row["mid_us"], 3)
     print(json.dumps(row), flush=True)
     for d in (dA, dB, dC): dg.free(d)
