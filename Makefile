@@ -27,6 +27,18 @@ lib16: $(PKG)/libdgemm_b200_w16.so
 $(PKG)/libdgemm_b200_w16.so: $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -DDG_WARPS_M=4 -DDG_WARPS_N=4 -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
 
+# measurement build: the producer hands every stage over WITHOUT loading it (results are garbage, timing is the consumers'
+# loop alone); load with DGEMM_B200_LIB=.../libdgemm_b200_dbg_notma.so (tools/r02_call19.sh)
+libdbg: $(PKG)/libdgemm_b200_dbg_notma.so
+$(PKG)/libdgemm_b200_dbg_notma.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_DEBUG_NO_TMA -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
+# measurement builds: the two consumer warps of a sub-partition skewed by n/64 of a stage (DG_SKEW_64THS)
+SKEWS ?= 2 4 8 12 16
+libskew: $(foreach n,$(SKEWS),$(PKG)/libdgemm_b200_skew$(n).so)
+$(PKG)/libdgemm_b200_skew%.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_SKEW_64THS=$* -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
 probe: $(PKG)/bin/peak_probe
 $(PKG)/bin/peak_probe: $(CSRC)/peak_probe.cu
 	mkdir -p $(PKG)/bin
@@ -53,4 +65,4 @@ sass: $(LIB)
 clean:
 	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
 	$(MAKE) -C oracle clean
-.PHONY: all build lib lib16 probe stage_probe harness oracle sass clean
+.PHONY: all build lib lib16 libdbg probe stage_probe harness oracle sass clean

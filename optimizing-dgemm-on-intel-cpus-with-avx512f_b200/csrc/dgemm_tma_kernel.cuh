@@ -31,6 +31,14 @@ struct Segment {
   int slot;           // workspace slot (split-K: unit index; stream-K contributor: own range id)
   int wave;           // phase 1: how many units this CTA has done before this one; -1 in phase 2
 };
+// Skew between the two consumer warps of an SM sub-partition (w and w + 4), in 64ths of the pair's time per stage; 0 = off.
+// Measured (tools/r02_call20.sh / r02_call21.sh, profiles/r02_consumer_warp_skew.txt): 2/64 .. 8/64 of a stage take the
+// 128 x 128 kernel from 36.52 to 36.70-36.76 TFLOP/s at 16384^3 (8192^3 36.39 -> 36.67, 4096^3 36.19 -> 36.36) and a whole
+// 128 x 64 tile from 139.3 to 137.9 us; 12/64 and more are WORSE than none (36.35), and the 64 x 64 tile gains nothing.
+#ifndef DG_SKEW_64THS
+#define DG_SKEW_64THS (DG_BM * DG_BN >= 128 * 64 ? 4 : 0)
+#endif
+constexpr long long SKEW_CLK = CONSUMER_WARPS == 8 ? (long long)FRAG_M * FRAG_N * 4 * 16 * 2 * DG_SKEW_64THS / 64 : 0;
 constexpr int SYNC_SLACK = 2;  // k-lockstep: a producer may run this many sync points ahead of the slowest CTA
 enum { SEG_DIRECT = 0, SEG_SPLITK = 1, SEG_SK_OWNER = 2, SEG_SK_CONTRIB = 3 };
 
@@ -140,6 +148,11 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
           const uint32_t full = bars + 8 * s;
           const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
+#ifdef DG_DEBUG_NO_TMA
+          // measurement build only (make libdbg): the stage is handed over without loading anything, so the consumers'
+          // loop runs against barriers that are always ready -- separates "waiting for operands" from the loop's own cost
+          if constexpr (SPLIT == SPLIT_NONE) { mbar_arrive(full); if (++s == STAGES) { s = 0; ph ^= 1; } continue; }
+#endif
           if constexpr (SPLIT == SPLIT_NONE) mbar_arrive_expect_tx(full, STAGE_BYTES);
           else mbar_arrive_expect_tx(full, tx_bytes);
           const int k0 = kt * BK;
@@ -300,6 +313,16 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
         // INCLUDING across the stage boundary (wait on the next stage's barrier before the last DMMA group)
         mbar_wait(bars + 8 * s, ph);
         if (tid == 0) stamp(P, tslot++);   // first operands of the segment have landed
+        if constexpr (SKEW_CLK > 0) {
+          // the two consumer warps of an SM sub-partition (w, w + 4) would otherwise walk the stages in lockstep and
+          // reach every stage boundary (barrier probe, branches, arrive: ~75 clk without a DMMA to issue) together;
+          // held back by a fraction of a stage, each one's boundary falls into the other's DMMA stream
+          consumer_bar_sync();
+          if (warp >= CONSUMER_WARPS / 2) {
+            const long long t0 = clock64();
+            while (clock64() - t0 < SKEW_CLK) {}
+          }
+        }
         load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
         for (int kt = sg.kb; kt < sg.ke; kt++) {
           const uint32_t sA = smem_base + s * STAGE_BYTES, sB = sA + A_STAGE_BYTES;

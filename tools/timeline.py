@@ -31,4 +31,8 @@ for j in range(16):
     col = rel[:, j]
     if np.all(np.isnan(col)): continue
     print(f"{names[j]:12s} min {np.nanmin(col):8.2f}  median {np.nanmedian(col):8.2f}  max {np.nanmax(col):8.2f} us  (n={np.sum(~np.isnan(col))})")
+for i in range(4):   # per-CTA main-loop duration of segment i (landed -> loop end): a whole tile where the segment is one
+    d = rel[:, 2 + 3 * i + 1] - rel[:, 2 + 3 * i]
+    if not np.all(np.isnan(d)):
+        print(f"seg{i} loop duration  min {np.nanmin(d):8.2f}  median {np.nanmedian(d):8.2f}  max {np.nanmax(d):8.2f} us")
 print("kernel span (first entry -> last stamp): %.2f us" % np.nanmax(rel))
