@@ -39,6 +39,11 @@ libskew: $(foreach n,$(SKEWS),$(PKG)/libdgemm_b200_skew$(n).so)
 $(PKG)/libdgemm_b200_skew%.so: $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -DDG_SKEW_64THS=$* -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
 
+# measurement builds: unroll factor of the consumers' k-tile loop (DG_KT_UNROLL; ptxas unrolls by 2 on its own)
+libunroll: $(PKG)/libdgemm_b200_unroll2.so $(PKG)/libdgemm_b200_unroll4.so
+$(PKG)/libdgemm_b200_unroll%.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_KT_UNROLL=$* -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
 probe: $(PKG)/bin/peak_probe
 $(PKG)/bin/peak_probe: $(CSRC)/peak_probe.cu
 	mkdir -p $(PKG)/bin

@@ -312,7 +312,7 @@ void plan_stream_k(dg::Params& P, int num_sms) {
 // or parity-split tensor maps; DGEMM_B200_NO_SMALL_TILE=1 switches it off.  Read per call.  Measured small / big tile, kernel-only
 // microseconds (tools/small_tile_probe.py, profiles/r01_small_tile_probe.jsonl): 100^3 12.4 / 32.9, 200^3 14.5 / 24.7,
 // 256^3 15.4 / 20.5, 512^3 22.6 / 25.0, 640^3 28.8 / 35.8, 1000^3 76.4 / 86.9, 1024^3 77.3 / 80.8, 1280^3 equal,
-// 1536^3 226.6 / 218.4 (the small tile's main loop loads 6 fragments per 8 DMMAs instead of 12 per 32), 512x512x4096
+// 1536^3 226.6 / 218.4 (the small tile's stages are a quarter as long and every stage boundary costs the same), 512x512x4096
 // 77.8 / 80.2, 512x512x16384 264.1 / 259.5.
 // The 128 x 64 build (dgemm_kernels_mid.cu) takes the band of 128 x 128-tile counts [DGEMM_B200_MID_TILE_MIN_TILES,
 // DGEMM_B200_MID_TILE_MAX_TILES] in between.  Returns Params::tile_small (dg::TILE_*).

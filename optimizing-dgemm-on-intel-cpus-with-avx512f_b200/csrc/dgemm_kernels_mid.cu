@@ -2,11 +2,11 @@
 // dg128x64): 8 DMMA consumer warps in a 4 x 2 grid with 32 x 32 warp tiles (64 accumulator registers), 24 KB pipeline
 // stages (A 128 x 16 as eight 16 x 16 boxes, B one 16 x 64 box), 64 KB stream-K partials.
 //
-// Why: the 64 x 64 build's main loop runs at ~86 % of the FP64 pipe (timeline at 1024^3: 110.7 k-tiles per CTA in
-// 66.8 us against 57.7 at the pipe's rate; 6 fragment loads and one barrier round per 8 / 32 DMMAs of a warp), the
-// 128 x 128 build's at 98 % but with four times the bytes per stream-K partial and a quarter of the tiles to balance.
-// This tile sits between them: 8 fragment loads per 16 DMMAs, 64 DMMAs per warp and stage, half the partial of the big
-// tile.  run_device picks it for the sizes between the two (dgemm_api.cu: choose_tile).
+// Why: every stage boundary costs a sub-partition ~75 clk whatever the tile (profiles/r02_loop_with_and_without_tma.txt),
+// so the 64 x 64 build's loop (1024-clk stages) runs at ~92 % of the FP64 pipe and the 128 x 128 build's (4096-clk stages)
+// at 98 %, but the latter with four times the bytes per stream-K partial and a quarter of the tiles to balance.  This
+// tile sits between them: 2048-clk stages (96 %), half the partial of the big tile.  run_device picks it for the sizes
+// between the two (dgemm_api.cu: choose_tile; measured band in profiles/r02_tile_probe_big_small_mid.jsonl).
 // Same role in the reference: the 16x8 / 8x8 edge micro-kernels beside the 24x8 one (include/kernel18.h:533-600).
 #define DG_NAMESPACE dg128x64
 #define DG_BM 128

@@ -4,8 +4,9 @@
 // Why: a problem with few 128 x 128 tiles (256^3: 4, 512^3: 16) can only fill 148 SMs by cutting K into many ranges per
 // tile, and then the partial-tile exchange dominates: R ranges of a tile write and read R x 128 KB through L2 (512^3:
 // 16 MB each way, ~6.5 us of an 18 us kernel).  A quarter-size tile needs a quarter of the ranges per tile and moves a
-// quarter of the bytes per partial.  Its main loop is less efficient (6 fragment loads per 8 DMMAs instead of 12 per
-// 32), which does not matter where the launch is a few microseconds long; run_device picks it only for small,
+// quarter of the bytes per partial.  Its main loop is less efficient (92 % of the pipe against 98 %: the ~75 clk every
+// stage boundary costs are 7 % of a 1024-clk stage and 2 % of a 4096-clk one -- not the fragment loads, see
+// tools/lds_dmma_probe.cu), which does not matter where the launch is a few microseconds long; run_device picks it only for small,
 // TMA-eligible problems (see dgemm_api.cu) and the 128 x 128 kernel stays the performance path.
 // Same role in the reference: the 8x8 / 2x8 ... edge micro-kernels beside the 24x8 one (include/kernel18.h:533-600).
 //

@@ -39,6 +39,13 @@ struct Segment {
 #define DG_SKEW_64THS (DG_BM * DG_BN >= 128 * 64 ? 4 : 0)
 #endif
 constexpr long long SKEW_CLK = CONSUMER_WARPS == 8 ? (long long)FRAG_M * FRAG_N * 4 * 16 * 2 * DG_SKEW_64THS / 64 : 0;
+// Unroll factor of the consumers' k-tile loop, 0 = ptxas' choice (one stage per trip on the 128-wide tiles, two on the
+// 64 x 64 one).  Forcing 2 or 4 is SLOWER (profiles/r02_kt_unroll.txt: 16384^3 36.74 -> 36.18 / 35.91 TFLOP/s, a whole
+// 128 x 128 tile 270.8 -> 275.6 / 277.8 us): a stage of the big tile is already ~5 KB of SASS.
+#ifndef DG_KT_UNROLL
+#define DG_KT_UNROLL 0
+#endif
+constexpr int KT_UNROLL = DG_KT_UNROLL > 0 ? DG_KT_UNROLL : 1;
 constexpr int SYNC_SLACK = 2;  // k-lockstep: a producer may run this many sync points ahead of the slowest CTA
 enum { SEG_DIRECT = 0, SEG_SPLITK = 1, SEG_SK_OWNER = 2, SEG_SK_CONTRIB = 3 };
 
@@ -324,6 +331,9 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           }
         }
         load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
+#if DG_KT_UNROLL > 0   // measurement builds only (make libunroll); left to ptxas otherwise (it unrolls the 64 x 64 loop by 2)
+#pragma unroll KT_UNROLL
+#endif
         for (int kt = sg.kb; kt < sg.ke; kt++) {
           const uint32_t sA = smem_base + s * STAGE_BYTES, sB = sA + A_STAGE_BYTES;
           const uint32_t cur_empty = bars + 8 * (STAGES + s);
