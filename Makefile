@@ -11,7 +11,7 @@ HOSTCXX  := /usr/bin/g++
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -lineinfo -std=c++17 -ccbin $(HOSTCXX) -Xcompiler -fPIC -Xcompiler -Wall
 LIB      := $(PKG)/libdgemm_b200.so
-LIB_SRCS := $(CSRC)/dgemm_kernels.cu $(CSRC)/dgemm_rank.cu $(CSRC)/dgemm_rankplan.cpp $(CSRC)/dgemm_kernels_small.cu $(CSRC)/dgemm_kernels_small2.cu $(CSRC)/dgemm_kernels_mid.cu $(CSRC)/dgemm_kernels_cluster.cu $(CSRC)/dgemm_ladder.cu $(CSRC)/dgemm_api.cu $(CSRC)/dgemm_multi.cu \
+LIB_SRCS := $(CSRC)/dgemm_kernels.cu $(CSRC)/dgemm_rank.cu $(CSRC)/dgemm_rankplan.cpp $(CSRC)/dgemm_kernels_small.cu $(CSRC)/dgemm_kernels_small2.cu $(CSRC)/dgemm_kernels_mid.cu $(CSRC)/dgemm_kernels_tiny.cu $(CSRC)/dgemm_kernels_cluster.cu $(CSRC)/dgemm_ladder.cu $(CSRC)/dgemm_api.cu $(CSRC)/dgemm_multi.cu \
             $(CSRC)/dgemm_hostplan.cpp $(CSRC)/dgemm_staging.cu
 LIB_HDRS := $(CSRC)/dgemm_device.cuh $(CSRC)/dgemm_launch.h $(CSRC)/dgemm_params.h $(CSRC)/dgemm_tma_kernel.cuh $(CSRC)/dgemm_small_tile.cuh $(CSRC)/dgemm_host.h include/dgemm_b200.h
 
@@ -44,6 +44,29 @@ libunroll: $(PKG)/libdgemm_b200_unroll2.so $(PKG)/libdgemm_b200_unroll4.so
 $(PKG)/libdgemm_b200_unroll%.so: $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -DDG_KT_UNROLL=$* -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
 
+# measurement builds: two k-tiles per ring slot in EVERY tile configuration (DG_KT_PER_STAGE=2, half as many slots)
+libkps: $(PKG)/libdgemm_b200_kps2.so
+$(PKG)/libdgemm_b200_kps2.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_KT_PER_STAGE=2 -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
+# measurement builds of the 64 x 32 tile alone (every other object is shared): libdgemm_b200_tiny_<name>.so
+#   kps2: two k-tiles per ring slot; nodual: one accumulator set; latedesc: descriptor prefetch after the barrier init
+OBJDIR   := build/obj
+LIB_OBJS := $(patsubst $(CSRC)/%,$(OBJDIR)/%.o,$(filter-out $(CSRC)/dgemm_kernels_tiny.cu,$(LIB_SRCS)))
+$(OBJDIR)/%.o: $(CSRC)/% $(LIB_HDRS)
+	mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -c -o $@ $<
+TINY_FLAGS_kps2     := -DDG_TINY_KPS=2
+TINY_FLAGS_nodual   := -DDG_TINY_DUAL_ACC=0
+TINY_FLAGS_latedesc := -DDG_TINY_EARLY_DESC=0
+TINY_FLAGS_plain    := -DDG_TINY_DUAL_ACC=0 -DDG_TINY_EARLY_DESC=0
+TINY_FLAGS_w16      := -DDG_TINY_WARPS16=1
+TINY_FLAGS_w4       := -DDG_TINY_WARPS4=1
+libtiny: $(foreach n,kps2 nodual latedesc plain w16 w4,$(PKG)/libdgemm_b200_tiny_$(n).so)
+$(PKG)/libdgemm_b200_tiny_%.so: $(LIB_OBJS) $(CSRC)/dgemm_kernels_tiny.cu $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) $(TINY_FLAGS_$*) -c -o $(OBJDIR)/tiny_$*.o $(CSRC)/dgemm_kernels_tiny.cu
+	$(NVCC) $(ARCH) -shared -o $@ $(LIB_OBJS) $(OBJDIR)/tiny_$*.o -Xlinker --no-undefined -ldl -lpthread
+
 probe: $(PKG)/bin/peak_probe
 $(PKG)/bin/peak_probe: $(CSRC)/peak_probe.cu
 	mkdir -p $(PKG)/bin
@@ -70,4 +93,4 @@ sass: $(LIB)
 clean:
 	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
 	$(MAKE) -C oracle clean
-.PHONY: all build lib lib16 libdbg probe stage_probe harness oracle sass clean
+.PHONY: all build lib lib16 libdbg libkps libtiny probe stage_probe harness oracle sass clean

@@ -69,6 +69,12 @@ struct Env {
   int force_tile = -1;
   long long mid_min_tiles = 49, mid_max_tiles = 100;   // measured: profiles/r02_tile_probe_big_small_mid.jsonl
   double mid_max_flops = 5e9;           // DGEMM_B200_MID_TILE_MAX_FLOPS (long K: the big tile's 98 % main loop wins)
+  // The 64 x 32 build (dgemm_kernels_tiny.cu) runs ONE data-parallel wave, no exchange: "auto" picks it when its tiles fit one
+  // wave and the SMs it leaves idle cost less than the exchange a stream-K schedule of a larger tile would pay
+  // (DGEMM_B200_TINY_GAIN_US, microseconds; 0 = never).  DGEMM_B200_TINY_SK=1: let plan_stream_k cut a partial wave of these
+  // tiles into ranges as it does for the other builds (tests, probes).
+  double tiny_gain_us = 4.0;
+  bool tiny_sk = false;
   bool no_lockstep = false;             // DGEMM_B200_NO_LOCKSTEP
   int sync_kt = 64;                     // DGEMM_B200_SYNC_KT
   int group_m = 16;                     // DGEMM_B200_GROUP_M
@@ -101,7 +107,10 @@ struct Env {
     if (const char* e = getenv("DGEMM_B200_SMALL_TILE_MAX_TILES")) small_max_tiles = atoll(e);
     small_max_flops = getd("DGEMM_B200_SMALL_TILE_MAX_FLOPS", small_max_flops);
     if (const char* t = getenv("DGEMM_B200_TILE"))
-      force_tile = !strcmp(t, "big") ? dg::TILE_BIG : !strcmp(t, "small") ? dg::TILE_SMALL : !strcmp(t, "mid") ? dg::TILE_MID : -1;
+      force_tile = !strcmp(t, "big") ? dg::TILE_BIG : !strcmp(t, "small") ? dg::TILE_SMALL : !strcmp(t, "mid") ? dg::TILE_MID
+                   : !strcmp(t, "tiny") ? dg::TILE_TINY : -1;
+    tiny_gain_us = getd("DGEMM_B200_TINY_GAIN_US", tiny_gain_us);
+    tiny_sk = has("DGEMM_B200_TINY_SK");
     if (const char* e = getenv("DGEMM_B200_MID_TILE_MIN_TILES")) mid_min_tiles = atoll(e);
     if (const char* e = getenv("DGEMM_B200_MID_TILE_MAX_TILES")) mid_max_tiles = atoll(e);
     mid_max_flops = getd("DGEMM_B200_MID_TILE_MAX_FLOPS", mid_max_flops);
@@ -274,12 +283,13 @@ int choose_splits(int tiles, int k_tiles, int num_sms) {
 void plan_stream_k(dg::Params& P, int num_sms) {
   const int SK_MIN_ITERS = env().sk_min_iters, SK_ALIGNED_MIN_ITERS = env().sk_aligned_min_iters;
   // the parallel fix-up hands out a tile's fragments (32 per thread on the 128 x 128 tile, 8 on the 64 x 64 one)
-  const int max_ranges = P.tile_small == dg::TILE_MID ? 16 : (P.tile_small ? 8 : 64);
+  const int max_ranges = P.tile_small == dg::TILE_MID ? 16 : (P.tile_small == dg::TILE_TINY ? 4 : (P.tile_small ? 8 : 64));
   const int tiles = P.tiles_m * P.tiles_n;
   P.sk_tile0 = tiles; P.sk_tiles = 0; P.sk_grid = 0; P.sk_parallel = 0;
   if (P.k_tiles < 8) return;
   const int full_waves = tiles / num_sms, rem = tiles % num_sms;
   if (rem == 0) return;
+  if (P.tile_small == dg::TILE_TINY && full_waves == 0 && !env().tiny_sk) return;   // the 64 x 32 build's point: one wave, no exchange
   if (full_waves >= 1) {
     P.sk_tiles = rem + num_sms;
     P.sk_grid = num_sms;
@@ -316,12 +326,19 @@ void plan_stream_k(dg::Params& P, int num_sms) {
 // 77.8 / 80.2, 512x512x16384 264.1 / 259.5.
 // The 128 x 64 build (dgemm_kernels_mid.cu) takes the band of 128 x 128-tile counts [DGEMM_B200_MID_TILE_MIN_TILES,
 // DGEMM_B200_MID_TILE_MAX_TILES] in between.  Returns Params::tile_small (dg::TILE_*).
-int choose_tile(int M, int N, int K, bool tma_kernel, bool has_fetch) {
+int choose_tile(int M, int N, int K, bool tma_kernel, bool has_fetch, int num_sms) {
   if (!tma_kernel || has_fetch) return dg::TILE_BIG;
   if (env().force_tile >= 0) return env().force_tile == dg::TILE_SMALL ? env().small_ctas : env().force_tile;
   if (env().no_small_tile) return dg::TILE_BIG;
   const long long big_tiles = (long long)((M + dg::BM - 1) / dg::BM) * ((N + dg::BN - 1) / dg::BN);
   const double flops = 2.0 * M * (double)N * K;
+  // 64 x 32 tiles, data-parallel: a k-tile of this build takes ~0.28 us (two per ring slot); the SMs one wave leaves idle
+  // cost (idle share) x (k-tiles) x 0.28 us against the ~4-5 us the exchange of a stream-K schedule costs at these sizes
+  const long long tiny_tiles = (long long)((M + dg::TINY_BM - 1) / dg::TINY_BM) * ((N + dg::TINY_BN - 1) / dg::TINY_BN);
+  if (tiny_tiles <= num_sms && env().tiny_gain_us > 0.0) {
+    const double k_tiles = (K + dg::BK - 1) / dg::BK;
+    if ((double)(num_sms - tiny_tiles) / num_sms * k_tiles * 0.28 < env().tiny_gain_us) return dg::TILE_TINY;
+  }
   if (big_tiles >= env().mid_min_tiles && big_tiles <= env().mid_max_tiles && flops <= env().mid_max_flops) return dg::TILE_MID;
   return big_tiles <= env().small_max_tiles && flops <= env().small_max_flops ? env().small_ctas : dg::TILE_BIG;
 }
@@ -457,7 +474,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (variant == dg::VARIANT_TMA && !tma_ok && !split_ok)
     return fail(DGEMM_B200_ERR_BAD_ARG, "variant %d: unaligned operands need K >= 2 and N >= 2 for parity-split tensor maps", variant);
   fill_params(P, M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, splits, variant, c.num_sms,
-              auto_variant ? choose_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0) : 0);
+              auto_variant ? choose_tile(M, N, K, tma_ok || use_split, fetch.bytes != 0, c.num_sms) : 0);
   // CTA slots of the device for the kernel build that will run (the dg64x2 build keeps two CTAs per SM resident)
   const int cta_slots = P.tile_small == 2 ? dg::SMALL_X2_CTAS_PER_SM * c.num_sms : c.num_sms;
   const bool uses_ws = P.splits > 1 || P.sk_tiles > 0;
@@ -1322,7 +1339,7 @@ int dgemm_b200_plan(int M, int N, int K, const double* dA, long long lda, const 
                        !env().realign_min_set;
   const int v = (tma_ok || split || realign) ? dg::VARIANT_TMA : dg::VARIANT_CPASYNC8;
   fill_params(P, M, N, std::max(K, 1), 1.0, dA, lda, dB, ldb, 0.0, nullptr, std::max(M, 1), 0, v, c->num_sms,
-              choose_tile(M, N, std::max(K, 1), tma_ok || split || realign, false));
+              choose_tile(M, N, std::max(K, 1), tma_ok || split || realign, false, c->num_sms));
   if (variant) *variant = v;
   if (splits) *splits = P.splits;
   if (sk_tiles) *sk_tiles = P.sk_tiles;

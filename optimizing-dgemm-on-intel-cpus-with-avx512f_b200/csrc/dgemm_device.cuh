@@ -49,6 +49,15 @@ constexpr int BN = DG_BN;
 constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+// k-tiles per ring slot of the TMA kernel (one full / empty mbarrier pair per slot).  Every slot boundary costs a
+// sub-partition ~75 clk whatever the tile (profiles/r02_loop_with_and_without_tma.txt), which is 2 % of a 128 x 128 stage
+// but 15 % of a 64 x 32 one; with two k-tiles per slot the consumers cross half as many.  1 = the layout every shipped
+// kernel but the 64 x 32 build uses; `make libkps2` builds all of them with 2 for A/B timing.
+#ifndef DG_KT_PER_STAGE
+#define DG_KT_PER_STAGE 1
+#endif
+constexpr int KPS = DG_KT_PER_STAGE;
+constexpr int SLOT_BYTES = KPS * STAGE_BYTES;
 // Warp grid inside the CTA tile, a build-time switch (-DDG_WARPS_M=.. -DDG_WARPS_N=..):
 //   2 x 4 (default)  8 consumer warps, 64x32 warp tiles, 128 accumulator registers, 2 warps per SM sub-partition
 //   4 x 4            16 consumer warps, 32x32 warp tiles, 64 accumulator registers, 4 warps per SM sub-partition
@@ -377,6 +386,7 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
   const double alpha = P.alpha, beta = P.beta;
   const bool use_c = beta != 0.0;
   const int mbase = m0 + warp_m * WM + mq;
+  constexpr int HP = FRAG_N >= 2 ? 2 : 1;   // row fragments per pass of the fast paths (one when the warp tile is 8 columns wide)
   // Fast path (warp tile fully inside C, 16-byte aligned columns): straight-line code, 16 independent 16-byte loads
   // in flight per lane before the first use.  The predicated edge path below puts every load in its own basic
   // block, which serialises the round trips (measured: ~9 us per tile instead of ~2).
@@ -394,11 +404,11 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
         for (int j = 0; j < FRAG_M; j++) {
           const int o = (j >> 1) * 16 + (j & 1) * 4;
           c[0][j][0] = col0[o]; c[0][j][1] = col0[o + 1];
-          c[1][j][0] = col1[o]; c[1][j][1] = col1[o + 1];
+          if (HP == 2) { c[1][j][0] = col1[o]; c[1][j][1] = col1[o + 1]; }
         }
       }
 #pragma unroll
-      for (int h = 0; h < 2; h++) {
+      for (int h = 0; h < HP; h++) {
         double* col = h ? col1 : col0;
 #pragma unroll
         for (int j = 0; j < FRAG_M; j++) {
@@ -422,11 +432,11 @@ __device__ __forceinline__ void epilogue_store(const double (&acc)[FRAG_N][FRAG_
 #pragma unroll
         for (int j = 0; j < FRAG_M; j++) {
           c[0][j] = *reinterpret_cast<const double2*>(col0 + (j >> 1) * 16 + (j & 1) * 4);
-          c[1][j] = *reinterpret_cast<const double2*>(col1 + (j >> 1) * 16 + (j & 1) * 4);
+          if (HP == 2) c[1][j] = *reinterpret_cast<const double2*>(col1 + (j >> 1) * 16 + (j & 1) * 4);
         }
       }
 #pragma unroll
-      for (int h = 0; h < 2; h++) {
+      for (int h = 0; h < HP; h++) {
         double* col = h ? col1 : col0;
 #pragma unroll
         for (int j = 0; j < FRAG_M; j++) {

@@ -29,7 +29,7 @@ bool tma_split_ok(const Params& P);   // needs P.A, P.B, P.lda, P.ldb, P.K, P.N
 cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t stream, bool cooperative = false,
                         bool pdl = false);
 // CTAs of the TMA kernel the current device can hold at once; tile_small as in Params (0: 128 x 128, 1: dg64, 2: dg64x2, 3: dg128x64)
-int tma_coresident_capacity(int tile_small, int num_sms);
+int tma_coresident_capacity(int tile_small, int num_sms);   // (4: dg64x32)
 cudaError_t small_tile_occupancy(int* ctas_per_sm);
 cudaError_t small_tile_occupancy_x2(int* ctas_per_sm);
 void tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
@@ -47,9 +47,14 @@ constexpr int MID_BM = 128, MID_BN = 64;
 cudaError_t launch_tma_small_mid(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                                  cudaStream_t stream, bool cooperative, bool pdl);
 cudaError_t small_tile_occupancy_mid(int* ctas_per_sm);
-enum { TILE_BIG = 0, TILE_SMALL = 1, TILE_SMALL_X2 = 2, TILE_MID = 3 };   // Params::tile_small
-inline int tile_bm(int t) { return t == TILE_BIG ? 128 : (t == TILE_MID ? MID_BM : SMALL_BM); }
-inline int tile_bn(int t) { return t == TILE_BIG ? 128 : (t == TILE_MID ? MID_BN : SMALL_BN); }
+// the TMA kernel on 64 x 32 tiles (dgemm_kernels_tiny.cu); Params::tile_small == 4; B boxes 16 x 32, two k-tiles per ring slot
+constexpr int TINY_BM = 64, TINY_BN = 32;
+cudaError_t launch_tma_small_tiny(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
+                                  cudaStream_t stream, bool cooperative, bool pdl);
+cudaError_t small_tile_occupancy_tiny(int* ctas_per_sm);
+enum { TILE_BIG = 0, TILE_SMALL = 1, TILE_SMALL_X2 = 2, TILE_MID = 3, TILE_TINY = 4, TILE_COUNT = 5 };   // Params::tile_small
+inline int tile_bm(int t) { return t == TILE_BIG ? 128 : (t == TILE_MID ? MID_BM : (t == TILE_TINY ? TINY_BM : SMALL_BM)); }
+inline int tile_bn(int t) { return t == TILE_BIG ? 128 : (t == TILE_MID ? MID_BN : (t == TILE_TINY ? TINY_BN : SMALL_BN)); }
 cudaError_t launch_ladder(const Params& P, int variant, cudaStream_t stream);
 cudaError_t launch_tma_cluster(const void* const maps[2], const Params& P, int num_sms, cudaStream_t stream);
 cudaError_t launch_scale_c(double* C, int M, int N, long long ldc, double beta, int num_sms, cudaStream_t stream);

@@ -320,7 +320,7 @@ int launch_count() { return g_launches.load(std::memory_order_relaxed); }
 void reset_launch_count() { g_launches.store(0, std::memory_order_relaxed); }
 
 #ifndef DG_TMA_STAGES
-#define DG_TMA_STAGES 6
+#define DG_TMA_STAGES (6 / DG_KT_PER_STAGE)   // ring slots of KPS k-tiles each: 192 KB of operands in flight
 #endif
 constexpr int TMA_STAGES = DG_TMA_STAGES;
 constexpr int CPA_STAGES = 4;
@@ -333,9 +333,9 @@ static cudaError_t set_smem(Kern k, int bytes) {
 // how many CTAs of the TMA kernel (either tile size, any split variant: same block size and shared memory) can be
 // resident on the current device at once; what a grid whose CTAs wait on each other must not exceed
 int tma_coresident_capacity(int tile_small, int num_sms) {
-  static std::atomic<int> per_sm[4][64];
+  static std::atomic<int> per_sm[TILE_COUNT][64];
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || tile_small < 0 || tile_small > 3) return 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || tile_small < 0 || tile_small >= TILE_COUNT) return 0;
   std::atomic<int>& slot = per_sm[tile_small][dev & 63];
   int n = slot.load(std::memory_order_relaxed);
   if (n == 0) {
@@ -343,8 +343,9 @@ int tma_coresident_capacity(int tile_small, int num_sms) {
     if (tile_small == 1) e = small_tile_occupancy(&n);
     else if (tile_small == 2) e = small_tile_occupancy_x2(&n);
     else if (tile_small == 3) e = small_tile_occupancy_mid(&n);
+    else if (tile_small == TILE_TINY) e = small_tile_occupancy_tiny(&n);
     else {
-      const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
+      const int smem = TMA_STAGES * SLOT_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
       e = set_smem(dgemm_tma_ws_kernel<TMA_STAGES>, smem);
       if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, dgemm_tma_ws_kernel<TMA_STAGES>, TMA_THREADS, smem);
     }
@@ -403,10 +404,11 @@ cudaError_t launch_gemm(const Params& P, int variant, int num_sms, cudaStream_t 
       const void* maps[4] = {&tmA, &tmA1, &tmB, &tmB1};
       g_launches++;
       if (P.tile_small == TILE_MID) return launch_tma_small_mid(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
+      if (P.tile_small == TILE_TINY) return launch_tma_small_tiny(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
       return P.tile_small == 2 ? launch_tma_small_x2(maps, split, Q, grid, dp_units, stream, cooperative, pdl)
                                : launch_tma_small(maps, split, Q, grid, dp_units, stream, cooperative, pdl);
     }
-    const int smem = TMA_STAGES * STAGE_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
+    const int smem = TMA_STAGES * SLOT_BYTES + 2 * TMA_STAGES * 8 + 16 + 1024;
     static std::atomic<bool> attr_done[64];  // function attributes are per device
     int dev = 0;
     if ((err = cudaGetDevice(&dev)) != cudaSuccess) return err;

@@ -13,6 +13,6 @@
 #define DG_BN 64
 #define DG_WARPS_M 4
 #define DG_WARPS_N 2
-#define DG_SMALL_STAGES 8   // 8 x 24 KB = 192 KB in flight, as the big tile's 6 x 32 KB
+#define DG_SMALL_STAGES (8 / DG_KT_PER_STAGE)   // 8 x 24 KB = 192 KB in flight, as the big tile's 6 x 32 KB
 #define DG_SMALL_FN(name) name##_mid
 #include "dgemm_small_tile.cuh"

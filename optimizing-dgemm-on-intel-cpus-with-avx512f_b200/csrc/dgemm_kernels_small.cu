@@ -13,6 +13,6 @@
 // Two builds of it (dgemm_small_tile.cuh): this one keeps ONE CTA per SM with 8 pipeline stages; dgemm_kernels_small2.cu
 // runs TWO CTAs per SM with 4 stages each, so that one CTA's epilogue / partial exchange overlaps the other's main loop.
 #define DG_NAMESPACE dg64
-#define DG_SMALL_STAGES 8   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
+#define DG_SMALL_STAGES (8 / DG_KT_PER_STAGE)   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
 #define DG_SMALL_FN(name) name
 #include "dgemm_small_tile.cuh"

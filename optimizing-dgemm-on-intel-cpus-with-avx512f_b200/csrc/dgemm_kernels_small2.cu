@@ -19,7 +19,7 @@
 // and their fix-up together and finish together, so there is little for one to overlap with in the other; the DMMA pipe
 // is busy 76 % of the elapsed cycles (83 % of the active ones), as before.  Kept selectable, not the default.  The reference has no counterpart (one thread per core, kernel19.h:678-755).
 #define DG_NAMESPACE dg64x2
-#define DG_SMALL_STAGES 4
+#define DG_SMALL_STAGES (4 / DG_KT_PER_STAGE)
 #define DG_MIN_CTAS 2
 #define DG_PRODUCER_REGS 40
 #define DG_CONSUMER_REGS 96

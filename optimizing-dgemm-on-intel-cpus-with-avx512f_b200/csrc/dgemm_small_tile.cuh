@@ -18,12 +18,13 @@
 namespace dg {
 
 namespace ks = DG_NAMESPACE;
-static_assert((ks::BM == SMALL_BM && ks::BN == SMALL_BN) || (ks::BM == MID_BM && ks::BN == MID_BN),
+static_assert((ks::BM == SMALL_BM && ks::BN == SMALL_BN) || (ks::BM == MID_BM && ks::BN == MID_BN) ||
+                  (ks::BM == TINY_BM && ks::BN == TINY_BN),
               "dgemm_host.h must state the tile's size");
 
 namespace {
 constexpr int SMALL_STAGES = DG_SMALL_STAGES;
-constexpr int SMALL_SMEM = SMALL_STAGES * ks::STAGE_BYTES + 2 * SMALL_STAGES * 8 + 16 + 1024;
+constexpr int SMALL_SMEM = SMALL_STAGES * ks::SLOT_BYTES + 2 * SMALL_STAGES * 8 + 16 + 1024;
 
 cudaError_t small_attrs() {
   constexpr int STAGES = SMALL_STAGES;

@@ -45,7 +45,17 @@ constexpr long long SKEW_CLK = CONSUMER_WARPS == 8 ? (long long)FRAG_M * FRAG_N 
 #ifndef DG_KT_UNROLL
 #define DG_KT_UNROLL 0
 #endif
+#ifndef DG_EARLY_DESC_PREFETCH
+#define DG_EARLY_DESC_PREFETCH 0
+#endif
 constexpr int KT_UNROLL = DG_KT_UNROLL > 0 ? DG_KT_UNROLL : 1;
+// Two accumulator sets per warp (even / odd k-steps, added once per segment): with a 16 x 16 warp tile a warp owns only four
+// accumulators, so every DMMA of a k-step waits for the same accumulator's DMMA of the previous one (26 clk) unless the
+// other warp of the sub-partition fills the gap; the second set doubles the distance.  Only for tiles whose accumulators
+// are few (the 64 x 32 build); changes the order of the sums inside a tile (same bound, still deterministic).
+#ifndef DG_DUAL_ACC
+#define DG_DUAL_ACC 0
+#endif
 constexpr int SYNC_SLACK = 2;  // k-lockstep: a producer may run this many sync points ahead of the slowest CTA
 enum { SEG_DIRECT = 0, SEG_SPLITK = 1, SEG_SK_OWNER = 2, SEG_SK_CONTRIB = 3 };
 
@@ -97,11 +107,17 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by SWIZZLE_128B; dynamic smem base is only guaranteed 16 B -> round up
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bars = smem_base + STAGES * STAGE_BYTES;  // full[STAGES] then empty[STAGES], 8 B each
+  const uint32_t bars = smem_base + STAGES * SLOT_BYTES;  // full[STAGES] then empty[STAGES], 8 B each (STAGES ring slots of KPS k-tiles)
   const uint32_t progress = bars + 16 * STAGES;            // segments the producer has started (paces the C prefetch)
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   if (tid == 0) stamp(P, 0);   // (debug timeline only; the one global write ahead of griddep_wait, into its own buffer)
+#if DG_EARLY_DESC_PREFETCH
+  // the descriptors are kernel parameters, not data of an earlier kernel: their fetch may start before the barriers exist
+  if constexpr (SPLIT == SPLIT_NONE) {
+    if (tid == CONSUMER_THREADS) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+  }
+#endif
 
   if (tid == 0) {
 #pragma unroll
@@ -124,10 +140,12 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
     // ------------------------------- producer warpgroup: one elected lane issues TMA --------------------------
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(PRODUCER_REGS));
     if (warp == CONSUMER_WARPS && lane == 0) {
+#if !DG_EARLY_DESC_PREFETCH
       if constexpr (SPLIT == SPLIT_NONE) {   // (a split kernel may have been handed a dummy map for a misaligned parity)
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
       }
+#endif
       // bytes per stage that arrive by TMA (the misaligned parity halves come from the helper warps)
       uint32_t tx_bytes = STAGE_BYTES;
       if constexpr ((SPLIT & SPLIT_A) != 0) tx_bytes -= (uint32_t)(P.a_mis[0] + P.a_mis[1]) * (A_STAGE_BYTES / 2);
@@ -152,16 +170,26 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
             point++;
             next_sync += P.sync_kt;
           }
-          mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
+          // k-tile number `sub` of its ring slot; the slot's barrier is armed once, for all the k-tiles it will hold
+          const int sub = KPS == 1 ? 0 : (kt - sg.kb) % KPS;
+          const bool slot_done = KPS == 1 || sub == KPS - 1 || kt + 1 == sg.ke;
           const uint32_t full = bars + 8 * s;
-          const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
+          const uint32_t dstA = smem_base + s * SLOT_BYTES + sub * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
+          if (sub == 0) mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);  // slot free?
 #ifdef DG_DEBUG_NO_TMA
           // measurement build only (make libdbg): the stage is handed over without loading anything, so the consumers'
           // loop runs against barriers that are always ready -- separates "waiting for operands" from the loop's own cost
-          if constexpr (SPLIT == SPLIT_NONE) { mbar_arrive(full); if (++s == STAGES) { s = 0; ph ^= 1; } continue; }
+          if constexpr (SPLIT == SPLIT_NONE) {
+            if (sub == 0) mbar_arrive(full);
+            if (slot_done && ++s == STAGES) { s = 0; ph ^= 1; }
+            continue;
+          }
 #endif
-          if constexpr (SPLIT == SPLIT_NONE) mbar_arrive_expect_tx(full, STAGE_BYTES);
-          else mbar_arrive_expect_tx(full, tx_bytes);
+          if (sub == 0) {
+            const uint32_t n_kt = KPS == 1 ? 1u : (uint32_t)min(KPS, sg.ke - kt);
+            if constexpr (SPLIT == SPLIT_NONE) mbar_arrive_expect_tx(full, n_kt * STAGE_BYTES);
+            else mbar_arrive_expect_tx(full, n_kt * tx_bytes);
+          }
           const int k0 = kt * BK;
           if constexpr ((SPLIT & SPLIT_A) != 0) {
             // A by k parity: per 16-row sub-tile one box of 16(m) x 8(even k) into rows 0..7, one of the odd k into 8..15
@@ -182,7 +210,7 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           } else {
             tma_load_2d(dstB, &tmB, full, k0, n0);   // B: one box of 16(k) x 128(n)
           }
-          if (++s == STAGES) { s = 0; ph ^= 1; }
+          if (slot_done && ++s == STAGES) { s = 0; ph ^= 1; }
         }
         if (sg.kind == SEG_SK_OWNER && !P.sk_parallel) {
           // serial stream-K fix-up: the partials of the ranges that hold the rest of this tile come in through the
@@ -200,7 +228,7 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
               mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
               const uint32_t full = bars + 8 * s;
               mbar_arrive_expect_tx(full, PARTIAL_CHUNK_BYTES);
-              bulk_load_1d(smem_base + s * STAGE_BYTES, src + (size_t)c * PARTIAL_CHUNK_BYTES, PARTIAL_CHUNK_BYTES, full);
+              bulk_load_1d(smem_base + s * SLOT_BYTES, src + (size_t)c * PARTIAL_CHUNK_BYTES, PARTIAL_CHUNK_BYTES, full);
               if (++s == STAGES) { s = 0; ph ^= 1; }
             }
           }
@@ -227,7 +255,7 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           decode_tile(P, sg.tile, tm, tn);
           const int m0 = tm * BM, n0 = tn * BN;
           for (int i = lane; i < BN * (BM / 16); i += 32) {   // one 128-byte line (16 doubles) per prefetch
-            const int n = n0 + (i >> 3), m = m0 + ((i & 7) << 4);
+            const int n = n0 + i / (BM / 16), m = m0 + (i % (BM / 16)) * 16;
             if (n < P.N && m < P.M)
               asm volatile("prefetch.global.L2 [%0];" ::"l"(P.C + (long long)n * P.ldc + m));
           }
@@ -249,8 +277,10 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           const int m0 = tm * BM, n0 = tn * BN;
 #pragma unroll 1
           for (int kt = sg.kb; kt < sg.ke; kt++) {
-            mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
-            const uint32_t dstA = smem_base + s * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
+            const int sub = KPS == 1 ? 0 : (kt - sg.kb) % KPS;
+            const bool slot_done = KPS == 1 || sub == KPS - 1 || kt + 1 == sg.ke;
+            if (sub == 0) mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
+            const uint32_t dstA = smem_base + s * SLOT_BYTES + sub * STAGE_BYTES, dstB = dstA + A_STAGE_BYTES;
             const int k0 = kt * BK;
             if constexpr ((SPLIT & SPLIT_A) != 0) {
 #pragma unroll 1
@@ -262,8 +292,10 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
               for (int p = 0; p < 2; p++)
                 if (P.b_mis[p]) helper_copy_b_half(P, dstB, n0, k0, p, t);
             }
-            cp_async_mbar_arrive_noinc(bars + 8 * s);
-            if (++s == STAGES) { s = 0; ph ^= 1; }
+            if (slot_done) {   // one arrival per helper thread and slot, behind the copies of all its k-tiles
+              cp_async_mbar_arrive_noinc(bars + 8 * s);
+              if (++s == STAGES) { s = 0; ph ^= 1; }
+            }
           }
           if (sg.kind == SEG_SK_OWNER && !P.sk_parallel) {
             const long long total = (long long)P.sk_tiles * P.k_tiles;
@@ -306,6 +338,12 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
     typename LaneOffsetsFor<SPLIT>::type lo;
     make_lane_offsets_t(lo, lane, warp_m, warp_n);
     double acc[FRAG_N][FRAG_M][2];
+#if DG_DUAL_ACC
+    double acc_odd[FRAG_N][FRAG_M][2];
+#define DG_ACC_ODD acc_odd
+#else
+#define DG_ACC_ODD acc
+#endif
     Frags f0, f1;
     uint32_t s = 0, ph = 0;
     SegmentWalker walk(P, num_units);
@@ -315,6 +353,9 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
     int fix_tile[2] = {-1, -1};  // parallel fix-up: tiles this range holds a partial of (head, tail)
     while (walk.next(P, sg)) {
       zero_acc(acc);
+#if DG_DUAL_ACC
+      zero_acc(acc_odd);
+#endif
       if (sg.kb < sg.ke) {
         // software pipeline over k-steps: the fragments of step i+1 are loaded while the 32 DMMAs of step i issue,
         // INCLUDING across the stage boundary (wait on the next stage's barrier before the last DMMA group)
@@ -330,33 +371,45 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
             while (clock64() - t0 < SKEW_CLK) {}
           }
         }
-        load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
+        load_frags(f0, smem_base + s * SLOT_BYTES, smem_base + s * SLOT_BYTES + A_STAGE_BYTES, lo, 0);
+        int sub = 0;   // k-tile of the current ring slot (KPS > 1 only)
 #if DG_KT_UNROLL > 0   // measurement builds only (make libunroll); left to ptxas otherwise (it unrolls the 64 x 64 loop by 2)
 #pragma unroll KT_UNROLL
 #endif
         for (int kt = sg.kb; kt < sg.ke; kt++) {
-          const uint32_t sA = smem_base + s * STAGE_BYTES, sB = sA + A_STAGE_BYTES;
+          const uint32_t sA = smem_base + s * SLOT_BYTES + (KPS == 1 ? 0 : sub * STAGE_BYTES), sB = sA + A_STAGE_BYTES;
           const uint32_t cur_empty = bars + 8 * (STAGES + s);
-          if (++s == STAGES) { s = 0; ph ^= 1; }
           const bool has_next = kt + 1 < sg.ke;
+          // boundary: this k-tile is the last one of its slot -- only then is there a barrier to probe and a slot to give back
+          const bool boundary = KPS == 1 || sub == KPS - 1 || !has_next;
+          if (boundary) { sub = 0; if (++s == STAGES) { s = 0; ph ^= 1; } } else { sub++; }
+          const uint32_t nA = smem_base + s * SLOT_BYTES + (KPS == 1 ? 0 : sub * STAGE_BYTES);   // where the next k-tile lies
           load_frags(f1, sA, sB, lo, 1);
           mma_frags(acc, f0);
           load_frags(f0, sA, sB, lo, 2);
-          mma_frags(acc, f1);
+          mma_frags(DG_ACC_ODD, f1);
           load_frags(f1, sA, sB, lo, 3);
           // probe the NEXT stage's barrier AFTER this stage's last loads (its acquire would hold them back) and
           // consume the answer one DMMA group (32 x 16 clk) later
-          const uint32_t next_ready = has_next ? mbar_test_wait(bars + 8 * s, ph) : 0u;
+          const uint32_t next_ready = (has_next && boundary) ? mbar_test_wait(bars + 8 * s, ph) : (boundary ? 0u : 1u);
           mma_frags(acc, f0);
           if (has_next) {
             if (!next_ready) mbar_wait(bars + 8 * s, ph);  // rare: the producer normally runs stages ahead
-            load_frags(f0, smem_base + s * STAGE_BYTES, smem_base + s * STAGE_BYTES + A_STAGE_BYTES, lo, 0);
+            load_frags(f0, nA, nA + A_STAGE_BYTES, lo, 0);
           }
-          mma_frags(acc, f1);  // consumes the last fragments read from the current stage ...
-          __syncwarp();
-          if (lane == 0) mbar_arrive(cur_empty);  // ... so the slot can go back to the producer
+          mma_frags(DG_ACC_ODD, f1);  // consumes the last fragments read from the current stage ...
+          if (boundary) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(cur_empty);  // ... so the slot can go back to the producer
+          }
         }
       }
+#if DG_DUAL_ACC
+#pragma unroll
+      for (int i = 0; i < FRAG_N; i++)
+#pragma unroll
+        for (int j = 0; j < FRAG_M; j++) { acc[i][j][0] += acc_odd[i][j][0]; acc[i][j][1] += acc_odd[i][j][1]; }
+#endif
       int tm, tn;
       decode_tile(P, sg.tile, tm, tn);
       if (tid == 0) stamp(P, tslot++);     // main loop of the segment done
@@ -385,7 +438,7 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
 #pragma unroll
           for (int c = 0; c < PARTIAL_CHUNKS; c++) {   // the producer fetched partial r into four stages of the ring
             mbar_wait(bars + 8 * s, ph);
-            add_partial_smem(acc, smem_base + s * STAGE_BYTES, c, tid);
+            add_partial_smem(acc, smem_base + s * SLOT_BYTES, c, tid);
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (STAGES + s));
             if (++s == STAGES) { s = 0; ph ^= 1; }
@@ -490,4 +543,5 @@ dgemm_tma_ws_split_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_
   tma_ws_body<STAGES, SPLIT>(tmA, tmA1, tmB, tmB1, P, num_units);
 }
 
+#undef DG_ACC_ODD
 }  // namespace DG_NAMESPACE

@@ -300,6 +300,54 @@ def test_mid_tile_build(dg, monkeypatch, case):
         dg.reload_env()
 
 
+@pytest.mark.parametrize("sk", [False, True])
+@pytest.mark.parametrize("case", [((64, 32, 16), (0, 0, 0), 1.0, 1.0), ((256, 256, 256), (0, 0, 0), 1.0, 1.0),
+                                  ((512, 512, 512), (0, 0, 0), 2.5, 0.5),          # 128 whole tiles, one wave
+                                  ((512, 512, 517), (0, 0, 0), 1.0, 1.0),          # odd number of k-tiles: a half-filled ring slot
+                                  ((500, 501, 499), (0, 0, 0), -1.0, 1.0),         # odd LDB: parity-split kernel of the build
+                                  ((500, 501, 499), (7, 7, 7), 1.5, 0.0),          # odd LDA, beta = 0 over NaN
+                                  ((501, 499, 503), (1, 1, 1), 1.0, 1.0),          # both operands split, odd LDC
+                                  ((640, 640, 640), (0, 0, 0), 1.0, 1.0),          # 200 tiles: a wave + stream-K tail
+                                  ((1000, 1003, 997), (0, 0, 0), 1.0, 1.0),
+                                  ((300, 700, 64), (2, 0, 0), 1.0, 1.0), ((65, 33, 4096), (0, 0, 0), 1.0, 0.5),
+                                  ((64, 64, 8192), (0, 0, 0), 1.0, 1.0),           # 2 tiles: with TINY_SK many ranges per tile
+                                  ((7, 9, 33), (0, 0, 0), 1.0, 1.0)])
+def test_tiny_tile_build(dg, monkeypatch, case, sk):
+    """DGEMM_B200_TILE=tiny: the TMA kernel compiled for 64 x 32 CTA tiles with 16 x 16 warp tiles and two k-tiles per ring
+    slot (csrc/dgemm_kernels_tiny.cu).  sk: DGEMM_B200_TINY_SK=1 lets a partial wave of these tiles be cut into stream-K
+    ranges (the build's default is one data-parallel wave).  Same bound as every other path; bit-identical run to run."""
+    (M, N, K), pad, alpha, beta = case
+    monkeypatch.setenv("DGEMM_B200_TILE", "tiny")
+    if sk:
+        monkeypatch.setenv("DGEMM_B200_TINY_SK", "1")
+    dg.reload_env()
+    try:
+        A, B, C0 = gu.make_inputs(M, N, K, pad, c_fill=np.nan if beta == 0.0 else None)
+        outs = []
+        for _ in range(2):
+            dA, dB, dC = gu.DevMat(dg, A), gu.DevMat(dg, B), gu.DevMat(dg, C0)
+            dg.dgemm_device(M, N, K, alpha, dA.ptr, dA.ld, dB.ptr, dB.ld, beta, dC.ptr, dC.ld)
+            assert dg.lib.dgemm_b200_sync(None) == 0, dg.last_error()
+            outs.append(dC.to_host())
+            dA.free(); dB.free(); dC.free()
+        if beta == 0.0:
+            C0[:M, :] = 0.0
+        gu.check(M, N, K, alpha, A, B, beta, C0, outs[0])
+        assert np.array_equal(outs[0], outs[1])
+    finally:
+        monkeypatch.delenv("DGEMM_B200_TILE")
+        if sk:
+            monkeypatch.delenv("DGEMM_B200_TINY_SK")
+        dg.reload_env()
+
+
+def test_auto_picks_the_tiny_tile_at_512(dg):
+    """512^3: 128 tiles of 64 x 32 in one data-parallel wave (no stream-K tiles, 128 CTAs), and the result is the oracle's."""
+    p = dg.plan(512, 512, 512)
+    assert p["ctas"] == 128 and p["stream_k_tiles"] == 0, p
+    assert gu.run_device(dg, 512, 512, 512, 1.0, 1.0) <= gu.BOUND_C
+
+
 def test_k_lockstep_changes_no_bits(dg, monkeypatch):
     """Large enough for the k-lockstep of the data-parallel waves (2 full waves, operands > 96 MB, K >= 4096): the
     producers' pacing must not change a single bit, twice in a row (the counters are re-zeroed per launch), and the

@@ -11,7 +11,10 @@ dA, dB, dC = dg.malloc(8 * M * K), dg.malloc(8 * K * N), dg.malloc(8 * M * N)
 dg.fill_signed(dA, M, K, M, 1); dg.fill_signed(dB, K, N, K, 2); dg.fill_signed(dC, M, N, M, 3)
 tl = dg.malloc(8 * ROWS * 16)
 host = np.zeros((ROWS, 16), dtype=np.uint64)
+FLUSH = int(os.environ.get("TL_FLUSH_MB", "0")) << 20   # > 0: evict the operands from L2 before every rep (as the sweep does)
+fl = dg.malloc(FLUSH) if FLUSH else 0
 for rep in range(3):
+    if FLUSH: dg.fill_signed(fl, FLUSH // 8, 1, FLUSH // 8, rep)
     dg.lib.dgemm_b200_h2d(tl, ROWS * 16, host.ctypes.data, ROWS * 16, ROWS * 16, 1, None)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(tl)
