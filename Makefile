@@ -62,6 +62,8 @@ TINY_FLAGS_latedesc := -DDG_TINY_EARLY_DESC=0
 TINY_FLAGS_plain    := -DDG_TINY_DUAL_ACC=0 -DDG_TINY_EARLY_DESC=0
 TINY_FLAGS_w16      := -DDG_TINY_WARPS16=1
 TINY_FLAGS_w4       := -DDG_TINY_WARPS4=1
+TINY_FLAGS_notma    := -DDG_DEBUG_NO_TMA
+TINY_FLAGS_w4notma  := -DDG_TINY_WARPS4=1 -DDG_DEBUG_NO_TMA
 libtiny: $(foreach n,kps2 nodual latedesc plain w16 w4,$(PKG)/libdgemm_b200_tiny_$(n).so)
 $(PKG)/libdgemm_b200_tiny_%.so: $(LIB_OBJS) $(CSRC)/dgemm_kernels_tiny.cu $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) $(TINY_FLAGS_$*) -c -o $(OBJDIR)/tiny_$*.o $(CSRC)/dgemm_kernels_tiny.cu

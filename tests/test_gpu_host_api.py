@@ -53,6 +53,42 @@ def test_v20_tiny_calls_take_the_latency_path(dg, shape, pad, alpha, beta):
     assert np.isfinite(Cg[:M, :]).all()
 
 
+def test_v20_concurrent_callers_are_serialised(dg):
+    """Four host threads call mydgemm_gpu_v20 at once on their own operands (ctypes drops the GIL for the call): the
+    library serialises whole calls behind one process-wide mutex (include/dgemm_b200.h:21, SURVEY.md section 8 b6: the reference is
+    re-entrant because it owns no state; this library owns device buffers, streams and a workspace), so every caller
+    must get ITS result, inside the bound, and its own status -- a failing call in one thread must not leak into another's
+    dgemm_b200_last_status()."""
+    import threading
+    shapes = [(600, 500, 700), (512, 512, 512), (1000, 1003, 997), (300, 2000, 64)]
+    cases = [gu.make_inputs(M, N, K, seed=10 + i) for i, (M, N, K) in enumerate(shapes)]
+    outs = [c[2].copy(order="F") for c in cases]
+    errors = []
+
+    def work(i):
+        try:
+            M, N, K = shapes[i]
+            A, B, _ = cases[i]
+            for _ in range(3):
+                outs[i][:] = cases[i][2]
+                dg.mydgemm_gpu_v20(M, N, K, 1.5, A, A.shape[0], B, B.shape[0], 0.5, outs[i], outs[i].shape[0])
+            if i == 0:   # a bad call (LDA < M) on this thread only
+                with pytest.raises(dg.DgemmError):
+                    dg.mydgemm_gpu_v20(M, N, K, 1.0, A, M - 1, B, B.shape[0], 0.0, outs[i].copy(order="F"), M)
+            else:
+                assert dg.lib.dgemm_b200_last_status() == 0
+        except BaseException as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(shapes))]
+    for t in threads: t.start()
+    for t in threads: t.join()
+    assert not errors, errors
+    for i, (M, N, K) in enumerate(shapes):
+        A, B, C0 = cases[i]
+        gu.check(M, N, K, 1.5, A, B, 0.5, C0, outs[i])
+
+
 def test_test_kernel_dispatch(dg):
     m = n = k = 400
     A, B, C0 = gu.make_inputs(m, n, k, dist="reference")
