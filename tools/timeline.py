@@ -39,3 +39,8 @@ for i in range(4):   # per-CTA main-loop duration of segment i (landed -> loop e
     if not np.all(np.isnan(d)):
         print(f"seg{i} loop duration  min {np.nanmin(d):8.2f}  median {np.nanmedian(d):8.2f}  max {np.nanmax(d):8.2f} us")
 print("kernel span (first entry -> last stamp): %.2f us" % np.nanmax(rel))
+if os.environ.get("TL_DUMP"):   # raw per-CTA stamps (us relative to the first entry; NaN = not stamped), CTA = row
+    import json
+    json.dump({"M": M, "N": N, "K": K, "plan": dg.plan(M, N, K, dA, M, dB, K), "names": names,
+               "stamps_us": [[None if np.isnan(v) else round(float(v), 3) for v in row] for row in rel]},
+              open(os.environ["TL_DUMP"], "w"))
