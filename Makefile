@@ -33,6 +33,14 @@ libdbg: $(PKG)/libdgemm_b200_dbg_notma.so
 $(PKG)/libdgemm_b200_dbg_notma.so: $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -DDG_DEBUG_NO_TMA -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
 
+# measurement builds: timeline stamps in SM cycles (clock64) instead of nanoseconds, with and without TMA; tools/timeline.py
+# then prints kilo-cycles where it says us (per-CTA differences only: the counters of different SMs are not aligned)
+libclk: $(PKG)/libdgemm_b200_clk.so $(PKG)/libdgemm_b200_clk_notma.so
+$(PKG)/libdgemm_b200_clk.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_STAMP_CLOCK64 -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+$(PKG)/libdgemm_b200_clk_notma.so: $(LIB_SRCS) $(LIB_HDRS)
+	$(NVCC) $(NVFLAGS) -DDG_STAMP_CLOCK64 -DDG_DEBUG_NO_TMA -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
+
 # measurement builds: the two consumer warps of a sub-partition skewed by n/64 of a stage (DG_SKEW_64THS)
 SKEWS ?= 2 4 8 12 16
 libskew: $(foreach n,$(SKEWS),$(PKG)/libdgemm_b200_skew$(n).so)
@@ -95,4 +103,4 @@ sass: $(LIB)
 clean:
 	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
 	$(MAKE) -C oracle clean
-.PHONY: all build lib lib16 libdbg libkps libtiny probe stage_probe harness oracle sass clean
+.PHONY: all build lib lib16 libdbg libkps libtiny libclk probe stage_probe harness oracle sass clean

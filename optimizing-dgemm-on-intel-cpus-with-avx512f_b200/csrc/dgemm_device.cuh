@@ -95,7 +95,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 __device__ __forceinline__ void stamp(const Params& P, int slot) {
+#ifdef DG_STAMP_CLOCK64   // measurement build (make libclk): SM cycles instead of nanoseconds -- differences inside ONE CTA only
+  if (P.timeline && slot < 16) P.timeline[blockIdx.x * 16 + slot] = (unsigned long long)clock64();
+#else
   if (P.timeline && slot < 16) P.timeline[blockIdx.x * 16 + slot] = globaltimer_ns();
+#endif
 }
 
 // ---- lane -> matrix index maps (see header comment) -------------------------------------------------------

@@ -13,6 +13,9 @@
 // Two builds of it (dgemm_small_tile.cuh): this one keeps ONE CTA per SM with 8 pipeline stages; dgemm_kernels_small2.cu
 // runs TWO CTAs per SM with 4 stages each, so that one CTA's epilogue / partial exchange overlaps the other's main loop.
 #define DG_NAMESPACE dg64
+#ifndef DG_KT_UNROLL
+#define DG_KT_UNROLL 1   // the k-tile loop NOT unrolled: left alone, nvcc unrolls this build's loop by two and a whole tile of 128 k-tiles
+#endif                   // takes 141.1 kclk instead of 136.2 (profiles/r02_kt_unroll_clk.txt); the other builds keep the compiler's choice
 #define DG_SMALL_STAGES (8 / DG_KT_PER_STAGE)   // 8 x 16 KB: the same 128 KB in flight as four stages of the big tile
 #define DG_SMALL_FN(name) name
 #include "dgemm_small_tile.cuh"

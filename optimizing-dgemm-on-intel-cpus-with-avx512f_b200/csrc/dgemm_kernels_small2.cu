@@ -19,6 +19,9 @@
 // and their fix-up together and finish together, so there is little for one to overlap with in the other; the DMMA pipe
 // is busy 76 % of the elapsed cycles (83 % of the active ones), as before.  Kept selectable, not the default.  The reference has no counterpart (one thread per core, kernel19.h:678-755).
 #define DG_NAMESPACE dg64x2
+#ifndef DG_KT_UNROLL
+#define DG_KT_UNROLL 1   // the k-tile loop NOT unrolled: left alone, nvcc unrolls this build's loop by two and a whole tile of 128 k-tiles
+#endif                   // takes 141.1 kclk instead of 136.2 (profiles/r02_kt_unroll_clk.txt); the other builds keep the compiler's choice
 #define DG_SMALL_STAGES (4 / DG_KT_PER_STAGE)
 #define DG_MIN_CTAS 2
 #define DG_PRODUCER_REGS 40

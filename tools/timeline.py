@@ -18,7 +18,7 @@ for rep in range(3):
     dg.lib.dgemm_b200_h2d(tl, ROWS * 16, host.ctypes.data, ROWS * 16, ROWS * 16, 1, None)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(tl)
-    dg.dgemm_device(M, N, K, 1.0, dA, M, dB, K, 1.0, dC, M, 0, int(os.environ.get("TL_VARIANT", "1")), splits)
+    dg.dgemm_device(M, N, K, 1.0, dA, M, dB, K, float(os.environ.get("TL_BETA", "1.0")), dC, M, 0, int(os.environ.get("TL_VARIANT", "1")), splits)
     dg.lib.dgemm_b200_sync(None)
     dg.lib.dgemm_b200_debug_timeline(None)
 out = np.zeros((ROWS, 16), dtype=np.uint64)
