@@ -45,6 +45,12 @@ constexpr long long SKEW_CLK = CONSUMER_WARPS == 8 ? (long long)FRAG_M * FRAG_N 
 #ifndef DG_KT_UNROLL
 #define DG_KT_UNROLL 0
 #endif
+#ifndef DG_UNIFORM_PROBE
+#define DG_UNIFORM_PROBE 0
+#endif
+#ifndef DG_NO_SYNCWARP_ARRIVE
+#define DG_NO_SYNCWARP_ARRIVE 0
+#endif
 #ifndef DG_EARLY_DESC_PREFETCH
 #define DG_EARLY_DESC_PREFETCH 0
 #endif
@@ -391,7 +397,13 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           load_frags(f1, sA, sB, lo, 3);
           // probe the NEXT stage's barrier AFTER this stage's last loads (its acquire would hold them back) and
           // consume the answer one DMMA group (32 x 16 clk) later
+#if DG_UNIFORM_PROBE
+          // the probe's answer made warp-uniform by a vote: the branch on it is then a uniform one and no reconvergence
+          // point sits in front of the next DMMA group (tools/loop_bubble_probe2.cu mode 8: 4138 -> 4118 clk per k-tile)
+          const uint32_t next_ready = __all_sync(0xffffffffu, (has_next && boundary) ? mbar_test_wait(bars + 8 * s, ph) : (boundary ? 0u : 1u));
+#else
           const uint32_t next_ready = (has_next && boundary) ? mbar_test_wait(bars + 8 * s, ph) : (boundary ? 0u : 1u);
+#endif
           mma_frags(acc, f0);
           if (has_next) {
             if (!next_ready) mbar_wait(bars + 8 * s, ph);  // rare: the producer normally runs stages ahead
@@ -399,7 +411,9 @@ __device__ __forceinline__ void tma_ws_body(const CUtensorMap& tmA, const CUtens
           }
           mma_frags(DG_ACC_ODD, f1);  // consumes the last fragments read from the current stage ...
           if (boundary) {
+#if !DG_NO_SYNCWARP_ARRIVE
             __syncwarp();
+#endif
             if (lane == 0) mbar_arrive(cur_empty);  // ... so the slot can go back to the producer
           }
         }

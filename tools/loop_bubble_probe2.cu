@@ -5,6 +5,8 @@
 //   mode 0  bare loop on stage 0            mode 1  + ring addressing        mode 2  + release (syncwarp, lane 0 arrives)
 //   mode 3  + acquire = the kernel's loop   mode 6  mode 3 in a 12-warp block with the kernel's setmaxnreg split
 //   mode 7  mode 6 + warp 9 polling a shared word with nanosleep (the C prefetch warp), warps 10-11 exit at once
+//   mode 8  mode 7 with the probe's answer made warp-uniform by a vote (no divergent branch in front of the next DMMA group)
+//   mode 9  mode 7 without __syncwarp() in front of the elected arrive (the last mma.sync is the convergence point)
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -DDG_BM=128 -DDG_BN=128 [-DDG_WARPS_M=.. -DDG_WARPS_N=..]
 //        -DPROBE_STAGES=6 -o loop_bubble_probe2_big tools/loop_bubble_probe2.cu
 #include "../optimizing-dgemm-on-intel-cpus-with-avx512f_b200/csrc/dgemm_device.cuh"
@@ -93,13 +95,14 @@ probe_kernel(double* out, unsigned long long* cyc, int iters) {
     load_frags(f1, sA, sB, lo, 3);
     uint32_t next_ready = 1u;
     if (MODE >= 3) next_ready = has_next ? mbar_test_wait(bars + 8 * s, ph) : 0u;
+    if (MODE == 8) next_ready = __all_sync(0xffffffffu, next_ready);
     mma_frags(acc, f0);
     if (has_next) {
       if (MODE >= 3) { if (!next_ready) mbar_wait(bars + 8 * s, ph); }
       load_frags(f0, nA, nA + A_STAGE_BYTES, lo, 0);
     }
     mma_frags(acc, f1);
-    if (MODE >= 2) { __syncwarp(); if (lane == 0) mbar_arrive(cur_empty); }
+    if (MODE >= 2) { if (MODE != 9) __syncwarp(); if (lane == 0) mbar_arrive(cur_empty); }
   }
   const unsigned long long c1 = clock64();
   double sum = 0;
@@ -140,6 +143,6 @@ int main(int argc, char** argv) {
   double* d_out; unsigned long long* d_cyc;
   CK(cudaMalloc(&d_out, 8 * nsm * 1024)); CK(cudaMalloc(&d_cyc, 8 * nsm));
 #define RUN(MODE) run(MODE, probe_kernel<MODE>, MODE >= 6 ? CONSUMER_THREADS + 128 : CONSUMER_THREADS + 32, iters, nsm, d_out, d_cyc)
-  RUN(0); RUN(1); RUN(2); RUN(3); RUN(6); RUN(7);
+  RUN(0); RUN(1); RUN(2); RUN(3); RUN(6); RUN(7); RUN(8); RUN(9);
   return 0;
 }
