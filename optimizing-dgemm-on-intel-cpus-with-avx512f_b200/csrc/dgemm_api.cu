@@ -61,14 +61,14 @@ struct Env {
   // (profiles/r02_small_tile_probe_one_vs_two_ctas.jsonl): two CTAs per SM are never faster -- 512^3 10.6 vs 11.9, 1024^3
   // 27.4 vs 27.8, 1000x1003x997 24.7 vs 25.1 TFLOP/s -- because the co-resident CTAs start, switch tiles and finish together
   int small_ctas = 1;
-  long long small_max_tiles = 64;       // DGEMM_B200_SMALL_TILE_MAX_TILES
+  long long small_max_tiles = 81;       // DGEMM_B200_SMALL_TILE_MAX_TILES (64 until the build's k-tile loop stopped being unrolled)
   double small_max_flops = 4e9;         // DGEMM_B200_SMALL_TILE_MAX_FLOPS
   // DGEMM_B200_TILE: "auto" (default) / "big" / "small" / "mid": force the CTA tile of the TMA kernel where it is eligible
   // (probes and tests); DGEMM_B200_MID_TILE_MIN_TILES / _MAX_TILES: the range of 128 x 128-tile counts for which "auto"
   // picks the 128 x 64 build (dgemm_kernels_mid.cu)
   int force_tile = -1;
-  long long mid_min_tiles = 49, mid_max_tiles = 100;   // measured: profiles/r02_tile_probe_big_small_mid.jsonl
-  double mid_max_flops = 5e9;           // DGEMM_B200_MID_TILE_MAX_FLOPS (long K: the big tile's 98 % main loop wins)
+  long long mid_min_tiles = 82, mid_max_tiles = 121;   // measured: profiles/r02_tile_probe_after_small_unroll1.jsonl (49 / 100 before)
+  double mid_max_flops = 6e9;           // DGEMM_B200_MID_TILE_MAX_FLOPS (long K: the big tile's 98 % main loop wins)
   // The 64 x 32 build (dgemm_kernels_tiny.cu) runs ONE data-parallel wave, no exchange: "auto" picks it when its tiles fit one
   // wave and the SMs it leaves idle cost less than the exchange a stream-K schedule of a larger tile would pay
   // (DGEMM_B200_TINY_GAIN_US, microseconds; 0 = never).  DGEMM_B200_TINY_SK=1: let plan_stream_k cut a partial wave of these
