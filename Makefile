@@ -70,6 +70,12 @@ TINY_FLAGS_latedesc := -DDG_TINY_EARLY_DESC=0
 TINY_FLAGS_plain    := -DDG_TINY_DUAL_ACC=0 -DDG_TINY_EARLY_DESC=0
 TINY_FLAGS_w16      := -DDG_TINY_WARPS16=1
 TINY_FLAGS_w4       := -DDG_TINY_WARPS4=1
+TINY_FLAGS_clk      := -DDG_STAMP_CLOCK64
+TINY_FLAGS_skew8    := -DDG_STAMP_CLOCK64 -DDG_SKEW_64THS=8
+TINY_FLAGS_skew16   := -DDG_STAMP_CLOCK64 -DDG_SKEW_64THS=16
+TINY_FLAGS_skew32   := -DDG_STAMP_CLOCK64 -DDG_SKEW_64THS=32
+TINY_FLAGS_regs96   := -DDG_STAMP_CLOCK64 -DDG_MIN_CTAS=2 -DDG_PRODUCER_REGS=40 -DDG_CONSUMER_REGS=96
+TINY_FLAGS_st8      := -DDG_STAMP_CLOCK64 -DDG_TINY_STAGES=8
 TINY_FLAGS_notma    := -DDG_DEBUG_NO_TMA
 TINY_FLAGS_w4notma  := -DDG_TINY_WARPS4=1 -DDG_DEBUG_NO_TMA
 libtiny: $(foreach n,kps2 nodual latedesc plain w16 w4,$(PKG)/libdgemm_b200_tiny_$(n).so)

@@ -39,6 +39,9 @@
 #define DG_EARLY_DESC_PREFETCH DG_TINY_EARLY_DESC
 #undef DG_KT_PER_STAGE
 #define DG_KT_PER_STAGE DG_TINY_KPS
-#define DG_SMALL_STAGES (12 / DG_KT_PER_STAGE)   // 144 KB in flight: 12 of the 32 k-tiles of a 512^3 tile
+#ifndef DG_TINY_STAGES
+#define DG_TINY_STAGES 12
+#endif
+#define DG_SMALL_STAGES (DG_TINY_STAGES / DG_KT_PER_STAGE)   // 144 KB in flight: 12 of the 32 k-tiles of a 512^3 tile
 #define DG_SMALL_FN(name) name##_tiny
 #include "dgemm_small_tile.cuh"
