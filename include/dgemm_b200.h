@@ -169,6 +169,11 @@ int dgemm_b200_host_plan(int M, int N, int K, double alpha, double beta, int *pa
  * Counterpart of the reference's outer N / K blocking loops (include/kernel18.h:652-669), one memory level further out. */
 int dgemm_b200_host_blocking(int M, int N, int K, double alpha, double beta, double budget_bytes, int *Mb, int *Nb, int *Kb,
                              double *pcie_bytes);
+/* Which build of the TMA kernel a device call of this shape runs (16-byte aligned operands, even leading dimensions, no fused
+ * fetch) on a GPU with num_sms SMs, how many CTAs it launches and how many of its tiles are cut into stream-K ranges.  Pure
+ * host logic, no device needed.  tile: 0 = 128x128, 1 = 64x64, 2 = 64x64 at two CTAs per SM, 3 = 128x64, 4 = 64x32 (the
+ * builds play the role of the reference's edge micro-kernels beside the 24x8 one, include/kernel18.h:533-600). */
+int dgemm_b200_tile_plan(int M, int N, int K, int num_sms, int *tile, int *ctas, int *stream_k_tiles);
 /* bytes of device memory the library's cached buffers hold on the current device (operand staging, workspaces) */
 size_t dgemm_b200_device_bytes(void);
 

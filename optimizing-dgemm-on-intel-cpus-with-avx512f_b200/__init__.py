@@ -35,7 +35,7 @@ EXPORTS = [
     "dgemm_b200_ipc_open", "dgemm_b200_ipc_close", "dgemm_b200_plan", "dgemm_b200_malloc", "dgemm_b200_free",
     "dgemm_b200_host_alloc", "dgemm_b200_host_free", "dgemm_b200_h2d", "dgemm_b200_d2h", "dgemm_b200_sync",
     "dgemm_b200_fill_signed", "dgemm_b200_time_device", "dgemm_b200_launch_count",
-    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_debug_launch_floor", "dgemm_b200_host_plan", "dgemm_b200_host_blocking",
+    "dgemm_b200_reset_launch_count", "dgemm_b200_sm_clock_mhz", "dgemm_b200_debug_timeline", "dgemm_b200_debug_occupy_sms", "dgemm_b200_debug_launch_floor", "dgemm_b200_host_plan", "dgemm_b200_host_blocking", "dgemm_b200_tile_plan",
     "dgemm_b200_device_bytes",
     "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled", "dgemm_b200_rank_pipeline",
     "dgemm_b200_exchange_bytes", "dgemm_b200_exchange_alloc", "dgemm_b200_rank_plan", "dgemm_b200_reload_env",
@@ -111,6 +111,7 @@ lib.dgemm_b200_debug_launch_floor.restype = C.c_double
 lib.dgemm_b200_debug_launch_floor.argtypes = [C.c_int, C.c_int, C.c_uint, C.c_int, C.c_int]
 lib.dgemm_b200_host_blocking.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_int),
                                          C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double)]
+lib.dgemm_b200_tile_plan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
 lib.dgemm_b200_device_bytes.restype = C.c_size_t
 lib.dgemm_b200_device_bytes.argtypes = []
 lib.dgemm_b200_debug_occupy_sms.argtypes = [C.c_int, C.c_uint, C.c_double]
@@ -173,6 +174,16 @@ def host_blocking(M, N, K, budget_bytes, alpha=1.0, beta=1.0):
     _check(lib.dgemm_b200_host_blocking(M, N, K, alpha, beta, float(budget_bytes), C.byref(mb), C.byref(nb), C.byref(kb),
                                         C.byref(by)))
     return {"Mb": mb.value, "Nb": nb.value, "Kb": kb.value, "pcie_bytes": by.value}
+
+
+TILE_NAMES = {0: "128x128", 1: "64x64", 2: "64x64x2", 3: "128x64", 4: "64x32"}
+
+
+def tile_plan(M, N, K, num_sms=148):
+    """Which tile build of the TMA kernel a device call of this shape runs, its CTAs and stream-K tiles (no GPU needed)."""
+    t, c, k = C.c_int(), C.c_int(), C.c_int()
+    _check(lib.dgemm_b200_tile_plan(M, N, K, num_sms, C.byref(t), C.byref(c), C.byref(k)))
+    return {"tile": TILE_NAMES[t.value], "ctas": c.value, "stream_k_tiles": k.value}
 
 
 def device_bytes():

@@ -1547,6 +1547,18 @@ int dgemm_b200_host_blocking(int M, int N, int K, double alpha, double beta, dou
   return ok();
 }
 
+int dgemm_b200_tile_plan(int M, int N, int K, int num_sms, int* tile, int* ctas, int* stream_k_tiles) {
+  if (M <= 0 || N <= 0 || K <= 0 || num_sms <= 0) return fail(DGEMM_B200_ERR_BAD_ARG, "dgemm_b200_tile_plan: bad arguments");
+  dg::Params P;
+  const int t = choose_tile(M, N, K, true, false, num_sms);
+  fill_params(P, M, N, K, 1.0, nullptr, (M + 1) & ~1, nullptr, (K + 1) & ~1, 0.0, nullptr, M, 0, dg::VARIANT_TMA, num_sms, t);
+  const int slots = P.tile_small == dg::TILE_SMALL_X2 ? dg::SMALL_X2_CTAS_PER_SM * num_sms : num_sms;
+  if (tile) *tile = P.tile_small;
+  if (ctas) *ctas = P.sk_tiles > 0 ? P.sk_grid : std::min(P.tiles_m * P.tiles_n, slots);
+  if (stream_k_tiles) *stream_k_tiles = P.sk_tiles;
+  return ok();
+}
+
 int dgemm_b200_launch_count(void) { return dg::launch_count(); }
 void dgemm_b200_reset_launch_count(void) { dg::reset_launch_count(); }
 
