@@ -41,6 +41,10 @@ def test_library_is_sm100a_cuda_not_cpu(dg):
     assert "SYNCS" in sass             # mbarrier
     assert "UBLKCP" in sass            # cp.async.bulk: stream-K partials come in through the TMA ring
     assert "dgemm_tma_ws_split_kernel" in sass   # parity-split variants for odd LD / 8-byte-aligned operands
+    for ns in ("N2dg", "N4dg64", "N6dg64x2", "N8dg128x64", "N7dg64x32"):   # every tile build of the kernel body is in the library
+        assert f"_Z{ns}19dgemm_tma_ws_kernel" in sass, ns
+    assert "dgemm_tma_cluster_kernel" in sass      # ladder rung 6: 2-CTA clusters + TMA multicast
+    assert "UTMALDG.2D.MULTICAST" in sass or "MULTICAST" in sass
 
 
 def test_product_does_not_link_the_oracle(dg):
