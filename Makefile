@@ -12,7 +12,7 @@ ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -lineinfo -std=c++17 -ccbin $(HOSTCXX) -Xcompiler -fPIC -Xcompiler -Wall
 LIB      := $(PKG)/libdgemm_b200.so
 LIB_SRCS := $(CSRC)/dgemm_kernels.cu $(CSRC)/dgemm_rank.cu $(CSRC)/dgemm_rankplan.cpp $(CSRC)/dgemm_kernels_small.cu $(CSRC)/dgemm_kernels_small2.cu $(CSRC)/dgemm_kernels_mid.cu $(CSRC)/dgemm_kernels_tiny.cu $(CSRC)/dgemm_kernels_cluster.cu $(CSRC)/dgemm_ladder.cu $(CSRC)/dgemm_api.cu $(CSRC)/dgemm_multi.cu \
-            $(CSRC)/dgemm_hostplan.cpp $(CSRC)/dgemm_staging.cu
+            $(CSRC)/dgemm_hostplan.cpp $(CSRC)/dgemm_staging.cu $(CSRC)/dgemm_static_scratch.cu
 LIB_HDRS := $(CSRC)/dgemm_device.cuh $(CSRC)/dgemm_launch.h $(CSRC)/dgemm_params.h $(CSRC)/dgemm_tma_kernel.cuh $(CSRC)/dgemm_small_tile.cuh $(CSRC)/dgemm_host.h include/dgemm_b200.h
 
 all: lib probe harness oracle

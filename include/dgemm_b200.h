@@ -96,6 +96,32 @@ int dgemm_b200_device_ex(int M, int N, int K, double alpha, const double *dA, lo
 int dgemm_b200_device_op(int layout, int transa, int transb, int M, int N, int K, double alpha, const double *dA,
                          long long lda, const double *dB, long long ldb, double beta, double *dC, long long ldc,
                          void *stream);
+/* The split-K DGEMM with NO allocation of any kind.  (No counterpart in the reference, whose kernels malloc and free their
+ * pack buffers inside every call, include/kernel18.h:647-648,670; this entry exists for GPU callers only.)
+ * Meant for programs that cannot let a library call cudaMalloc: a process whose own memory pool has already taken nearly all
+ * of the HBM (the library's request would fail with out-of-memory, or eat into what the pool believes it owns), and code in a
+ * latency-critical or many-stream loop, where the device-wide lock of cudaMalloc and the device-wide wait of cudaFree stall
+ * every other stream.  All other device entries may allocate (context on first use, workspace growth later).
+ * Here the partial tiles of the split-K kernels live in an array that is part of the library image: every GPU the library
+ * runs on carries DGEMM_B200_STATIC_SCRATCH_BYTES of it from module load to process exit, used or not.
+ *   operands   device pointers on the CURRENT device, as for dgemm_b200_device; `stream` a cudaStream_t (NULL = default)
+ *   splits     0 = choose (2 .. what the scratch holds), or >= 2; 1 is rejected (nothing to keep in scratch: a caller that
+ *              wants no split has no use for this entry)
+ *   limit      ceil(M/128) * ceil(N/128) * splits <= DGEMM_B200_STATIC_SCRATCH_BYTES / (128*128*8) = 128 partial tiles, so
+ *              at most 64 output tiles (e.g. 1024 x 1024, any K).  Larger calls fail with DGEMM_B200_ERR_BAD_ARG and a
+ *              message naming the limit; nothing is launched and C is untouched
+ *   result     bit-identical to dgemm_b200_device_ex(variant = TMA for 16-byte aligned operands with even LDA / LDB, else
+ *              CPASYNC8, same splits); same degenerate-case semantics as every entry (alpha == 0 or K == 0: C = beta*C)
+ *   sharing    every call on a GPU uses the same array.  Calls on one stream may follow each other freely (nothing in the
+ *              array has to be zero at the start: each unit overwrites its whole slot before it is read).  Calls whose
+ *              kernels can run at the same time on one GPU — different streams — race and return garbage SILENTLY:
+ *              order them with events
+ *   first call on each device: looks up the array's device address and the SM count (cudaGetSymbolAddress, no
+ *              allocation).  Make it before any stream capture starts on that device */
+#define DGEMM_B200_STATIC_SCRATCH_BYTES (16u << 20)
+int dgemm_b200_device_static_scratch(int M, int N, int K, double alpha, const double *dA, long long lda,
+                                     const double *dB, long long ldb, double beta, double *dC, long long ldc,
+                                     void *stream, int splits);
 /* C (M x N, ldc) += beta * X (M x N, ldx), device pointers, asynchronous on `stream`.  The "deferred C" step of a
  * pipelined caller: start the panel's DGEMM calls with beta = 0 while C is still on its way over PCIe, add beta*C_in
  * after the last one (mydgemm_gpu_v20 does this internally; bench.py's multi-GPU end-to-end pipeline uses this entry).

@@ -39,6 +39,7 @@ EXPORTS = [
     "dgemm_b200_device_bytes",
     "dgemm_b200_cblas_dgemm", "dgemm_b200_device_op", "dgemm_b200_add_scaled", "dgemm_b200_rank_pipeline",
     "dgemm_b200_exchange_bytes", "dgemm_b200_exchange_alloc", "dgemm_b200_rank_plan", "dgemm_b200_reload_env",
+    "dgemm_b200_device_static_scratch",
 ]
 
 
@@ -69,6 +70,7 @@ lib.dgemm_b200_set_max_gpus.argtypes = [C.c_int]
 _DEV_ARGS = [C.c_int, C.c_int, C.c_int, C.c_double, _vp, _ll, _vp, _ll, C.c_double, _vp, _ll]
 lib.dgemm_b200_device.argtypes = _DEV_ARGS + [_vp]
 lib.dgemm_b200_device_ex.argtypes = _DEV_ARGS + [_vp, C.c_int, C.c_int]
+lib.dgemm_b200_device_static_scratch.argtypes = _DEV_ARGS + [_vp, C.c_int]
 lib.dgemm_b200_device_fetch.argtypes = _DEV_ARGS + [_vp, _vp, _vp, C.c_size_t]
 lib.dgemm_b200_ipc_export.argtypes = [_vp, C.c_char_p]
 lib.dgemm_b200_ipc_open.argtypes = [C.c_char_p, C.POINTER(_vp)]
@@ -288,6 +290,20 @@ def dgemm_device(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0, vari
     """Asynchronous DGEMM on device pointers of the current CUDA device (ints / data_ptr())."""
     st = lib.dgemm_b200_device_ex(M, N, K, float(alpha), int(dA), lda, int(dB), ldb, float(beta), int(dC), ldc,
                                   int(stream) or None, variant, splits)
+    _check(st)
+
+
+STATIC_SCRATCH_BYTES = 16 << 20   # DGEMM_B200_STATIC_SCRATCH_BYTES: 128 partial tiles of 128 x 128 doubles
+
+
+def dgemm_device_static_scratch(M, N, K, alpha, dA, lda, dB, ldb, beta, dC, ldc, stream=0, splits=0):
+    """Split-K DGEMM on device pointers that allocates nothing (include/dgemm_b200.h: dgemm_b200_device_static_scratch).
+
+    For callers that cannot let the library call cudaMalloc (their own pool holds the HBM, or they cannot afford the
+    device-wide stall of cudaMalloc / cudaFree).  The partial tiles live in a fixed 16 MiB array inside the library, so at
+    most 128 (tile, split) units fit: larger calls raise DgemmError(ERR_BAD_ARG).  Calls on different streams race."""
+    st = lib.dgemm_b200_device_static_scratch(M, N, K, float(alpha), int(dA), lda, int(dB), ldb, float(beta), int(dC), ldc,
+                                              int(stream) or None, splits)
     _check(st)
 
 
