@@ -28,7 +28,7 @@ $(PKG)/libdgemm_b200_w16.so: $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -DDG_WARPS_M=4 -DDG_WARPS_N=4 -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
 
 # measurement build: the producer hands every stage over WITHOUT loading it (results are garbage, timing is the consumers'
-# loop alone); load with DGEMM_B200_LIB=.../libdgemm_b200_dbg_notma.so (tools/r02_call19.sh)
+# loop alone); load with DGEMM_B200_LIB=.../libdgemm_b200_dbg_notma.so (tools/history/r02_call19.sh)
 libdbg: $(PKG)/libdgemm_b200_dbg_notma.so
 $(PKG)/libdgemm_b200_dbg_notma.so: $(LIB_SRCS) $(LIB_HDRS)
 	$(NVCC) $(NVFLAGS) -DDG_DEBUG_NO_TMA -shared -o $@ $(LIB_SRCS) -Xlinker --no-undefined -ldl -lpthread
@@ -109,4 +109,4 @@ sass: $(LIB)
 clean:
 	rm -f $(LIB) $(PKG)/bin/peak_probe $(PKG)/bin/dgemm_b200
 	$(MAKE) -C oracle clean
-.PHONY: all build lib lib16 libdbg libkps libtiny libclk probe stage_probe harness oracle sass clean
+.PHONY: all build lib lib16 libdbg libkps libtiny libclk libskew libunroll probe stage_probe harness oracle sass clean

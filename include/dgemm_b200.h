@@ -158,7 +158,13 @@ int dgemm_b200_ipc_close(void *dptr);
  *             pass p+1 from starting on any rank before every rank has returned from pass p (one host barrier)
  *   timeline  optional: receives (kind, index, milliseconds since the pass began) triples, kind 0 = H2D for call `index`
  *             complete, 1 / 2 = call `index` started / finished, 3 = D2H of column sub-panel `index` complete
- * Same semantics as mydgemm_gpu_v20 on the panel (alpha == 0 or K == 0 -> C = beta*C; beta == 0 -> C not read). */
+ * Same semantics as mydgemm_gpu_v20 on the panel (alpha == 0 or K == 0 -> C = beta*C; beta == 0 -> C not read).
+ * Errors: when a peer's slab does not arrive within DGEMM_B200_FLAG_TIMEOUT_MS the call returns DGEMM_B200_ERR_CUDA AFTER the
+ * pass has drained, and the caller's C_panel is then UNDEFINED (sub-panels computed on the incomplete A have already been
+ * written back): keep a copy of C if beta != 0 and the pass must be repeatable.
+ * Host memory: the overlap of H2D, compute and D2H (and the quoted throughput) needs PINNED A_slab / B_panel / C_panel;
+ * pageable operands are correct but every copy then blocks the launching thread (also true for mydgemm_gpu_v21, which
+ * runs this pipeline on one thread per GPU: the reference harness's malloc'ed matrices take that slower road). */
 int dgemm_b200_rank_pipeline(int M, int ncols, int K, double alpha, const double *A_slab, int LDA,
                              const double *B_panel, int LDB, double beta, double *C_panel, int LDC, int rank,
                              int world, const int *kb, void *const *xbuf, unsigned int pass, double *timeline,

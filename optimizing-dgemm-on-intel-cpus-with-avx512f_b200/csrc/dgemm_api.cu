@@ -160,7 +160,7 @@ struct DeviceCtx {
   cudaEvent_t ws_free = nullptr;  // recorded after the last kernel that used ws
   bool ws_used = false;
   cudaStream_t ws_stream = nullptr;  // ... and the stream it ran on (the same stream needs no event wait)
-  unsigned int* fetch_fail = nullptr;  // set by a fused fetch whose source never arrived (Params::fetch_fail)
+  unsigned int* fetch_fail = nullptr;  // set by wait_flag_kernel when a peer's K-slab never arrived (dgemm_rank.cu)
   Buf a, b, c;                // staging for the host-pointer entries
   Buf x;                      // C_in of the deferred-C panels of the host pipeline
   Buf ra, rb;                 // realigned copies of TMA-ineligible device operands (see run_device)
@@ -332,7 +332,7 @@ int choose_tile(int M, int N, int K, bool tma_kernel, bool has_fetch, int num_sm
   if (env().no_small_tile) return dg::TILE_BIG;
   const long long big_tiles = (long long)((M + dg::BM - 1) / dg::BM) * ((N + dg::BN - 1) / dg::BN);
   const double flops = 2.0 * M * (double)N * K;
-  // 64 x 32 tiles, data-parallel: a k-tile of this build takes ~0.28 us (two per ring slot); the SMs one wave leaves idle
+  // 64 x 32 tiles, data-parallel: a k-tile of this build takes ~0.28 us (one per ring slot); the SMs one wave leaves idle
   // cost (idle share) x (k-tiles) x 0.28 us against the ~4-5 us the exchange of a stream-K schedule costs at these sizes
   const long long tiny_tiles = (long long)((M + dg::TINY_BM - 1) / dg::TINY_BM) * ((N + dg::TINY_BN - 1) / dg::TINY_BN);
   if (tiny_tiles <= num_sms && env().tiny_gain_us > 0.0) {
@@ -396,9 +396,7 @@ int odd_ld_mode() { return env().odd_ld; }   // DGEMM_B200_ODD_LD (tests and pro
 struct Fetch {
   const void* src = nullptr;
   void* dst = nullptr;
-  size_t bytes = 0;
-  const unsigned int* flag = nullptr;  // owner's "landed" sequence word (peer memory); nullptr: the source is complete
-  unsigned int need = 0;               // value it must have reached (signed distance)
+  size_t bytes = 0;   // (the source must be complete in stream order: the multi-GPU layer queues wait_flag_kernel ahead of the call)
 };
 
 int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA, long long lda, const double* dB,
@@ -407,9 +405,7 @@ int run_device(DeviceCtx& c, int M, int N, int K, double alpha, const double* dA
   if (fetch.bytes && (((uintptr_t)fetch.src | (uintptr_t)fetch.dst | fetch.bytes) & 15))
     return fail(DGEMM_B200_ERR_BAD_ARG, "fused fetch needs 16-byte aligned src/dst and a multiple of 16 bytes");
   if (M == 0 || N == 0 || alpha == 0.0 || K == 0) {
-    // no GEMM kernel to fuse with: the copy engine does the fetch (a flagged source needs the fetch warps' wait, and the
-    // multi-GPU layer never attaches one to a degenerate call)
-    if (fetch.bytes && fetch.flag) return fail(DGEMM_B200_ERR_BAD_ARG, "a flagged fused fetch needs M, N, K > 0 and alpha != 0");
+    // no GEMM kernel to fuse with: the copy engine does the fetch
     if (fetch.bytes) CU_TRY(cudaMemcpyAsync(fetch.dst, fetch.src, fetch.bytes, cudaMemcpyDefault, stream));
     if (M == 0 || N == 0) return ok();
     CU_TRY(dg::launch_scale_c(dC, M, N, ldc, beta, c.num_sms, stream));  // C = beta*C only (kernel18.h:644-645)
@@ -1083,7 +1079,9 @@ void* dgemm_b200_exchange_alloc(int M, int K) {
   }
   void* p = dgemm_b200_malloc(dg::exchange_bytes(M, K));
   if (!p) return nullptr;
-  if (cudaMemset(static_cast<char*>(p) + dg::exchange_flag_offset(M, K), 0, 256) != cudaSuccess) {
+  // (synchronised: the caller's first pass publishes / waits on non-blocking streams that are not ordered behind this memset)
+  if (cudaMemset(static_cast<char*>(p) + dg::exchange_flag_offset(M, K), 0, 256) != cudaSuccess ||
+      cudaStreamSynchronize(0) != cudaSuccess) {
     cudaGetLastError();
     cudaFree(p);
     fail(DGEMM_B200_ERR_CUDA, "dgemm_b200_exchange_alloc: cudaMemset of the sequence words failed");

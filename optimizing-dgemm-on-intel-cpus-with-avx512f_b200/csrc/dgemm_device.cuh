@@ -51,8 +51,9 @@ constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 // k-tiles per ring slot of the TMA kernel (one full / empty mbarrier pair per slot).  Every slot boundary costs a
 // sub-partition ~75 clk whatever the tile (profiles/r02_loop_with_and_without_tma.txt), which is 2 % of a 128 x 128 stage
-// but 15 % of a 64 x 32 one; with two k-tiles per slot the consumers cross half as many.  1 = the layout every shipped
-// kernel but the 64 x 32 build uses; `make libkps2` builds all of them with 2 for A/B timing.
+// but 15 % of a 64 x 32 one; with two k-tiles per slot the consumers cross half as many.  1 = the layout EVERY shipped
+// kernel uses (the 64 x 32 build included: 2 was measured and rejected); `make libkps` builds all of
+// them with 2 for A/B timing.
 #ifndef DG_KT_PER_STAGE
 #define DG_KT_PER_STAGE 1
 #endif

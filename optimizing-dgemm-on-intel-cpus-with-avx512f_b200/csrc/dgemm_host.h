@@ -47,7 +47,7 @@ constexpr int MID_BM = 128, MID_BN = 64;
 cudaError_t launch_tma_small_mid(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                                  cudaStream_t stream, bool cooperative, bool pdl);
 cudaError_t small_tile_occupancy_mid(int* ctas_per_sm);
-// the TMA kernel on 64 x 32 tiles (dgemm_kernels_tiny.cu); Params::tile_small == 4; B boxes 16 x 32, two k-tiles per ring slot
+// the TMA kernel on 64 x 32 tiles (dgemm_kernels_tiny.cu); Params::tile_small == 4; B boxes 16 x 32, one k-tile per ring slot
 constexpr int TINY_BM = 64, TINY_BN = 32;
 cudaError_t launch_tma_small_tiny(const void* const maps[4], int split, const Params& P, int grid, int dp_units,
                                   cudaStream_t stream, bool cooperative, bool pdl);

@@ -1,13 +1,14 @@
 // dgemm_kernels_tiny.cu — the persistent TMA kernel of dgemm_tma_kernel.cuh compiled for a 64 x 32 CTA tile (namespace
 // dg64x32): 8 DMMA consumer warps in a 4 x 2 grid with 16 x 16 warp tiles (8 accumulator registers), 12 KB k-tiles (A 64 x 16
-// as four 16 x 16 boxes, B one 16 x 32 box), TWO k-tiles per ring slot (DG_KT_PER_STAGE), 16 KB stream-K partials.
+// as four 16 x 16 boxes, B one 16 x 32 box), ONE k-tile per ring slot (DG_TINY_KPS = 1, see below), 16 KB stream-K partials.
 //
 // Why: 512^3 is 16 big, 32 mid or 64 small tiles for 148 SMs; each of those builds fills the GPU by cutting K into ranges,
 // and when every range of a tile ends at the same moment the owner pays the whole exchange after its loop (partial
 // store, flag, bulk load, add, C read-modify-write: ~5 of 22.5 us, profiles/r02_timelines_small_tile_one_vs_two_ctas.txt),
 // which is why cuBLAS (64 x 32 tiles, 128 data-parallel CTAs, no exchange) was ahead at this one size: 15.2 against
 // 11.8 TFLOP/s.  This tile gives 512^3 128 whole tiles: one wave, no workspace, no flags.  A 64 x 32 k-tile is only 512 clk
-// of DMMAs, so the ~75 clk a ring-slot boundary costs a sub-partition would be 15 %: hence two k-tiles per slot (7 %).
+// of DMMAs, so the ~75 clk a ring-slot boundary costs a sub-partition is 15 %.  Two k-tiles per slot (DG_TINY_KPS=2, `make
+// libtiny`) halve the crossings but were measured no faster end to end and are NOT shipped: KPS = 1.
 // run_device picks it where one data-parallel wave of these tiles covers most of the GPU (dgemm_api.cu: choose_tile).
 // Same role in the reference: the narrowest edge micro-kernels (m8n4 ... m2n4, include/kernel18.h:571-600).
 #define DG_NAMESPACE dg64x32

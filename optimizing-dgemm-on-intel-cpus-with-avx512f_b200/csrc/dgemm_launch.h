@@ -10,6 +10,11 @@
 //   programmatic  every other launch allows programmatic dependent launch: the kernel's prologue (barrier init, tensor-map
 //                 prefetch) runs while the previous kernel of the stream drains, and griddepcontrol.wait holds back its first
 //                 global access until that kernel has completed.
+//                 INVARIANT: a kernel launched with this attribute MUST execute griddepcontrol.wait before its first global
+//                 memory access (the TMA kernels do, dgemm_tma_kernel.cuh).  Every other kernel of the library (cp.async,
+//                 split-K reduce, scale / add / realign / transpose, ladder rungs, flag kernels) is launched with <<<>>> and
+//                 no attribute, so it starts only after the previous kernel of its stream has completed and needs no wait.
+//                 Do not pass pdl = true for a kernel that lacks the instruction.
 #pragma once
 #include <cuda_runtime.h>
 

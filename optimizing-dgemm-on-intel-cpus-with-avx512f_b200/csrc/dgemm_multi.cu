@@ -229,6 +229,11 @@ static int run_host_multi_ranked(int M, int N, int K, double alpha, const double
       s.x_cap_bytes = xbytes; s.x_M = M; s.x_K = K;
     }
     MCU(cudaMemset(static_cast<char*>(s.xbuf) + dg::exchange_flag_offset(M, K), 0, 256));
+    // The memset runs on the legacy default stream; the rank threads publish and wait on cudaStreamNonBlocking streams (and
+    // the peers' waits run on other devices), which nothing orders behind it.  The buffer is kept across calls, so until the
+    // zeroes land the words still hold the LAST call's final values and would satisfy every wait of this one.  Finish it here,
+    // before any rank thread exists.
+    MCU(cudaStreamSynchronize(0));
   }
   std::vector<void*> xbuf(G);
   for (int d = 0; d < G; d++) xbuf[d] = m.dev[d].xbuf;

@@ -32,7 +32,7 @@ struct Segment {
   int wave;           // phase 1: how many units this CTA has done before this one; -1 in phase 2
 };
 // Skew between the two consumer warps of an SM sub-partition (w and w + 4), in 64ths of the pair's time per stage; 0 = off.
-// Measured (tools/r02_call20.sh / r02_call21.sh, profiles/r02_consumer_warp_skew.txt): 2/64 .. 8/64 of a stage take the
+// Measured (tools/history/r02_call20.sh / r02_call21.sh, profiles/r02_consumer_warp_skew.txt): 2/64 .. 8/64 of a stage take the
 // 128 x 128 kernel from 36.52 to 36.70-36.76 TFLOP/s at 16384^3 (8192^3 36.39 -> 36.67, 4096^3 36.19 -> 36.36) and a whole
 // 128 x 64 tile from 139.3 to 137.9 us; 12/64 and more are WORSE than none (36.35), and the 64 x 64 tile gains nothing.
 #ifndef DG_SKEW_64THS

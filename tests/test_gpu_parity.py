@@ -313,7 +313,7 @@ def test_mid_tile_build(dg, monkeypatch, case):
                                   ((64, 64, 8192), (0, 0, 0), 1.0, 1.0),           # 2 tiles: with TINY_SK many ranges per tile
                                   ((7, 9, 33), (0, 0, 0), 1.0, 1.0)])
 def test_tiny_tile_build(dg, monkeypatch, case, sk):
-    """DGEMM_B200_TILE=tiny: the TMA kernel compiled for 64 x 32 CTA tiles with 16 x 16 warp tiles and two k-tiles per ring
+    """DGEMM_B200_TILE=tiny: the TMA kernel compiled for 64 x 32 CTA tiles with 16 x 16 warp tiles and one k-tile per ring
     slot (csrc/dgemm_kernels_tiny.cu).  sk: DGEMM_B200_TINY_SK=1 lets a partial wave of these tiles be cut into stream-K
     ranges (the build's default is one data-parallel wave).  Same bound as every other path; bit-identical run to run."""
     (M, N, K), pad, alpha, beta = case
