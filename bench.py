@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--no-cublas", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the whole-panel oracle check before the timed region")
     ap.add_argument("--no-v21", action="store_true", help="N > 1: skip the single-process mydgemm_gpu_v21 leg")
+    ap.add_argument("--no-configs", action="store_true", help="N = 1: skip the configs 1-3 sweep (2048^3, 256..8192, edges, skinny)")
     ap.add_argument("--no-scale-base", action="store_true", help="N = 1: skip the one 65536^3 pass (strong-scaling base)")
     return ap.parse_args()
 
@@ -530,6 +531,14 @@ def main():
             e2e_v21 = run_v21(torch, dg, N, int(os.environ.get("BENCH_V21_SIZE", "32768")), 2)
         host_barrier()
 
+    # BASELINE configs 1-3 (2048^3 both scalar pairs, 256..8192, the edge shapes, the skinny one) in the driver-run line
+    sweep = None
+    if N == 1 and args.size is None and not args.no_configs:
+        try:
+            sweep = configs_sweep(torch, dg, dev, n_sms, (clocks or {}).get("sm_mhz") or 1965.0)
+        except Exception as e:  # noqa: BLE001 - reported, never a reason to lose the headline number
+            sweep = {"error": repr(e)}
+
     if rank != 0:
         if N > 1:
             dist.destroy_process_group()
@@ -594,7 +603,11 @@ def main():
         line["e2e_v21"] = e2e_v21
     if scale_base is not None:
         line["strong_scaling_base"] = scale_base
+    if sweep is not None:
+        line["configs"] = sweep
     emit(line)
+    if sweep is not None and sweep.get("max_err_over_bound", 0.0) > 2.0:
+        sys.exit("configs sweep: a shape is outside the parity bound")
     if N > 1:
         dist.destroy_process_group()
 
@@ -772,6 +785,118 @@ def run_v21(torch, dg, G, size, reps):
             "spot_check": f"{len(idx)} entries (incl. both sides of every panel boundary) recomputed on the host in long double",
             "api": f"mydgemm_gpu_v21(M,N,K,alpha,A,LDA,B,LDB,beta,C,LDC), M=N=K={size}, pinned host pointers, one process "
                    f"driving {G} GPUs (one host thread per GPU, the same rank pipeline as dgemm_b200_rank_pipeline)"}
+
+
+# BASELINE.json configs[0..2] beside the headline shape (N = 1 only): (label, M, N, K, alpha, beta, (pad_a, pad_b, pad_c))
+SWEEP_SHAPES = (
+    [("square", n, n, n, 1.0, 1.0, (0, 0, 0)) for n in (256, 512, 1024, 1536, 2048)] +
+    [("config 1 harness scalars alpha=2 beta=0 (reference test.c:25)", 2048, 2048, 2048, 2.0, 0.0, (0, 0, 0)),
+     ("square", 4096, 4096, 4096, 1.0, 1.0, (0, 0, 0)),
+     ("square", 8192, 8192, 8192, 1.0, 1.0, (0, 0, 0)),
+     ("edge, LD=dim (LDB odd: B read by column parity)", 1000, 1003, 997, 2.5, 0.5, (0, 0, 0)),
+     ("edge, LD=dim+7 (LDA odd: A read by k parity)", 1000, 1003, 997, 2.5, 0.5, (7, 7, 7)),
+     ("edge, LD=1024", 1000, 1003, 997, 2.5, 0.5, (24, 27, 24)),
+     ("edge, odd M, LD=dim", 1001, 1003, 997, 2.5, 0.5, (0, 0, 0)),
+     ("tall-skinny", 512, 512, 16384, 1.0, 1.0, (0, 0, 0))])
+SWEEP_FULL_PARITY_MAX_FLOPS = 1.5e11   # every entry against the oracle up to 4096^3; sampled entries above
+
+
+def configs_sweep(torch, dg, dev, n_sms, sm_mhz):
+    """BASELINE.json configs 1-3 on one GPU, in the driver-run line: per shape the kernel-only TFLOP/s (CUDA events inside
+    dgemm_b200_time_device, operands resident, a 256 MB buffer overwritten before every repetition so that nothing is served
+    from L2), its fraction of the FP64 pipe at the sampled clock, the tile build the heuristic picked, cuBLAS on the same
+    buffers (ceiling only), end to end through mydgemm_gpu_v20 from pinned host memory, and parity: EVERY entry of the
+    device call and of the host-pointer call against the oracle (checker only; never timed) for shapes up to 4096^3."""
+    import numpy as np
+    import oracle_lib as ol
+    peak = n_sms * FLOP_PER_CLK_PER_SM * sm_mhz * 1e6 / 1e12
+    l2_flush = 256 << 20
+    rows, worst = [], 0.0
+    t_begin = time.perf_counter()
+
+    def pinned(arr):   # F-ordered (ld x cols) numpy -> pinned torch tensor (cols x ld), same bytes
+        t = torch.empty((arr.shape[1], arr.shape[0]), dtype=torch.float64).pin_memory()
+        t.numpy()[...] = arr.T
+        return t
+
+    for (label, M, Nn, K, alpha, beta, pad) in SWEEP_SHAPES:
+        lda, ldb, ldc = M + pad[0], K + pad[1], M + pad[2]
+        flops = 2.0 * M * Nn * K
+        Ah, Bh, C0 = (ol.fill_signed(M, K, lda, 1, pad_value=0.0), ol.fill_signed(K, Nn, ldb, 2, pad_value=0.0),
+                      ol.fill_signed(M, Nn, ldc, 3, pad_value=-777.0))
+        hA, hB, hC = pinned(Ah), pinned(Bh), pinned(C0)
+        dA, dB, dC = hA.to(dev), hB.to(dev), hC.to(dev)
+        torch.cuda.synchronize()
+        row = {"label": label, "M": M, "N": Nn, "K": K, "alpha": alpha, "beta": beta, "lda": lda, "ldb": ldb, "ldc": ldc}
+        # ---- parity of the device call (fresh C), then timing on the same buffers
+        dg.dgemm_device(M, Nn, K, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta, dC.data_ptr(), ldc)
+        torch.cuda.synchronize()
+        got_dev = np.asfortranarray(dC.cpu().numpy().T)
+        plan = dg.plan(M, Nn, K, dA.data_ptr(), lda, dB.data_ptr(), ldb)
+        tp = dg.tile_plan(M, Nn, K, n_sms)
+        row["plan"] = plan
+        row["tile"] = tp["tile"] if plan["variant"] == "tma_ws" else "128x128 (cp.async kernel)"
+        reps = 3 if flops > 5e11 else 10
+        ms = dg.time_device(M, Nn, K, alpha, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta, dC.data_ptr(), ldc, warmup=3,
+                            reps=reps, flush_l2_bytes=l2_flush)
+        row["kernel_ms"] = ms
+        row["kernel_tflops"] = flops / ms / 1e9
+        row["frac"] = row["kernel_tflops"] / peak
+        if K >= 8 * max(M, Nn):   # skinny: does the K decomposition keep the loads streaming?
+            row["hbm_gbs"] = 8.0 * (M * K + K * Nn + (2 if beta else 1) * M * Nn) / ms / 1e6
+        if pad == (0, 0, 0):
+            a, b = dA.t(), dB.t()   # column-major == transposed row-major
+            for _ in range(2):
+                c = a @ b
+            flush = torch.empty(l2_flush, dtype=torch.uint8, device=dev)
+            tot = 0.0
+            for i in range(reps):
+                flush.fill_(i)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); c = a @ b; e1.record()
+                torch.cuda.synchronize()
+                tot += e0.elapsed_time(e1)
+            del c, flush
+            row["cublas_tflops"] = flops / (tot / reps) / 1e9
+        # ---- end to end through the reference's signature, pinned host operands; first call checked, next three timed
+        dg.mydgemm_gpu_v20(M, Nn, K, alpha, hA.data_ptr(), lda, hB.data_ptr(), ldb, beta, hC.data_ptr(), ldc)
+        got_e2e = np.asfortranarray(hC.numpy().T.copy())
+        t0 = time.perf_counter()
+        for _ in range(3):
+            dg.mydgemm_gpu_v20(M, Nn, K, alpha, hA.data_ptr(), lda, hB.data_ptr(), ldb, beta, hC.data_ptr(), ldc)
+        dt = (time.perf_counter() - t0) / 3
+        row["e2e_ms"] = dt * 1e3
+        row["e2e_tflops"] = flops / dt / 1e12
+        # ---- the checker
+        if flops <= SWEEP_FULL_PARITY_MAX_FLOPS:
+            want = C0.copy(order="F")
+            if beta == 0.0:
+                want[:M, :] = 0.0
+            ol.oracle_k18(M, Nn, K, alpha, Ah, Bh, beta, want)
+            C0b = C0 if beta != 0.0 else np.zeros_like(C0)
+            r_dev = ol.bound_ratio(M, Nn, K, alpha, Ah, Bh, beta, C0b, got_dev, want)[0]
+            r_e2e = ol.bound_ratio(M, Nn, K, alpha, Ah, Bh, beta, C0b, got_e2e, want)[0]
+            pad_ok = bool(np.array_equal(got_dev[M:, :], C0[M:, :]) and np.array_equal(got_e2e[M:, :], C0[M:, :]))
+            row["parity"] = "every entry vs oracle kernel18"
+        else:
+            rng = np.random.default_rng(M)
+            idx = [(0, 0), (M - 1, Nn - 1)] + [(int(rng.integers(M)), int(rng.integers(Nn))) for _ in range(30)]
+            before = [float(C0[i, j]) for i, j in idx]
+            r_dev = spot_check(before, [float(got_dev[i, j]) for i, j in idx], idx, M, K, 0, alpha, beta)
+            r_e2e = spot_check(before, [float(got_e2e[i, j]) for i, j in idx], idx, M, K, 0, alpha, beta)
+            pad_ok = True
+            row["parity"] = "32 sampled entries vs long-double dot products"
+        if not (r_dev == r_dev and r_e2e == r_e2e) or not pad_ok:
+            r_dev = r_e2e = float("inf")
+        row["max_err_over_bound"] = r_dev
+        row["e2e_max_err_over_bound"] = r_e2e
+        worst = max(worst, r_dev, r_e2e)
+        rows.append(row)
+        del dA, dB, dC, hA, hB, hC
+    return {"note": "BASELINE.json configs[0..2]; kernel-only = CUDA events, L2 flushed before every repetition; frac of "
+                    f"{n_sms} SMs x 128 flop/clk x {sm_mhz:.0f} MHz; e2e = mydgemm_gpu_v20 from pinned host memory (mean of 3); "
+                    "bound c = 2 as in tests/", "max_err_over_bound": worst, "seconds": time.perf_counter() - t_begin,
+            "shapes": rows}
 
 
 def gen_signed(seed, rows, cols):

@@ -829,6 +829,28 @@ size_t ctx_held_bytes(const DeviceCtx& c) {
   return c.ws.cap + c.a.cap + c.b.cap + c.c.cap + c.x.cap + c.ra.cap + c.rb.cap + c.ta.cap + c.tb.cap + c.flush.cap;
 }
 
+// Give every cached buffer of the context back to the driver (device idle first).  grow() only ever frees the buffer it is
+// asked to enlarge, so what an earlier call of ANOTHER shape left behind (staging a / b / c / x, realign and transpose
+// scratch, the L2 flush buffer) would otherwise stay allocated next to the blocks of an out-of-core run whose blocking was
+// computed as if that memory were available.
+int release_cached(DeviceCtx& c) {
+  int prev = 0;
+  cudaGetDevice(&prev);
+  CU_TRY(cudaSetDevice(c.dev));
+  const cudaError_t e = cudaDeviceSynchronize();
+  if (e == cudaSuccess) {
+    for (Buf* b : {&c.ws, &c.a, &c.b, &c.c, &c.x, &c.ra, &c.rb, &c.ta, &c.tb, &c.flush}) {
+      if (b->p) cudaFree(b->p);
+      b->p = nullptr;
+      b->cap = 0;
+    }
+    c.ws_used = c.r_used = c.t_used = false;   // (their last users have completed: nothing left to order against)
+  }
+  cudaSetDevice(prev);
+  CU_TRY(e);
+  return DGEMM_B200_OK;
+}
+
 struct HostBlocking { int Mb = 0, Nb = 0, Kb = 0; double pcie_bytes = 0.0; };
 
 // fewest PCIe bytes among the block shapes that fit (block edges multiples of 128 / 16, or the whole dimension)
@@ -887,6 +909,9 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
       st = run_host_incore(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
       if (st != DGEMM_B200_ERR_OOM) return st;   // (the buffers are grown before anything is copied or computed)
     }
+    // the budget is what the driver can really hand out: the context's own cached buffers are released first, so that
+    // none of them (grown for an earlier call of another shape) sits beside the blocks of this one
+    if ((st = release_cached(*cp))) return st;
     int prev = 0;
     cudaGetDevice(&prev);
     CU_TRY(cudaSetDevice(dev));
@@ -894,9 +919,11 @@ int run_host_single(int dev, int M, int N, int K, double alpha, const double* A,
     const cudaError_t e = cudaMemGetInfo(&free_b, &total_b);
     cudaSetDevice(prev);
     CU_TRY(e);
-    budget = 0.9 * (double)(free_b + ctx_held_bytes(*cp));
+    budget = 0.9 * (double)free_b;
   }
   if ((double)need <= budget) return run_host_incore(dev, M, N, K, alpha, A, LDA, B, LDB, beta, C, LDC);
+  // blocked run: its buffers are sized to the budget exactly, so nothing else of this library may stay allocated
+  if (ctx_held_bytes(*cp) && (st = release_cached(*cp))) return st;
   HostBlocking hb;
   if (!choose_host_blocking(M, N, K, need_ab, need_c_in, cp->num_sms, (size_t)budget, &hb))
     return fail(DGEMM_B200_ERR_OOM, "HBM budget of %.0f MB is too small for any block of M=%d N=%d K=%d", budget / 1048576.0, M, N, K);

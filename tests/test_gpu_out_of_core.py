@@ -70,3 +70,22 @@ def test_v20_out_of_core_8192_under_256_mb(dg, budget):
     assert dg.device_bytes() <= 256 << 20
     after = [float(Cm[i, j]) for i, j in idx]
     assert bench.spot_check(before, after, idx, M, K, 0, 1.0, 1.0) <= 1.0
+
+
+def test_buffers_of_an_earlier_shape_do_not_sit_beside_the_blocks(dg, monkeypatch):
+    """An in-core call of another shape leaves ~100 MB of staging buffers cached in the context.  The blocked run that follows
+    sizes its blocks to the budget, so those buffers have to be given back first (run_host_single: release_cached) — without
+    a dgemm_b200_shutdown() in between, which is what a real caller would not think of."""
+    M0 = 2048
+    A, B, C0 = gu.make_inputs(M0, M0, M0)
+    dg.mydgemm_gpu_v20(M0, M0, M0, 1.0, A, M0, B, M0, 1.0, C0.copy(order="F"), M0)
+    assert dg.device_bytes() > 90 << 20
+    M, N, K = 1000, 1003, 997
+    limit = WS + (12 << 20)
+    monkeypatch.setenv("DGEMM_B200_HBM_BUDGET", str(limit))
+    dg.reload_env()
+    A, B, C0 = gu.make_inputs(M, N, K, (7, 3, 5))
+    Cg = C0.copy(order="F")
+    dg.mydgemm_gpu_v20(M, N, K, 2.5, A, A.shape[0], B, B.shape[0], 0.5, Cg, Cg.shape[0])
+    gu.check(M, N, K, 2.5, A, B, 0.5, C0, Cg)
+    assert dg.device_bytes() <= limit, "buffers of the earlier call are still allocated next to the blocks"
