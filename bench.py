@@ -477,12 +477,22 @@ def main():
     c0 = [float(gen_signed(3, np.array([i]), np.array([n0 + j]))[0]) for i, j in idx]
     # n passes of (C <- A*B + C): same as one pass with alpha = n on the original C (the bound scales with alpha)
     value_check = spot_check(c0, got, idx, M, K, n0, float(n_pass), 1.0)
+    # ... and whole 192 x 16 blocks of it through the oracle: corners, stream-K tail tiles, tile seams
+    import oracle_lib as ol
+    vblocks = parity_block_positions(M, ncols, [], 4242 + rank)
+    Cv = Cm[: M * ncols].view(ncols, M)
+    value_blocks = parity_blocks(
+        vblocks, K, n0, float(n_pass), 1.0,
+        lambda b: ol.fill_signed(b[2], b[3], b[2], 3, row0=b[0], col0=n0 + b[1]),
+        lambda b: Cv[b[1]: b[1] + b[3], b[0]: b[0] + b[2]].cpu().numpy().T)
     if N > 1:
-        vc = torch.tensor([value_check], dtype=torch.float64, device=dev)
+        vc = torch.tensor([value_check, value_blocks], dtype=torch.float64, device=dev)
         dist.all_reduce(vc, op=dist.ReduceOp.MAX)
-        value_check = float(vc.item())
+        value_check, value_blocks = float(vc[0].item()), float(vc[1].item())
     if not value_check <= 1.0:
         raise SystemExit(f"bench.py: timed result is WRONG: max |err|/bound = {value_check}")
+    if not value_blocks <= 2.0:
+        raise SystemExit(f"bench.py: timed result is WRONG: block parity max |err|/bound = {value_blocks}")
     total_ms = ev[0].elapsed_time(ev[steps])
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
     if N > 1:
@@ -594,6 +604,9 @@ def main():
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "cublas_ceiling": cublas,
         "spot_check_max_err_over_bound": value_check,
+        "parity_blocks_max_ratio": value_blocks,
+        "parity_blocks": f"{len(vblocks)} blocks of {BLOCK_H} x {BLOCK_W} outputs per rank (corners, stream-K tail tiles, tile "
+                         "seams) after the timed region, every entry against oracle_dgemm_k18 on compact copies; bound c = 2",
         "pct_of_fp64_peak": 100.0 * value / (N * peak),
     }
     if parity is not None:
@@ -899,6 +912,58 @@ def configs_sweep(torch, dg, dev, n_sms, sm_mhz):
             "shapes": rows}
 
 
+BLOCK_H, BLOCK_W = 192, 16   # the reference's M_BLOCKING rows x one packed sliver of B (kernel18.h:7, :660)
+
+
+def parity_block_positions(M, ncols, seams, seed, count=16):
+    """Where the sampled output blocks of a big panel lie: the four corners (first data-parallel tile, last edge tile), three
+    blocks inside the last rasterisation band's last tile columns (the tiles a launch cuts into stream-K ranges), one block
+    ACROSS every column seam in `seams` (sub-panel / host-panel boundaries: both sides in one block) and random blocks that
+    straddle a 128-row and a 128-column tile boundary.  Returns [(i0, j0, h, w)]."""
+    import numpy as np
+    h, w = min(BLOCK_H, M), min(BLOCK_W, ncols)
+    if h <= 0 or w <= 0:
+        return []
+    rng = np.random.default_rng(seed)
+    ci = lambda i: int(min(max(int(i), 0), M - h))
+    cj = lambda j: int(min(max(int(j), 0), ncols - w))
+    pos = [(0, 0), (M - h, ncols - w), (M - h, 0), (0, ncols - w)]
+    for k in (1, 2, 3):
+        pos.append((ci(M - h - 128 * k + 32), cj(ncols - w - 128 * k + 8)))
+    for c in seams:
+        if 0 < c < ncols:
+            pos.append((ci(128 * int(rng.integers(max(1, M // 128))) + 32), cj(c - w // 2)))
+    while len(pos) < count:
+        pos.append((ci(128 * int(rng.integers(max(1, M // 128))) + 32), cj(128 * int(rng.integers(max(1, ncols // 128))) + 120)))
+    out = []
+    for q in pos:
+        if q not in out:
+            out.append(q)
+    return [(i, j, h, w) for i, j in out]
+
+
+def parity_blocks(blocks, K, n0, alpha, beta, before, after):
+    """SURVEY.md 8(c) for sizes the oracle cannot run whole: every block's 192 rows of A and 16 columns of B are regenerated
+    compactly (counter-based generator, seeds 1 / 2 as on the device), pushed through the oracle's kernel18 restatement
+    (oracle_dgemm_k18, reference include/kernel18.h:629-671 on the compact copies) with the block of C before the pass, and the
+    block of C after the pass is held to the north-star bound, every entry.  before / after: (i0, j0, h, w) -> F-ordered
+    h x w array.  Checker only (never timed).  Returns max |err| / bound over all entries of all blocks (<= 2 passes)."""
+    import numpy as np
+    import oracle_lib as ol
+    worst = 0.0
+    for blk in blocks:
+        i0, j0, h, w = blk
+        Ab = ol.fill_signed(h, K, h, 1, row0=i0, col0=0)
+        Bb = ol.fill_signed(K, w, K, 2, row0=0, col0=n0 + j0)
+        C0 = np.asfortranarray(before(blk), dtype=np.float64)
+        got = np.asfortranarray(after(blk), dtype=np.float64)
+        want = C0.copy(order="F")
+        ol.oracle_k18(h, w, K, alpha, Ab, Bb, beta, want)
+        r = ol.bound_ratio(h, w, K, alpha, Ab, Bb, beta, C0, got, want)[0]
+        worst = max(worst, r if r == r else float("inf"))
+    return worst
+
+
 def gen_signed(seed, rows, cols):
     """numpy copy of the counter-based input generator (dgemm_b200_fill_signed): entry (i, j) = f(seed, i, j).
     rows / cols are integer arrays of equal length; returns float64 values.  Used only to spot-check bench results."""
@@ -991,9 +1056,19 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
     rng = np.random.default_rng(1234 + rank)
     idx = [(int(rng.integers(M)), int(rng.integers(ncols))) for _ in range(6)] + [(M - 1, ncols - 1), (0, 0)]
     before = [float(hC[j * M + i]) for i, j in idx]
+    # whole blocks as well: across every seam of the schedule's column sub-panels / host panels
+    if N > 1:
+        seams = sorted({c["c0"] for c in dg.rank_plan(M, ncols, K, N, rank, kb, beta != 0.0)["calls"]})
+    else:
+        seams = dg.host_plan(M, Nn, K, alpha, beta)[0]
+    eblocks = parity_block_positions(M, ncols, seams, 777 + rank, count=max(16, len(seams) + 10))
+    hCv = hC.numpy().reshape(ncols, M)
+    cut = lambda b: hCv[b[1]: b[1] + b[3], b[0]: b[0] + b[2]].T.copy(order="F")
+    before_blocks = {b: cut(b) for b in eblocks}
     tl = one(30000 if N > 1 else 0)
     after = [float(hC[j * M + i]) for i, j in idx]
     check = spot_check(before, after, idx, M, K, n0, alpha, beta)
+    check_blocks = parity_blocks(eblocks, K, n0, alpha, beta, lambda b: before_blocks[b], cut)
     host_barrier()
     torch.cuda.synchronize()
     dg.reset_launch_count()
@@ -1014,9 +1089,9 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
         b = torch.tensor([h2d, d2h, launches], dtype=torch.int64, device=dev)
         dist.all_reduce(b, op=dist.ReduceOp.SUM)
         h2d, d2h, launches = int(b[0].item()), int(b[1].item()), int(b[2].item())
-        ck = torch.tensor([check], dtype=torch.float64, device=dev)
+        ck = torch.tensor([check, check_blocks], dtype=torch.float64, device=dev)
         dist.all_reduce(ck, op=dist.ReduceOp.MAX)
-        check = float(ck.item())
+        check, check_blocks = float(ck[0].item()), float(ck[1].item())
         # where one pass spends its time, per rank (CUDA events inside the library, ms since the pass began)
         mine = summarise_timeline(tl)
         allr = [None] * N
@@ -1036,7 +1111,12 @@ def run_e2e(torch, dist, dg, N, rank, dev, M, Nn, K, alpha, beta, nb, kb, A_ptr,
                                "ranks": allt}, f)
     if not check <= 1.0:
         raise SystemExit(f"bench.py: end-to-end result is WRONG: max |err|/bound = {check}")
+    if not check_blocks <= 2.0:
+        raise SystemExit(f"bench.py: end-to-end result is WRONG: block parity max |err|/bound = {check_blocks}")
     return {"value": 2.0 * M * Nn * K * reps / dt / 1e12, "spot_check_max_err_over_bound": check,
+            "parity_blocks_max_ratio": check_blocks,
+            "parity_blocks": f"{len(eblocks)} blocks of {BLOCK_H} x {BLOCK_W} outputs per rank incl. one across every column seam "
+                             "of the schedule, every entry against oracle_dgemm_k18 on compact copies; bound c = 2",
             "spot_check": f"{len(idx)} entries per rank recomputed on the host in long double", "unit": UNIT, "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * dt / reps, "reps": reps,
             "ms_per_rep_this_rank": [round(1e3 * x, 2) for x in per_rep], "gpu_launches": launches,

@@ -177,12 +177,34 @@ PATCHED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 
 @pytest.mark.skipif(not os.path.exists(PATCHED), reason="oracle/_ref/dgemm_x86_patched not built (tools/patch_reference.sh "
                                                         "needs the reference tree, which exists in the build container)")
+PATCHED_ORACLE = PATCHED + "_oracle"
+
+
+@pytest.mark.skipif(not os.path.exists(PATCHED_ORACLE), reason="oracle/_ref/dgemm_x86_patched_oracle not built "
+                                                               "(tools/patch_reference.sh, build container only)")
+@pytest.mark.parametrize("kernel", [20, 21, 18])
+def test_patched_reference_harness_verifies_the_gpu_kernels_against_a_cpu_cblas(kernel):
+    """The same patched reference harness, linked so that cblas_dgemm — the harness's own verification call, test.c:38 — is
+    the plain-C kernel18 restatement (oracle/mkl_shim.c) and NOT the B200 library.  Here `./dgemm_x86 20` and `21` compare
+    mydgemm_gpu_v20 / v21 with an independent CPU result through the reference's own 1e-2 check (test.c:36-43, exit -3 on a
+    mismatch); in the B200-served binary below those two cases would compare the GPU with itself.  18: the harness and the
+    stand-in agree with the reference's own kernel, so a pass means something."""
+    import re
+    import subprocess
+    env = dict(os.environ, DGEMM_X86_MAX_SIZE="500", OMP_NUM_THREADS="2")
+    r = subprocess.run([PATCHED_ORACLE, str(kernel)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    sizes = re.findall(r"^M=N=K=(\d+):$", r.stdout, flags=re.M)
+    assert sizes == ["100", "200", "300", "400", "500"]
+
+
 @pytest.mark.parametrize("kernel", [0, 18, 19, 20, 21])
 def test_patched_reference_harness_dispatches_every_kernel_number(kernel):
     """The reference's own test.c / utils.c / kernels.h with the INTEGRATION.md patch applied (tools/patch_reference.sh), built
     against libdgemm_b200.so: `./dgemm_x86 N` for the reference's kernels, for kernel 0 (cblas_dgemm, served by the B200) and
     for the two GPU kernel numbers.  First five sizes; the harness verifies every kernel against cblas_dgemm with its own
-    1e-2 check (test.c:36-43) and exits -3 on a mismatch, -6 when a GPU kernel reports an error."""
+    1e-2 check (test.c:36-43) and exits -3 on a mismatch, -6 when a GPU kernel reports an error.  (In THIS binary cblas_dgemm is
+    the B200 too, so 20 / 21 prove dispatch only; their correctness check is the _oracle binary's test above.)"""
     import re
     import subprocess
     env = dict(os.environ, DGEMM_X86_MAX_SIZE="500", OMP_NUM_THREADS="2")   # two threads: even row bands (SURVEY.md F3)

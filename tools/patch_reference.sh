@@ -38,5 +38,18 @@ make build > build.log 2>&1 || { cat build.log >&2; exit 3; }
 mkdir -p "$REPO/oracle/_ref"
 cp dgemm_x86 "$REPO/oracle/_ref/dgemm_x86_patched"
 echo "patch_reference: built $REPO/oracle/_ref/dgemm_x86_patched (kernel numbers 0..21); patched copy in $SCRATCH"
+# --- the same patched tree once more, with cblas_dgemm served by the CHECKER (oracle/mkl_shim.c -> the kernel18 restatement
+#     in liboracle.so) instead of by the B200 library: in THIS binary the harness's own 1e-2 verification of kernels 20 / 21
+#     (reference test.c:36-43) compares the GPU with an independent CPU result, not the GPU with itself
+if [ -f "$REPO/oracle/liboracle.so" ]; then
+  cp "$REPO/oracle/mkl_shim.c" "$REPO/oracle/mkl.h" .
+  rm -f dgemm_x86
+  make build INCFLAGS="-I. -I$REPO/include" \
+       LDFLAGS="-L$PKG -L$REPO/oracle -Wl,--no-as-needed -ldgemm_b200 -loracle -Wl,-rpath,'\$\$ORIGIN/../../optimizing-dgemm-on-intel-cpus-with-avx512f_b200' -Wl,-rpath,'\$\$ORIGIN/..' -lpthread -lm -ldl" \
+       > build_oracle.log 2>&1 || { cat build_oracle.log >&2; exit 3; }
+  cp dgemm_x86 "$REPO/oracle/_ref/dgemm_x86_patched_oracle"
+  rm -f mkl_shim.c mkl.h
+  echo "patch_reference: built $REPO/oracle/_ref/dgemm_x86_patched_oracle (cblas_dgemm = the plain-C oracle)"
+fi
 diff -u "$REF_ROOT/test.c" test.c > "$SCRATCH/test.c.diff" || true
 diff -u "$REF_ROOT/utils.c" utils.c > "$SCRATCH/utils.c.diff" || true
