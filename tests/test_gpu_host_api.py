@@ -175,8 +175,6 @@ def test_add_scaled_is_exact(dg):
 PATCHED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "dgemm_x86_patched")
 
 
-@pytest.mark.skipif(not os.path.exists(PATCHED), reason="oracle/_ref/dgemm_x86_patched not built (tools/patch_reference.sh "
-                                                        "needs the reference tree, which exists in the build container)")
 PATCHED_ORACLE = PATCHED + "_oracle"
 
 
@@ -198,6 +196,8 @@ def test_patched_reference_harness_verifies_the_gpu_kernels_against_a_cpu_cblas(
     assert sizes == ["100", "200", "300", "400", "500"]
 
 
+@pytest.mark.skipif(not os.path.exists(PATCHED), reason="oracle/_ref/dgemm_x86_patched not built (tools/patch_reference.sh "
+                                                        "needs the reference tree, which exists in the build container)")
 @pytest.mark.parametrize("kernel", [0, 18, 19, 20, 21])
 def test_patched_reference_harness_dispatches_every_kernel_number(kernel):
     """The reference's own test.c / utils.c / kernels.h with the INTEGRATION.md patch applied (tools/patch_reference.sh), built
