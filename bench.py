@@ -538,7 +538,12 @@ def main():
         torch.cuda.synchronize()
         host_barrier()
         if rank == 0:
-            e2e_v21 = run_v21(torch, dg, N, int(os.environ.get("BENCH_V21_SIZE", "32768")), 2)
+            # 32768^3 on any N; at 8 GPUs also the headline 65536^3 (3 x 34 GB of pinned host memory in this one process)
+            sizes = [int(x) for x in os.environ.get("BENCH_V21_SIZE", "32768,65536" if N >= 8 else "32768").split(",")]
+            runs = [run_v21(torch, dg, N, sz, 2) for sz in sizes]
+            e2e_v21 = runs[-1]
+            if len(runs) > 1:
+                e2e_v21["other_sizes"] = runs[:-1]
         host_barrier()
 
     # BASELINE configs 1-3 (2048^3 both scalar pairs, 256..8192, the edge shapes, the skinny one) in the driver-run line
@@ -626,9 +631,10 @@ def main():
 
 
 def parity_panels(torch, dist, dg, N, rank, dev, host_group):
-    """Whole-panel parity of BOTH multi-GPU paths at sizes the oracle finishes in seconds, every entry, bound c = 2:
-      (i)  dgemm_b200_rank_pipeline  host operands -> pipelined uploads, NVLink pulls behind sequence words, deferred C, D2H
-      (ii) the fused device step     sharded_dgemm_step_fused over dgemm_b200_device_fetch (what `value` times)
+    """Whole-panel parity of ALL THREE multi-GPU paths at sizes the oracle finishes in seconds, every entry, bound c = 2:
+      (i)   dgemm_b200_rank_pipeline  host operands -> pipelined uploads, NVLink pulls behind sequence words, deferred C, D2H
+      (ii)  the fused device step     sharded_dgemm_step_fused over dgemm_b200_device_fetch (what `value` times)
+      (iii) mydgemm_gpu_v21           one call with the reference's signature from rank 0, all N GPUs (what `e2e_v21` times)
     The oracle (oracle/liboracle.so, kernel18's arithmetic restated) is the CHECKER here, exactly as in tests/: it is never
     timed and nothing it computes reaches a reported number."""
     import numpy as np
@@ -688,14 +694,30 @@ def parity_panels(torch, dist, dg, N, rank, dev, host_group):
         dist.barrier(group=host_group)
         dg.free(x)
         del nanfill, dB, dC
-        both = torch.tensor([r1, r2], dtype=torch.float64, device=dev)
+        # (iii) mydgemm_gpu_v21, the reference's 11-argument signature (include/kernel19.h:678-689): ONE call from rank 0
+        # drives all N GPUs on the whole problem while the other ranks wait; every entry of C against the oracle
+        r3 = -1.0   # -1: rank 0 cannot see all N GPUs (one visible device per rank), leg not run
+        if rank == 0 and dg.device_count() >= N:
+            Bf, Cf0 = ol.fill_signed(K, Nn, K, 2), ol.fill_signed(M, Nn, M, 3)
+            wantf = Cf0.copy(order="F")
+            ol.oracle_k18(M, Nn, K, alpha, Ah, Bf, beta, wantf)
+            Cf = Cf0.copy(order="F")
+            dg.lib.dgemm_b200_set_max_gpus(N)
+            dg.mydgemm_gpu_v21(M, Nn, K, alpha, Ah, M, Bf, K, beta, Cf, M)
+            r3 = ol.bound_ratio(M, Nn, K, alpha, Ah, Bf, beta, Cf0, Cf, wantf)[0]
+            if not r3 == r3:
+                r3 = float("inf")
+            del Bf, Cf0, Cf, wantf
+        dist.barrier(group=host_group)
+        both = torch.tensor([r1, r2, r3], dtype=torch.float64, device=dev)
         dist.all_reduce(both, op=dist.ReduceOp.MAX)
-        r1, r2 = float(both[0].item()), float(both[1].item())
+        r1, r2, r3 = float(both[0].item()), float(both[1].item()), float(both[2].item())
         if not (r1 == r1 and r2 == r2):   # NaN: a pull or a multiply ran ahead of its data
             r1 = r2 = float("inf")
         out["cases"].append({"M": M, "N": Nn, "K": K, "alpha": alpha, "beta": beta,
-                             "rank_pipeline_max_ratio": r1, "fused_step_max_ratio": r2})
-        worst = max(worst, r1, r2)
+                             "rank_pipeline_max_ratio": r1, "fused_step_max_ratio": r2,
+                             "v21_max_ratio": r3 if r3 >= 0.0 else None})
+        worst = max(worst, r1, r2, r3)
     out["max_ratio"] = worst
     return out
 
