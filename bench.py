@@ -567,6 +567,8 @@ def main():
     peak = n_sms * FLOP_PER_CLK_PER_SM * sm_mhz * 1e6 / 1e12
     probe = load_profile_json("profiles/fp64_peak_probe.json")
     traffic = load_profile_json("profiles/ncu_traffic.json")
+    sha_now, sha_stored = kernel_sources_sha16(), (traffic or {}).get("kernel_sources_sha16")
+    traffic_fresh = sha_now is not None and sha_now == sha_stored
     roofline = {"bound": "tensor", "pipe": "fp64 DMMA (mma.sync.m8n8k4.f64)", "achieved": achieved, "peak": peak,
                 "unit": UNIT, "frac": achieved / peak,
                 "peak_source": f"{n_sms} SMs x 128 flop/clk/SM x {sm_mhz:.0f} MHz sampled by nvidia-smi during the "
@@ -574,9 +576,12 @@ def main():
                                "127.5 flop/clk/SM with DMMA alone)",
                 "dmma_probe_tflops": (probe or {}).get("dmma_tflops"),
                 "frac_of_dmma_probe": (achieved / probe["dmma_tflops"]) if probe and probe.get("dmma_tflops") else None,
-                "traffic": (traffic or {}).get(str(size)) if N == 1 else None,
-                "traffic_source": "STORED: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of "
-                                  "this kernel at this size (profiles/ncu_traffic.json) -- not measured in this run"
+                "traffic": (traffic or {}).get(str(size)) if N == 1 and traffic_fresh else None,
+                "traffic_source": ("STORED: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of "
+                                   "this kernel at this size (profiles/ncu_traffic.json), taken on a build of the SAME kernel "
+                                   f"sources (fingerprint {sha_now}) -- not measured in this run" if traffic_fresh else
+                                   f"stale: profiles/ncu_traffic.json was captured on kernel sources {sha_stored}, this build "
+                                   f"is {sha_now}; re-capture with ncu --set full and tools/stamp_traffic.py")
                                   if N == 1 else "no single-kernel capture of the sharded step (see profiles/ for the "
                                                  "fused-fetch kernel's ncu counters)",
                 "algorithmic_bytes": 8.0 * (M * K + K * Nn + 2 * M * Nn),
@@ -1014,6 +1019,24 @@ def spot_check(before, after, idx, M, K, n0, alpha, beta):
         bound = 2.0 * K * 2.220446049250313e-16 * (abs(alpha) * mag + abs(beta * b))
         worst = max(worst, abs(a - want) / bound)
     return worst
+
+
+KERNEL_SOURCES = ("dgemm_tma_kernel.cuh", "dgemm_device.cuh", "dgemm_kernels.cu", "dgemm_params.h", "dgemm_launch.h")
+
+
+def kernel_sources_sha16():
+    """Fingerprint of the sources the dominant kernel is compiled from.  profiles/ncu_traffic.json carries the fingerprint of
+    the build its DRAM-traffic figures were captured on (tools/stamp_traffic.py); a different one here means the stored figure
+    describes another kernel, and the bench line then says so instead of repeating it."""
+    import hashlib
+    h = hashlib.sha256()
+    try:
+        for name in KERNEL_SOURCES:
+            with open(os.path.join(ROOT, "optimizing-dgemm-on-intel-cpus-with-avx512f_b200", "csrc", name), "rb") as f:
+                h.update(f.read())
+    except OSError:
+        return None
+    return h.hexdigest()[:16]
 
 
 def load_profile_json(rel):
