@@ -1,6 +1,7 @@
 /* test.c — the reference's CLI harness (reference test.c:1-54) for the GPU kernel numbers.
  *
- *   dgemm_b200 <kernel_num> [max_size] [alpha beta]      kernel_num: 20 = one B200, 21 = all B200s of the box
+ *   dgemm_b200 <kernel_num> [max_size] [alpha beta]      kernel_num: 20 = one B200, 21 = all B200s of the box,
+ *                                                        22-27 = the six rungs of the optimisation ladder
  *
  * Same flow and the same two output lines per size as the reference ("M=N=K=%d:" and "Average elasped time: %f
  * second, performance: %f GFLOPS." — test.c:35,49 — so data/data.sh-style scraping keeps working): sizes 100..3000
@@ -23,8 +24,8 @@ int main(int argc, char *argv[]) {
     exit(-1);
   }
   int kernel_num = atoi(argv[1]);
-  if (kernel_num != 20 && kernel_num != 21) {
-    printf("Please enter a valid kernel number (20-21).\n");
+  if (kernel_num < 20 || kernel_num > 27) { /* 22-27: the six rungs of the GPU optimisation ladder (include/kernel20.h) */
+    printf("Please enter a valid kernel number (20-27).\n");
     exit(-2);
   }
   int max_size = argc > 2 ? atoi(argv[2]) : 3000;

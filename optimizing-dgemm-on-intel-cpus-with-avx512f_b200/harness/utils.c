@@ -75,6 +75,8 @@ void test_kernel(int kernel_num, int m, int n, int k, double alpha, double *A, d
   switch (kernel_num) {
     case 20: test_mydgemm_v20(m, n, k, alpha, A, B, beta, C); break;
     case 21: test_mydgemm_v21(m, n, k, alpha, A, B, beta, C); break;
+    case 22: case 23: case 24: case 25: case 26: case 27: /* the ladder's rungs, include/kernel20.h */
+      test_mydgemm_ladder(kernel_num, m, n, k, alpha, A, B, beta, C); break;
     default: break;
   }
 }

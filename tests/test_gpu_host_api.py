@@ -171,7 +171,7 @@ def test_add_scaled_is_exact(dg):
         dg.add_scaled(8, 8, 1.0, dX.ptr, 4, dC.ptr, 8)          # ldx < M
 
 
-# ---- ONE harness binary for kernel numbers 0..21 (reference test.c:8-19, utils.c:167-191, kernels.h:1-19) -----------------
+# ---- ONE harness binary for kernel numbers 0..27 (reference test.c:8-19, utils.c:167-191, kernels.h:1-19) -----------------
 PATCHED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "dgemm_x86_patched")
 
 
@@ -216,9 +216,36 @@ def test_patched_reference_harness_dispatches_every_kernel_number(kernel):
     assert all(float(g) > 0 for _t, g in perf)
 
 
-def test_patched_reference_harness_rejects_kernel_22():
+def test_patched_reference_harness_rejects_kernel_28():
     if not os.path.exists(PATCHED):
         pytest.skip("oracle/_ref/dgemm_x86_patched not built")
     import subprocess
-    r = subprocess.run([PATCHED, "22"], capture_output=True, text=True, timeout=60)
-    assert r.returncode == 254 and "0-21" in r.stdout     # exit(-2), reference test.c:16-19 with the widened range
+    r = subprocess.run([PATCHED, "28"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 254 and "0-27" in r.stdout     # exit(-2), reference test.c:16-19 with the widened range
+
+
+@pytest.mark.skipif(not os.path.exists(PATCHED_ORACLE), reason="oracle/_ref/dgemm_x86_patched_oracle not built")
+@pytest.mark.parametrize("kernel", [22, 23, 24, 25, 26, 27])
+def test_ladder_rungs_are_kernel_numbers_of_the_reference_harness(kernel):
+    """`./dgemm_x86 22` .. `27`: the six rungs of the GPU optimisation ladder dispatched the way the reference dispatches its
+    tutorial steps 1 .. 19 (utils.c:167-191), each printing the reference's two lines and each verified by the reference's own
+    check against a CPU cblas_dgemm (the oracle-served binary).  First three sizes (rung 22 is one thread per entry)."""
+    import re
+    import subprocess
+    env = dict(os.environ, DGEMM_X86_MAX_SIZE="300")
+    r = subprocess.run([PATCHED_ORACLE, str(kernel)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert re.findall(r"^M=N=K=(\d+):$", r.stdout, flags=re.M) == ["100", "200", "300"]
+    assert len(re.findall(r"^Average elasped time: [0-9.]+ second, performance: [0-9.]+ GFLOPS\.$", r.stdout, flags=re.M)) == 3
+
+
+@pytest.mark.parametrize("kernel", [22, 25, 27])
+def test_ladder_rungs_in_the_repo_harness(kernel):
+    """bin/dgemm_b200 22 .. 27 (harness/test.c): same dispatch in this repo's own harness, verified with the north-star bound."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(PATCHED), "..", "..", "optimizing-dgemm-on-intel-cpus-with-avx512f_b200", "bin", "dgemm_b200")
+    if not os.path.exists(exe):
+        pytest.skip("bin/dgemm_b200 not built (make harness)")
+    r = subprocess.run([exe, str(kernel), "300"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert r.stdout.count("Average elasped time:") == 3
